@@ -1,0 +1,245 @@
+/*
+ * omnia_recall.h -- C ABI of the B200 recall engine (libomnia_recall.so).
+ *
+ * This is the drop-in boundary for ONE path of AltairaLabs/Omnia: semantic recall
+ * over the agent memory store and the near-duplicate scan of memory consolidation.
+ * The reference has no FFI for this path (it is pure Go issuing pgvector SQL), so
+ * every entry point below names the reference interface it stands in for; a Go
+ * `gpustore` package binds them with cgo (INTEGRATION.md shows the stubs).
+ *
+ * Conventions
+ *  - Every function returns 0 (OMR_OK) or a negative OMR_E_* code; the message for
+ *    the calling thread's last failure is omr_last_error().  Nothing aborts.
+ *  - Host-pointer arguments are only read/written during the call (cgo pointer rule);
+ *    the library copies what it keeps.
+ *  - A store handle may be used from many threads; calls on one store serialise.
+ *  - uuids are 16 raw bytes in network order, compared bytewise as Postgres does.
+ *  - Entry points whose name contains `_device_` take DEVICE pointers and a CUDA
+ *    stream (cudaStream_t passed as void*); they are what bench.py times with the
+ *    inputs already resident in HBM, and what the multi-GPU host code drives.
+ *  - There is no CPU fallback: without a CUDA device omr_open fails.
+ */
+#ifndef OMNIA_RECALL_H_
+#define OMNIA_RECALL_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define OMR_API __attribute__((visibility("default")))
+#else
+#define OMR_API
+#endif
+
+#define OMR_OK 0
+#define OMR_E_INVALID (-1)   /* bad argument */
+#define OMR_E_CUDA (-2)      /* a CUDA call failed */
+#define OMR_E_DIM (-3)       /* embedding dimension mismatch (hnsw_ef_search_test.go:126-144 wants an error) */
+#define OMR_E_CAPACITY (-4)  /* store or output buffer full */
+#define OMR_E_NOT_FOUND (-5) /* memory.ErrNotFound, internal/memory/store.go:69 */
+#define OMR_E_WORKSPACE (-6) /* errWorkspaceRequired, internal/memory/store.go:60 */
+
+/* Row flag bits (the boolean columns the recall WHERE clause reads, store.go:250-258). */
+#define OMR_ROW_FORGOTTEN 1u     /* memory_entities.forgotten */
+#define OMR_ROW_SUPERSEDED 2u    /* memory_observations.superseded_by IS NOT NULL */
+#define OMR_ROW_HAS_EMBEDDING 4u /* memory_observations.embedding IS NOT NULL */
+#define OMR_ROW_MUTABLE 8u       /* mutability = 'mutable' (consolidation/prefilter.go:125-126) */
+
+/* How a scope column is matched.  Single-tier recall uses ANY / EQ
+ * (`$2::text IS NULL OR e.virtual_user_id = $2`, store.go:252-253); multi-tier uses
+ * NULL_ONLY / NULL_OR_EQ (internal/memory/retrieve_multi_tier.go:313-328). */
+#define OMR_MATCH_ANY 0
+#define OMR_MATCH_NULL_ONLY 1
+#define OMR_MATCH_EQ 2
+#define OMR_MATCH_NULL_OR_EQ 3
+
+#define OMR_NO_EXPIRY INT64_MAX /* valid_until IS NULL */
+#define OMR_MAX_DIM 2000        /* internal/memory/postgres/embedding_schema.go:64-68 */
+
+typedef struct omr_store omr_store;
+
+/* Replaces the vector column created by EnsureEmbeddingSchema
+ * (internal/memory/postgres/embedding_schema.go:125-151): `dim` fixes the width. */
+typedef struct omr_config {
+  int32_t dim;              /* 1..OMR_MAX_DIM */
+  int32_t device;           /* CUDA ordinal */
+  int64_t capacity;         /* rows this shard can hold */
+  int64_t row_base;         /* global row id = row_base + local_row * row_stride */
+  int64_t row_stride;       /* 0 is read as 1 */
+  float candidate_margin;   /* bf16 stage safety margin in cosine units; <= 0 -> 1e-3 */
+  int32_t sub_bucket;       /* 0 = choose from k; else 32 / 64 / 128 / 256 */
+  int32_t rescore_width;    /* 0 = choose from k; candidates rescored exactly per query */
+  int32_t force_path;       /* 0 auto, 1 streaming scorer, 2 tensor-core scorer, 3 exact scan only */
+} omr_config;
+
+OMR_API int omr_open(const omr_config* cfg, omr_store** out);
+OMR_API void omr_close(omr_store* s);
+OMR_API const char* omr_last_error(void);
+OMR_API int64_t omr_count(const omr_store* s); /* rows in use, tombstones included */
+
+/* ---- ingest ----------------------------------------------------------------
+ * Bulk form of UpdateEmbedding / UpdateObservationEmbedding
+ * (internal/memory/store_write.go:557-600) for the start-up load and the re-embed
+ * worker (internal/memory/reembed_worker.go:181-218).  Struct-of-arrays with small
+ * string tables so a million rows cross the boundary without a million strings.
+ * Any array pointer may be NULL: ids default to the row number, entity = observation,
+ * user/agent NULL, confidence 1, flags HAS_EMBEDDING|MUTABLE, no expiry, kind/purpose 0. */
+typedef struct omr_bulk {
+  int64_t n;
+  const float* vectors;            /* [n][dim], host */
+  const uint8_t* observation_ids;  /* [n][16] */
+  const uint8_t* entity_ids;       /* [n][16] */
+  const char* const* workspaces;   int32_t n_workspaces;  const uint32_t* workspace_idx; /* [n] */
+  const char* const* users;        int32_t n_users;       const int32_t* user_idx;       /* -1 = NULL */
+  const char* const* agents;       int32_t n_agents;      const int32_t* agent_idx;      /* -1 = NULL */
+  const char* const* kinds;        int32_t n_kinds;       const uint16_t* kind_idx;
+  const char* const* purposes;     int32_t n_purposes;    const uint16_t* purpose_idx;
+  const float* confidence;
+  const uint8_t* flags;
+  const int64_t* valid_until_us;
+} omr_bulk;
+OMR_API int omr_bulk_load(omr_store* s, const omr_bulk* b);
+
+/* One row with its scope as strings.  If observation_id is already resident the row is
+ * overwritten in place (UpdateObservationEmbedding, store_write.go:580-600). */
+typedef struct omr_row {
+  uint8_t observation_id[16];
+  uint8_t entity_id[16];
+  const char* workspace_id;    /* required */
+  const char* virtual_user_id; /* NULL = SQL NULL */
+  const char* agent_id;        /* NULL = SQL NULL */
+  const char* kind;
+  const char* purpose;
+  float confidence;
+  uint32_t flags;
+  int64_t valid_until_us;
+} omr_row;
+OMR_API int omr_upsert(omr_store* s, const omr_row* row, const float* vec, int32_t dim);
+/* UpdateEmbedding (store_write.go:557-578): new vector for the entity's latest observation. */
+OMR_API int omr_update_embedding(omr_store* s, const uint8_t entity_id[16], const float* vec, int32_t dim);
+
+/* Row-state edits that change recall eligibility. */
+OMR_API int omr_set_row_flags(omr_store* s, const uint8_t observation_id[16], uint32_t set_mask, uint32_t clear_mask);
+OMR_API int omr_set_entity_flags(omr_store* s, const uint8_t entity_id[16], uint32_t set_mask, uint32_t clear_mask);
+OMR_API int omr_set_valid_until(omr_store* s, const uint8_t observation_id[16], int64_t valid_until_us);
+OMR_API int omr_set_confidence(omr_store* s, const uint8_t observation_id[16], float confidence);
+OMR_API int omr_delete_entity(omr_store* s, const uint8_t entity_id[16]); /* hard delete, store_delete.go:60-103 */
+
+/* ---- recall ------------------------------------------------------------------
+ * The WHERE clause of the recall queries (reference row a8). */
+typedef struct omr_filter {
+  const char* workspace_id;     /* required: e.workspace_id = $1 */
+  const char* virtual_user_id;  int32_t user_mode;
+  const char* agent_id;         int32_t agent_mode;
+  const char* const* kinds;     int32_t n_kinds;     /* kind = ANY($types); 0 = no constraint */
+  const char* const* purposes;  int32_t n_purposes;
+  float min_confidence;         /* o.confidence >= $8 */
+  double max_distance;          /* `o.embedding <=> $1 <= $5` (store_read.go:278); >= 2 or NaN = none */
+  int64_t now_us;               /* the query's now() for `valid_until > now()` */
+} omr_filter;
+
+typedef struct omr_hit {
+  uint8_t observation_id[16];
+  uint8_t entity_id[16];
+  double distance; /* pgvector cosine distance; similarity = 1 - distance (store_read.go:268) */
+  int64_t row;     /* global row id */
+} omr_hit;
+
+/* `ORDER BY o.embedding <=> $q LIMIT k` under a filter, for a batch of queries.
+ * Replaces the SQL of FindSimilarObservations (internal/memory/store_read.go:243-306) and
+ * the cosine_ann CTEs (internal/memory/store.go:240-261,
+ * internal/memory/retrieve_multi_tier_hybrid.go:78-96).  query_filter[i] picks the filter
+ * of query i (NULL = filter 0 for all).  hits is [nq][k]; counts[i] <= k entries are valid,
+ * nearest first, ties by row id. */
+OMR_API int omr_search(omr_store* s, const float* queries, int32_t nq, int32_t dim, const omr_filter* filters,
+               int32_t n_filters, const int32_t* query_filter, int32_t k, omr_hit* hits, int32_t* counts);
+
+/* Same query as omr_search with struct-of-arrays results and no uuid lookup: rows [nq][k]
+ * global row ids (-1 pad), distances [nq][k] (+inf pad).  For callers that keep their own
+ * row -> id table (the spliced-SQL drop-in passes row ids straight to `unnest($ids, $dists)`). */
+OMR_API int omr_search_rows(omr_store* s, const float* queries, int32_t nq, int32_t dim, const omr_filter* filters,
+                            int32_t n_filters, const int32_t* query_filter, int32_t k, int64_t* rows,
+                            double* distances, int32_t* counts);
+
+/* The whole cosine arm of the hybrid query: cosine_ann (top 4*fanout observations) ->
+ * cosine (nearest observation per entity) -> cosine_ranked (LIMIT fanout)
+ * (internal/memory/store.go:240-272).  hits[i] is the entity's nearest observation,
+ * rank = i + 1. */
+OMR_API int omr_cosine_ranked(omr_store* s, const float* query, int32_t dim, const omr_filter* filter, int32_t fanout,
+                      omr_hit* hits, int32_t* count);
+
+/* ---- consolidation near-duplicate scan ---------------------------------------
+ * Replaces BuildEntityDuplicateCandidatesQuery + RunEntityDuplicateCandidates
+ * (internal/memory/consolidation/prefilter.go:112-138,
+ * internal/memory/postgres/consolidation_prefilter.go:176-203).  An entity is represented
+ * by its latest embedded observation (the row UpdateEmbedding targets). */
+typedef struct omr_selfjoin_opts {
+  const char* workspace_id;
+  float similarity_floor;    /* PreFilterOptions.SimilarityFloor, a Go float32 (prefilter.go:18) */
+  int32_t limit;             /* MaxBucketsPerPass; <= 0 = no limit */
+  int32_t require_same_kind; /* e1.kind = e2.kind */
+  int32_t require_mutable;   /* both mutability = 'mutable' */
+} omr_selfjoin_opts;
+
+typedef struct omr_pair {
+  uint8_t canonical_id[16]; /* the smaller entity uuid (e1.id < e2.id) */
+  uint8_t dupe_id[16];
+  double similarity;
+  int64_t canonical_row, dupe_row;
+  uint32_t kind;
+} omr_pair;
+/* Writes min(found, cap) pairs ordered by similarity DESC; *found is the total. */
+OMR_API int omr_selfjoin(omr_store* s, const omr_selfjoin_opts* opts, omr_pair* out, int64_t cap, int64_t* found);
+
+/* ---- device-pointer entry points ----------------------------------------------
+ * Same recall, with queries, bitmaps and results in device memory and the work enqueued
+ * on `stream`.  d_bitmaps is [n_groups][omr_bitmap_words()] (NULL = every live row),
+ * d_query_group [nq] (NULL = group 0), d_max_distance [nq] (NULL = no cutoff).
+ * Outputs: d_rows [nq][k] global row ids (-1 pad), d_dist [nq][k] (+inf pad), d_count [nq].
+ * The call returns after the last kernel is enqueued and the (rare) exact-fallback
+ * decision is read back, i.e. it synchronises the stream once. */
+OMR_API int64_t omr_bitmap_words(const omr_store* s);
+OMR_API int omr_device_build_bitmaps(omr_store* s, const omr_filter* filters, int32_t n_filters, uint32_t* d_bitmaps,
+                             void* stream);
+OMR_API int omr_device_search(omr_store* s, const float* d_queries, int32_t nq, const uint32_t* d_bitmaps, int32_t n_groups,
+                      const int32_t* d_query_group, const double* d_max_distance, int32_t k, int64_t* d_rows,
+                      double* d_dist, int32_t* d_count, void* stream);
+/* Row-sharded stores: merges the G per-shard answers gathered into [G][nq][k]
+ * (the gather itself is an NCCL allgather done by the host code). */
+OMR_API int omr_device_merge_topk(omr_store* s, const int64_t* d_in_rows, const double* d_in_dist, int32_t n_shards,
+                          int32_t nq, int32_t k, int64_t* d_rows, double* d_dist, int32_t* d_count, void* stream);
+
+/* ---- introspection ---------------------------------------------------------------*/
+typedef struct omr_stats {
+  int64_t kernel_launches;   /* kernels this store has enqueued */
+  int64_t searches;          /* query batches */
+  int64_t queries;           /* queries */
+  int64_t rescued_rows;      /* rows rescored because their sub-bucket was suspect */
+  int64_t fallback_queries;  /* queries answered by the exact scan */
+  int32_t last_path;         /* 1 streaming, 2 tensor-core, 3 exact */
+  int32_t last_sub_bucket;
+  int32_t last_rescore_width;
+  int32_t num_sms;
+  double scorer_ms_sum;      /* device time of the approximate scorer, summed (profiling on) */
+  int64_t scorer_timed;      /* batches that sum covers */
+} omr_stats;
+OMR_API int omr_get_stats(const omr_store* s, omr_stats* out);
+/* Brackets the approximate scorer (the dominant kernel) with CUDA events on the search stream
+ * and accumulates its device time in omr_stats; off by default.  Resets the accumulators. */
+OMR_API int omr_set_profiling(omr_store* s, int32_t on);
+OMR_API const char* omr_kind_name(const omr_store* s, uint32_t kind);
+/* Test hook, no reference counterpart: runs query preparation and ONE approximate scorer
+ * (path 1 = streaming, 2 = tensor-core) over every live row and returns the raw packed
+ * candidate keys, [nq][ceil(n/256) * (256/S) * 2] int32 on the host.  A key is the
+ * order-preserving int32 image of the bf16-accurate cosine with its low 8 bits replaced by
+ * the row's offset inside its S-row sub-bucket; INT32_MIN = no eligible row. */
+OMR_API int omr_debug_candidate_keys(omr_store* s, const float* queries, int32_t nq, int32_t path, int32_t S,
+                                     int32_t* out_keys, int64_t out_len);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* OMNIA_RECALL_H_ */

@@ -1,0 +1,348 @@
+// Large-batch scorer: Q * M^T on the 5th-generation tensor cores with the top-k
+// pre-selection fused into the epilogue, so the Q x N score matrix never exists.
+//
+// Replaces, for a whole batch of queries at once, the scan behind
+// `ORDER BY o.embedding <=> $q LIMIT n` (internal/memory/store.go:240-261,
+// internal/memory/retrieve_multi_tier_hybrid.go:78-96) and, in its self-join
+// form, the O(N^2) nested loop of BuildEntityDuplicateCandidatesQuery
+// (internal/memory/consolidation/prefilter.go:112-138).
+//
+// Shape of one CTA (persistent, one per SM, 256 threads):
+//   warp 0      TMA producer: per 64-wide K block, a 128-query x 64 box (A) and a
+//               256-row x 64 box (B) land in 128B-swizzled shared memory.
+//   warp 1      one lane issues tcgen05.mma (M=128 queries, N=256 rows, K=16) four
+//               times per K block into one of two 256-column TMEM accumulators.
+//   warp 2      allocates / frees the 512 TMEM columns.
+//   warps 4-7   epilogue: thread t owns query t of the tile (TMEM lane t), reads its
+//               256 scores 32 columns at a time with tcgen05.ld, applies the scope
+//               bitmap, and keeps the two best per S-row sub-bucket as packed keys.
+// While the epilogue drains accumulator i, the tensor core fills accumulator i^1.
+//
+// Rows and queries are unit-normalised before they are rounded to bf16 (k_ingest.cu),
+// so the accumulator IS the approximate cosine: the norm scaling costs nothing here.
+// The exact fp32->fp64 rescore of the surviving candidates is in k_select.cu.
+//
+// Roofline: tensor for >= ~256 queries (2*Q*N*D flops per launch), HBM below that
+// (the bf16 matrix is read once per launch: consecutive CTAs take the query tiles
+// of the same row tile, so its K blocks are served from L2 after the first read).
+#include "kernels.cuh"
+#include "ptx.cuh"
+
+namespace omr {
+
+namespace {
+
+constexpr int kStages = 4;
+constexpr int kABytes = kQueryTile * kBlockK * 2;  // 16 KB
+constexpr int kBBytes = kTileRows * kBlockK * 2;   // 32 KB
+constexpr int kStageBytes = kABytes + kBBytes;
+constexpr int kNumThreads = 256;
+constexpr int kEpilogueWarp0 = 4;
+constexpr uint32_t kTmemCols = 512;
+
+struct __align__(8) PipeBarriers {
+  uint64_t full[kStages];
+  uint64_t empty[kStages];
+  uint64_t tmem_full[2];
+  uint64_t tmem_empty[2];
+  uint32_t tmem_base;
+};
+
+constexpr int kSmemBytes = kStages * kStageBytes + (int)sizeof(PipeBarriers) + 1024;  // +1024: manual alignment
+
+// Epilogue of the recall scorer: two best keys per sub-bucket for this thread's query.
+template <int S>
+struct Top2Epilogue {
+  const uint32_t* bitmap_row;  // this query's filter-group bitmap, already offset to the group
+  int32_t* out;                // cand_keys row of this query
+  int32_t m1, m2;
+
+  __device__ __forceinline__ void begin_tile() { m1 = kKeyNone; m2 = kKeyNone; }
+
+  // c = 32-column chunk index inside the 256-row tile
+  __device__ __forceinline__ void chunk(int row_tile, int c, const uint32_t (&v)[32]) {
+    const uint32_t mask = __ldg(bitmap_row + (int64_t)row_tile * 8 + c);
+    if (mask == 0xffffffffu) {
+#pragma unroll
+      for (int j = 0; j < 32; j++) top2_insert(m1, m2, pack_key(__uint_as_float(v[j]), (c * 32 + j) & (S - 1)));
+    } else if (mask != 0u) {
+#pragma unroll
+      for (int j = 0; j < 32; j++) {
+        const int32_t key = pack_key(__uint_as_float(v[j]), (c * 32 + j) & (S - 1));
+        top2_insert(m1, m2, ((mask >> j) & 1u) ? key : kKeyNone);
+      }
+    }
+    if (((c + 1) * 32) % S == 0) {
+      const int64_t sb = (int64_t)row_tile * (kTileRows / S) + (c * 32) / S;
+      *reinterpret_cast<int2*>(out + sb * 2) = make_int2(m1, m2);
+      m1 = kKeyNone;
+      m2 = kKeyNone;
+    }
+  }
+};
+
+// Epilogue of the self-join: emit (a, b) for a < b when the approximate cosine clears the
+// (margin-lowered) floor and both rows are members of the join.
+struct PairEpilogue {
+  const uint32_t* member;  // bitmap over rows
+  PairCand* pairs;
+  unsigned long long cap;
+  unsigned long long* count;
+  float threshold;
+  int32_t row_a;
+  bool a_member;
+
+  __device__ __forceinline__ void chunk(int b_tile, int c, const uint32_t (&v)[32]) {
+    const int32_t b0 = b_tile * kTileRows + c * 32;
+    uint32_t mask = __ldg(member + (b0 >> 5));
+    if (!a_member) mask = 0;
+    // rows b <= a are the lower triangle: drop them
+    if (row_a >= b0 + 31) mask = 0;
+    else if (row_a >= b0) mask &= ~((2u << (row_a - b0)) - 1u);
+    uint32_t pass = 0;
+#pragma unroll
+    for (int j = 0; j < 32; j++) pass |= (__uint_as_float(v[j]) >= threshold) ? (1u << j) : 0u;
+    pass &= mask;
+    if (pass) {
+#pragma unroll
+      for (int j = 0; j < 32; j++) {
+        if ((pass >> j) & 1u) {
+          const unsigned long long slot = atomicAdd(count, 1ull);
+          if (slot < cap) pairs[slot] = PairCand{row_a, b0 + j};
+        }
+      }
+    }
+  }
+};
+
+template <bool kSelfJoin, int S>
+struct KernelArgs {
+  int n_a_tiles;   // recall: query tiles; self-join: unused
+  int n_b_tiles;   // 256-row tiles of the store
+  int64_t n_work;  // total (a tile, b tile) work items
+  int k_blocks;
+  // recall
+  const uint32_t* bitmaps;
+  int words_per_group;
+  const int32_t* query_group;
+  int32_t* cand_keys;
+  int64_t keys_per_query;
+  // self-join
+  PairEpilogue pe;
+};
+
+// Work item -> (A tile of 128, B tile of 256).  Recall: a-tile fastest, so the CTAs that
+// run concurrently share B tiles through L2.  Self-join: B tile jb meets A tiles 0..2jb+1
+// (everything at or above the diagonal), jb(jb+1) items come before it.
+template <bool kSelfJoin>
+__device__ __forceinline__ void decode_work(int64_t w, int n_a_tiles, int& a_tile, int& b_tile) {
+  if (!kSelfJoin) {
+    b_tile = (int)(w / n_a_tiles);
+    a_tile = (int)(w % n_a_tiles);
+  } else {
+    int64_t jb = (int64_t)((sqrt(4.0 * (double)w + 1.0) - 1.0) * 0.5);
+    while (jb * (jb + 1) > w) jb--;
+    while ((jb + 1) * (jb + 2) <= w) jb++;
+    b_tile = (int)jb;
+    a_tile = (int)(w - jb * (jb + 1));
+  }
+}
+
+template <bool kSelfJoin, int S>
+__global__ void __launch_bounds__(kNumThreads, 1)
+    score_umma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+                      const KernelArgs<kSelfJoin, S> args) {
+  extern __shared__ uint8_t smem_raw[];
+  // SWIZZLE_128B tiles must start on a 1024-byte boundary.
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem_a = smem;
+  uint8_t* smem_b = smem + kStages * kABytes;
+  PipeBarriers* bars = reinterpret_cast<PipeBarriers*>(smem + kStages * kStageBytes);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  if (warp == 0 && lane == 0) {
+    ptx::tma_prefetch_desc(&tmap_a);
+    ptx::tma_prefetch_desc(&tmap_b);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int i = 0; i < kStages; i++) {
+      ptx::mbar_init(&bars->full[i], 1);
+      ptx::mbar_init(&bars->empty[i], 1);
+    }
+    for (int i = 0; i < 2; i++) {
+      ptx::mbar_init(&bars->tmem_full[i], 1);
+      ptx::mbar_init(&bars->tmem_empty[i], 128);
+    }
+    ptx::fence_barrier_init();
+  }
+  if (warp == 2) ptx::tmem_alloc(&bars->tmem_base, kTmemCols);
+  ptx::tc_fence_before_sync();
+  __syncthreads();
+  ptx::tc_fence_after_sync();
+  const uint32_t tmem_base = bars->tmem_base;
+
+  if (warp == 0) {
+    // ---------------- TMA producer ----------------
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int64_t w = blockIdx.x; w < args.n_work; w += gridDim.x) {
+        int a_tile, b_tile;
+        decode_work<kSelfJoin>(w, args.n_a_tiles, a_tile, b_tile);
+        for (int kb = 0; kb < args.k_blocks; kb++) {
+          ptx::mbar_wait(&bars->empty[stage], phase ^ 1);
+          ptx::mbar_arrive_expect_tx(&bars->full[stage], kStageBytes);
+          ptx::tma_load_2d(smem_a + stage * kABytes, &tmap_a, &bars->full[stage], kb * kBlockK,
+                           a_tile * kQueryTile, ptx::kEvictLast);
+          ptx::tma_load_2d(smem_b + stage * kBBytes, &tmap_b, &bars->full[stage], kb * kBlockK,
+                           b_tile * kTileRows, kSelfJoin ? ptx::kEvictLast : ptx::kEvictNormal);
+          if (++stage == kStages) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ---------------- MMA issuer ----------------
+    constexpr uint32_t idesc = ptx::make_idesc_bf16(kQueryTile, kTileRows);
+    int stage = 0;
+    uint32_t phase = 0;
+    uint32_t it = 0;
+    for (int64_t w = blockIdx.x; w < args.n_work; w += gridDim.x, it++) {
+      const uint32_t as = it & 1, aphase = (it >> 1) & 1;
+      ptx::mbar_wait(&bars->tmem_empty[as], aphase ^ 1);
+      ptx::tc_fence_after_sync();
+      for (int kb = 0; kb < args.k_blocks; kb++) {
+        ptx::mbar_wait(&bars->full[stage], phase);
+        ptx::tc_fence_after_sync();
+        if (lane == 0) {
+          const uint64_t da = ptx::make_smem_desc_sw128(ptx::smem_u32(smem_a + stage * kABytes));
+          const uint64_t db = ptx::make_smem_desc_sw128(ptx::smem_u32(smem_b + stage * kBBytes));
+#pragma unroll
+          for (int k = 0; k < kBlockK / 16; k++)
+            ptx::umma_bf16(tmem_base + as * kTileRows, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
+          ptx::umma_commit(&bars->empty[stage]);  // frees the smem stage when these MMAs retire
+          if (kb == args.k_blocks - 1) ptx::umma_commit(&bars->tmem_full[as]);
+        }
+        __syncwarp();
+        if (++stage == kStages) {
+          stage = 0;
+          phase ^= 1;
+        }
+      }
+    }
+  } else if (warp >= kEpilogueWarp0) {
+    // ---------------- epilogue ----------------
+    const int quarter = warp & 3;  // TMEM lanes [32*quarter, 32*quarter+32) are this warp's
+    const int t_local = quarter * 32 + lane;
+    const uint32_t lane_addr = tmem_base + ((uint32_t)(quarter * 32) << 16);
+    uint32_t it = 0;
+    Top2Epilogue<S> te;
+    PairEpilogue pe = args.pe;
+    for (int64_t w = blockIdx.x; w < args.n_work; w += gridDim.x, it++) {
+      int a_tile, b_tile;
+      decode_work<kSelfJoin>(w, args.n_a_tiles, a_tile, b_tile);
+      const uint32_t as = it & 1, aphase = (it >> 1) & 1;
+      if (!kSelfJoin) {
+        const int q = a_tile * kQueryTile + t_local;
+        const int g = args.query_group ? __ldg(args.query_group + q) : 0;
+        te.bitmap_row = args.bitmaps + (int64_t)g * args.words_per_group;
+        te.out = args.cand_keys + (int64_t)q * args.keys_per_query;
+        te.begin_tile();
+      } else {
+        pe.row_a = a_tile * kQueryTile + t_local;
+        pe.a_member = (__ldg(pe.member + (pe.row_a >> 5)) >> (pe.row_a & 31)) & 1u;
+      }
+      ptx::mbar_wait(&bars->tmem_full[as], aphase);
+      ptx::tc_fence_after_sync();
+#pragma unroll 1
+      for (int c = 0; c < kTileRows / 32; c += 2) {
+        uint32_t v0[32], v1[32];
+        ptx::tmem_ld_32x32(lane_addr + as * kTileRows + c * 32, v0);
+        ptx::tmem_ld_32x32(lane_addr + as * kTileRows + (c + 1) * 32, v1);
+        ptx::tmem_ld_wait();
+        if (!kSelfJoin) {
+          te.chunk(b_tile, c, v0);
+          te.chunk(b_tile, c + 1, v1);
+        } else {
+          pe.chunk(b_tile, c, v0);
+          pe.chunk(b_tile, c + 1, v1);
+        }
+      }
+      ptx::tc_fence_before_sync();
+      ptx::mbar_arrive(&bars->tmem_empty[as]);
+    }
+  }
+
+  ptx::tc_fence_before_sync();
+  __syncthreads();
+  if (warp == 2) ptx::tmem_dealloc(tmem_base, kTmemCols);
+}
+
+template <int S>
+int launch_recall_s(const CUtensorMap& tmap_q, const CUtensorMap& tmap_rows, int n_qtiles, int n_tiles, int k_blocks,
+                    const uint32_t* bitmaps, int words_per_group, const int32_t* query_group, int32_t* cand_keys,
+                    int num_sms, cudaStream_t st) {
+  KernelArgs<false, S> a{};
+  a.n_a_tiles = n_qtiles;
+  a.n_b_tiles = n_tiles;
+  a.n_work = (int64_t)n_qtiles * n_tiles;
+  a.k_blocks = k_blocks;
+  a.bitmaps = bitmaps;
+  a.words_per_group = words_per_group;
+  a.query_group = query_group;
+  a.cand_keys = cand_keys;
+  a.keys_per_query = (int64_t)n_tiles * (kTileRows / S) * 2;
+  auto kern = score_umma_kernel<false, S>;
+  OMR_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+  int grid = num_sms;
+  if ((int64_t)grid > a.n_work) grid = (int)a.n_work;
+  kern<<<grid, kNumThreads, kSmemBytes, st>>>(tmap_q, tmap_rows, a);
+  OMR_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+}  // namespace
+
+int score_umma_smem_bytes() { return kSmemBytes; }
+
+int launch_score_umma(const CUtensorMap& tmap_q, const CUtensorMap& tmap_rows, int n_qtiles, int n_tiles,
+                      int k_blocks, int S, const uint32_t* bitmaps, int words_per_group,
+                      const int32_t* query_group, int32_t* cand_keys, int num_sms, cudaStream_t st) {
+  if (n_qtiles <= 0 || n_tiles <= 0) return 0;
+  switch (S) {
+    case 32: return launch_recall_s<32>(tmap_q, tmap_rows, n_qtiles, n_tiles, k_blocks, bitmaps, words_per_group, query_group, cand_keys, num_sms, st);
+    case 64: return launch_recall_s<64>(tmap_q, tmap_rows, n_qtiles, n_tiles, k_blocks, bitmaps, words_per_group, query_group, cand_keys, num_sms, st);
+    case 128: return launch_recall_s<128>(tmap_q, tmap_rows, n_qtiles, n_tiles, k_blocks, bitmaps, words_per_group, query_group, cand_keys, num_sms, st);
+    case 256: return launch_recall_s<256>(tmap_q, tmap_rows, n_qtiles, n_tiles, k_blocks, bitmaps, words_per_group, query_group, cand_keys, num_sms, st);
+  }
+  return fail_msg(-2, "sub-bucket size must be 32, 64, 128 or 256, got %d", S);
+}
+
+int launch_selfjoin_umma(const CUtensorMap& tmap_a, const CUtensorMap& tmap_b, int64_t n, int k_blocks,
+                         float threshold, const uint32_t* member_bitmap, PairCand* pairs, unsigned long long cap,
+                         unsigned long long* pair_count, int num_sms, cudaStream_t st) {
+  if (n <= 0) return 0;
+  const int64_t nb = (n + kTileRows - 1) / kTileRows;
+  KernelArgs<true, 256> a{};
+  a.n_a_tiles = (int)(2 * nb);
+  a.n_b_tiles = (int)nb;
+  a.n_work = nb * (nb + 1);  // sum over jb of (2jb + 2)
+  a.k_blocks = k_blocks;
+  a.pe.member = member_bitmap;
+  a.pe.pairs = pairs;
+  a.pe.cap = cap;
+  a.pe.count = pair_count;
+  a.pe.threshold = threshold;
+  auto kern = score_umma_kernel<true, 256>;
+  OMR_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+  int grid = num_sms;
+  if ((int64_t)grid > a.n_work) grid = (int)a.n_work;
+  kern<<<grid, kNumThreads, kSmemBytes, st>>>(tmap_a, tmap_b, a);
+  OMR_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+}  // namespace omr

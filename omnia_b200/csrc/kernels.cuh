@@ -1,0 +1,91 @@
+// Launchers for the recall engine's kernels.  Each launcher enqueues on the given
+// stream and returns 0 or a negative omr error code; none of them allocates.
+#pragma once
+#include <cuda.h>
+
+#include "common.cuh"
+
+namespace omr {
+
+// ---- ingest / query preparation (k_ingest.cu) ------------------------------
+int launch_ingest_rows(const float* src, int64_t n, int dim, int pitch, int64_t row0, __nv_bfloat16* rows_bf16,
+                       float* rows_f32, double* norm2, cudaStream_t st);
+int launch_prep_queries(const float* q, int nq, int qpad, int dim, int pitch, __nv_bfloat16* qn, double* qnorm2,
+                        cudaStream_t st);
+constexpr uint32_t kAnyWorkspaceId = 0xFFFFFFFFu;  // DeviceFilter.workspace wildcard
+int launch_build_bitmaps(RowMetaView meta, int64_t n, int words_per_group, const DeviceFilter* filters,
+                         int n_filters, uint32_t* bitmaps, cudaStream_t st);
+
+// ---- approximate scoring -> per-sub-bucket top-2 keys ------------------------
+// cand_keys is [qpad][n_tiles * (256 / S) * 2]; S = sub-bucket rows.
+int launch_score_stream(const ShardView& sh, const __nv_bfloat16* qn, int nq, int n_tiles, int S,
+                        const uint32_t* bitmaps, int words_per_group, const int32_t* query_group,
+                        int32_t* cand_keys, int num_sms, cudaStream_t st);
+int launch_score_umma(const CUtensorMap& tmap_q, const CUtensorMap& tmap_rows, int n_qtiles, int n_tiles,
+                      int k_blocks, int S, const uint32_t* bitmaps, int words_per_group,
+                      const int32_t* query_group, int32_t* cand_keys, int num_sms, cudaStream_t st);
+int score_umma_smem_bytes();
+
+// ---- select / exact rescore / finalize (k_select.cu) -------------------------
+// Candidate slots of a query are sel_rows/sel_dist[q][K2x]: the first K2 hold the keys
+// select_keys picked, the remaining K2x - K2 are "extra" slots that finalize pass 1 fills
+// with every eligible row of a suspect sub-bucket.
+int launch_select_keys(const int32_t* cand_keys, int nq, int64_t keys_per_query, int S, int K2, int K2x,
+                       int32_t* sel_rows, float* sel_bound, cudaStream_t st);
+int launch_rescore(const ShardView& sh, const float* q, const double* qnorm2, int nq, int K2, int K2x,
+                   const int32_t* sel_rows, double* sel_dist, cudaStream_t st);
+int launch_rescore_items(const ShardView& sh, const float* q, const double* qnorm2, int K2x, const int32_t* items,
+                         const int32_t* item_count, const int32_t* sel_rows, double* sel_dist, int num_sms,
+                         cudaStream_t st);
+
+struct FinalizeArgs {
+  int nq = 0, K2 = 0, K2x = 0, k = 0, S = 256;
+  int32_t* sel_rows = nullptr;
+  const double* sel_dist = nullptr;
+  const double* max_dist = nullptr;    // per query; nullptr = no cutoff
+  const float* sel_bound = nullptr;
+  const int32_t* cand_keys = nullptr;  // nullptr = no certificate (exact fallback results)
+  int64_t keys_per_query = 0;
+  float margin = 0.0f;
+  const uint32_t* bitmaps = nullptr;
+  int words_per_group = 0;
+  const int32_t* query_group = nullptr;
+  int64_t row_base = 0;                // returned row = row_base + local_row * row_stride
+  int64_t row_stride = 1;
+  int64_t* out_rows = nullptr;
+  double* out_dist = nullptr;
+  int32_t* out_count = nullptr;
+  int32_t* extra_cnt = nullptr;        // [nq]
+  int32_t* extra_items = nullptr;      // flat slot indices to rescore, [nq * (K2x - K2)]
+  int32_t* extra_total = nullptr;      // device counter
+  int32_t* fail_list = nullptr;        // queries that need the exact fallback
+  int32_t* fail_count = nullptr;
+  const int32_t* qlist = nullptr;      // optional subset of queries
+  int nlist = 0;
+};
+int launch_finalize(const FinalizeArgs& a, cudaStream_t st);
+int launch_finalize_extra(const FinalizeArgs& a, cudaStream_t st);
+
+// Exact fallback: distances of `nslots` queries (indices in slot_query) to every row.
+int launch_exact_scan(const ShardView& sh, const float* q, const double* qnorm2, const int32_t* slot_query,
+                      int nslots, const uint32_t* bitmaps, int words_per_group, const int32_t* query_group,
+                      double* dist_out, cudaStream_t st);
+int launch_select_exact(const double* dist, int64_t n, const int32_t* slot_query, int nslots, int K2, int K2x, int k,
+                        int32_t* sel_rows, double* sel_dist, cudaStream_t st);
+
+// Multi-GPU: merge G gathered per-shard results [G][nq][k] into [nq][k].
+int launch_merge_topk(const int64_t* in_rows, const double* in_dist, int G, int nq, int k, int64_t* out_rows,
+                      double* out_dist, int32_t* out_count, cudaStream_t st);
+
+// ---- near-duplicate self-join (k_score_umma.cu / k_select.cu) ----------------
+struct PairCand {
+  int32_t a, b;
+};
+int launch_selfjoin_umma(const CUtensorMap& tmap_a, const CUtensorMap& tmap_b, int64_t n, int k_blocks,
+                         float threshold, const uint32_t* member_bitmap, PairCand* pairs, unsigned long long cap,
+                         unsigned long long* pair_count, int num_sms, cudaStream_t st);
+int launch_pair_rescore(const ShardView& sh, const PairCand* pairs, unsigned long long n_pairs, double* sim,
+                        cudaStream_t st);
+int launch_gather_rows(const ShardView& sh, const int32_t* idx, int64_t m, __nv_bfloat16* dst, cudaStream_t st);
+
+}  // namespace omr

@@ -1,0 +1,1132 @@
+// Host side of the recall engine: the resident store and the C ABI above it.
+//
+// The reference keeps embeddings in Postgres (`memory_observations.embedding`,
+// internal/memory/postgres/embedding_schema.go:103-111) and answers recall with SQL
+// (internal/memory/store_read.go:243-306, internal/memory/store.go:240-272).  Here the
+// same rows live in HBM: an fp32 master matrix (exact rescoring), a unit-normalised bf16
+// copy (what the scorers stream), fp64 squared norms and the metadata columns the WHERE
+// clause reads, all struct-of-arrays.  The host keeps uuid <-> row maps and mirrors of
+// the metadata so that row-state edits are one small cudaMemcpy.
+#include <algorithm>
+#include <atomic>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <unordered_map>
+#include <vector>
+
+#include "../../include/omnia_recall.h"
+#include "kernels.cuh"
+
+namespace omr {
+
+static thread_local std::string g_err;
+
+int fail_msg(int code, const char* fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof buf, fmt, ap);
+  va_end(ap);
+  g_err = buf;
+  return code;
+}
+
+int fail_cuda(cudaError_t e, const char* what, const char* file, int line) {
+  return fail_msg(OMR_E_CUDA, "memory: gpu: %s failed: %s (%s:%d)", what, cudaGetErrorString(e), file, line);
+}
+
+int launch_iota(int32_t* p, int n, cudaStream_t st);
+int launch_fill_empty(int64_t* rows, double* dist, int32_t* count, int nq, int k, cudaStream_t st);
+int launch_pair_remap(PairCand* pairs, unsigned long long n, const int32_t* remap, cudaStream_t st);
+
+namespace {
+
+struct Key128 {
+  uint64_t a, b;
+  bool operator==(const Key128& o) const { return a == o.a && b == o.b; }
+};
+struct Key128Hash {
+  size_t operator()(const Key128& k) const { return (size_t)(k.a * 0x9E3779B97F4A7C15ull ^ (k.b + 0x7F4A7C15ull)); }
+};
+Key128 key_of(const uint8_t* p) {
+  Key128 k;
+  memcpy(&k.a, p, 8);
+  memcpy(&k.b, p + 8, 8);
+  return k;
+}
+void key_to(const Key128& k, uint8_t* p) {
+  memcpy(p, &k.a, 8);
+  memcpy(p + 8, &k.b, 8);
+}
+Key128 key_from_index(int64_t i) {  // default ids: big-endian row number in the low bytes
+  uint8_t b[16] = {0};
+  for (int j = 0; j < 8; j++) b[15 - j] = (uint8_t)((uint64_t)i >> (8 * j));
+  return key_of(b);
+}
+
+struct Interner {
+  std::unordered_map<std::string, uint32_t> ids;
+  std::vector<std::string> names;
+  uint32_t base;
+  explicit Interner(uint32_t b) : base(b) {}
+  uint32_t intern(const std::string& s) {
+    auto it = ids.find(s);
+    if (it != ids.end()) return it->second;
+    uint32_t id = base + (uint32_t)names.size();
+    names.push_back(s);
+    ids.emplace(s, id);
+    return id;
+  }
+  bool lookup(const char* s, uint32_t* out) const {
+    auto it = ids.find(s);
+    if (it == ids.end()) return false;
+    *out = it->second;
+    return true;
+  }
+};
+
+constexpr uint32_t kNoSuchId = 0xFFFFFFFEu;  // matches no row
+constexpr uint32_t kAnyWorkspace = kAnyWorkspaceId;
+constexpr int kExtraSlots = 1024;
+
+template <typename T>
+struct DevBuf {
+  T* p = nullptr;
+  size_t n = 0;
+  int reserve(size_t want) {
+    if (want <= n) return 0;
+    if (p) cudaFree(p);
+    p = nullptr;
+    n = 0;
+    OMR_CUDA_OK(cudaMalloc(&p, want * sizeof(T)));
+    n = want;
+    return 0;
+  }
+  void release() {
+    if (p) cudaFree(p);
+    p = nullptr;
+    n = 0;
+  }
+};
+
+template <typename T>
+struct PinBuf {
+  T* p = nullptr;
+  size_t n = 0;
+  int reserve(size_t want) {
+    if (want <= n) return 0;
+    if (p) cudaFreeHost(p);
+    p = nullptr;
+    n = 0;
+    OMR_CUDA_OK(cudaHostAlloc(&p, want * sizeof(T), cudaHostAllocDefault));
+    n = want;
+    return 0;
+  }
+  void release() {
+    if (p) cudaFreeHost(p);
+    p = nullptr;
+    n = 0;
+  }
+};
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+int pow2ceil_i(int v) {
+  int p = 1;
+  while (p < v) p <<= 1;
+  return p;
+}
+
+}  // namespace
+}  // namespace omr
+
+using namespace omr;
+
+struct omr_store {
+  omr_config cfg{};
+  int dim = 0, pitch = 0, num_sms = 148;
+  int64_t cap = 0, n = 0;
+  float margin = 1e-3f;
+  std::mutex mu;
+  cudaStream_t stream = nullptr;
+  EncodeTiledFn encode = nullptr;
+
+  // resident matrices and metadata (device)
+  __nv_bfloat16* d_bf16 = nullptr;
+  float* d_f32 = nullptr;
+  double* d_norm2 = nullptr;
+  uint32_t *d_ws = nullptr, *d_user = nullptr, *d_agent = nullptr;
+  uint16_t *d_kind = nullptr, *d_purpose = nullptr;
+  float* d_conf = nullptr;
+  uint8_t* d_flags = nullptr;
+  int64_t* d_valid = nullptr;
+  CUtensorMap tmap_rows_b{}, tmap_rows_a{};
+
+  // host mirrors and identity maps
+  std::vector<uint32_t> h_ws, h_user, h_agent, h_entity;
+  std::vector<uint16_t> h_kind, h_purpose;
+  std::vector<float> h_conf;
+  std::vector<uint8_t> h_flags;
+  std::vector<int64_t> h_valid;
+  std::vector<Key128> obs_id;
+  std::vector<Key128> entity_id;                 // by entity index
+  std::vector<int64_t> entity_latest;            // entity index -> representative row
+  std::vector<std::vector<int64_t>> entity_rows; // entity index -> rows
+  std::unordered_map<Key128, int64_t, Key128Hash> obs_row;
+  std::unordered_map<Key128, uint32_t, Key128Hash> entity_idx;
+  Interner ws_names{1}, user_names{1}, agent_names{1}, kind_names{0}, purpose_names{0};
+
+  // per-search scratch (grown on demand, reused)
+  DevBuf<__nv_bfloat16> w_qn;
+  DevBuf<double> w_qnorm2, w_sel_dist, w_exact, w_maxdist, w_out_dist, w_pair_sim;
+  DevBuf<int32_t> w_cand, w_sel_rows, w_extra_cnt, w_extra_items, w_fail_list, w_counters, w_qgroup, w_out_count, w_idx;
+  DevBuf<float> w_sel_bound, w_queries, w_stage;
+  DevBuf<uint32_t> w_bitmaps, w_live, w_member;
+  DevBuf<int64_t> w_out_rows;
+  DevBuf<DeviceFilter> w_filters;
+  DevBuf<PairCand> w_pairs;
+  DevBuf<unsigned long long> w_pair_count;
+  DevBuf<__nv_bfloat16> w_gather;
+  PinBuf<uint8_t> pin_in, pin_out;
+  PinBuf<int32_t> pin_counters;
+  CUtensorMap tmap_q{};
+  size_t tmap_q_rows = 0;
+  const void* tmap_q_ptr = nullptr;
+  bool live_dirty = true;
+
+  std::atomic<int64_t> st_launches{0}, st_searches{0}, st_queries{0}, st_rescued{0}, st_fallback{0};
+  // optional device timing of the dominant kernel (the approximate scorer), for bench.py's roofline
+  bool profiling = false;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  double scorer_ms_sum = 0.0;
+  int64_t scorer_timed = 0;
+  int last_path = 0, last_S = 0, last_K2 = 0;
+
+  int64_t words() const { return (cap / kTileRows) * 8; }
+  ShardView view() const { return ShardView{d_bf16, d_f32, d_norm2, n, dim, pitch}; }
+  RowMetaView meta() const { return RowMetaView{d_ws, d_user, d_agent, d_kind, d_purpose, d_conf, d_flags, d_valid, d_norm2}; }
+
+  int make_tmap(CUtensorMap* out, const void* ptr, uint64_t rows, uint32_t box_rows) {
+    cuuint64_t dims[2] = {(cuuint64_t)pitch, (cuuint64_t)rows};
+    cuuint64_t strides[1] = {(cuuint64_t)pitch * 2};
+    cuuint32_t box[2] = {(cuuint32_t)kBlockK, box_rows};
+    cuuint32_t es[2] = {1, 1};
+    CUresult r = encode(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, es,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return fail_msg(OMR_E_CUDA, "memory: gpu: cuTensorMapEncodeTiled failed (%d)", (int)r);
+    return 0;
+  }
+
+  int open();
+  void destroy();
+  int append(int64_t count, const float* vecs, int64_t row0);
+  int push_meta(int64_t row0, int64_t count);
+  int push_flag(int64_t row);
+  int to_device_filter(const omr_filter& f, DeviceFilter* out, double* maxd);
+  int ensure_live(cudaStream_t st);
+  int device_search(const float* d_q, int nq, const uint32_t* d_bitmaps, const int32_t* d_qgroup,
+                    const double* d_maxdist, int k, int64_t* d_rows, double* d_dist, int32_t* d_count, cudaStream_t st);
+  int host_search(const float* queries, int nq, const omr_filter* filters, int n_filters, const int32_t* query_filter,
+                  int k, omr_hit* hits, int32_t* counts, int64_t* soa_rows = nullptr, double* soa_dist = nullptr);
+  void fill_hit(omr_hit* h, int64_t grow, double dist) const;
+};
+
+int omr_store::open() {
+  OMR_CUDA_OK(cudaSetDevice(cfg.device));
+  cudaDeviceProp prop;
+  OMR_CUDA_OK(cudaGetDeviceProperties(&prop, cfg.device));
+  if (prop.major != 10)
+    return fail_msg(OMR_E_CUDA, "memory: gpu: device %d is sm_%d%d; this library is built for sm_100a only", cfg.device,
+                    prop.major, prop.minor);
+  num_sms = prop.multiProcessorCount;
+  void* fn = nullptr;
+  cudaDriverEntryPointQueryResult qres;
+  OMR_CUDA_OK(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres));
+  if (!fn || qres != cudaDriverEntryPointSuccess)
+    return fail_msg(OMR_E_CUDA, "memory: gpu: cuTensorMapEncodeTiled not available from the driver");
+  encode = (EncodeTiledFn)fn;
+  OMR_CUDA_OK(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
+  const size_t c = (size_t)cap;
+  OMR_CUDA_OK(cudaMalloc(&d_bf16, c * pitch * sizeof(__nv_bfloat16)));
+  OMR_CUDA_OK(cudaMalloc(&d_f32, c * pitch * sizeof(float)));
+  OMR_CUDA_OK(cudaMalloc(&d_norm2, c * sizeof(double)));
+  OMR_CUDA_OK(cudaMalloc(&d_ws, c * 4));
+  OMR_CUDA_OK(cudaMalloc(&d_user, c * 4));
+  OMR_CUDA_OK(cudaMalloc(&d_agent, c * 4));
+  OMR_CUDA_OK(cudaMalloc(&d_kind, c * 2));
+  OMR_CUDA_OK(cudaMalloc(&d_purpose, c * 2));
+  OMR_CUDA_OK(cudaMalloc(&d_conf, c * 4));
+  OMR_CUDA_OK(cudaMalloc(&d_flags, c));
+  OMR_CUDA_OK(cudaMalloc(&d_valid, c * 8));
+  OMR_CUDA_OK(cudaMemset(d_bf16, 0, c * pitch * sizeof(__nv_bfloat16)));
+  OMR_CUDA_OK(cudaMemset(d_f32, 0, c * pitch * sizeof(float)));
+  OMR_CUDA_OK(cudaMemset(d_norm2, 0, c * sizeof(double)));
+  OMR_CUDA_OK(cudaMemset(d_flags, 0, c));
+  OMR_CUDA_OK(cudaMemset(d_ws, 0, c * 4));
+  int rc = make_tmap(&tmap_rows_b, d_bf16, (uint64_t)cap, kTileRows);
+  if (rc) return rc;
+  rc = make_tmap(&tmap_rows_a, d_bf16, (uint64_t)cap, kQueryTile);
+  if (rc) return rc;
+  OMR_CUDA_OK(cudaEventCreate(&ev0));
+  OMR_CUDA_OK(cudaEventCreate(&ev1));
+  rc = pin_counters.reserve(4);
+  if (rc) return rc;
+  rc = w_counters.reserve(4);
+  return rc;
+}
+
+void omr_store::destroy() {
+  cudaSetDevice(cfg.device);
+  if (stream) cudaStreamSynchronize(stream);
+  void* ptrs[] = {d_bf16, d_f32, d_norm2, d_ws, d_user, d_agent, d_kind, d_purpose, d_conf, d_flags, d_valid};
+  for (void* p : ptrs)
+    if (p) cudaFree(p);
+  w_qn.release(); w_qnorm2.release(); w_sel_dist.release(); w_exact.release(); w_maxdist.release();
+  w_out_dist.release(); w_pair_sim.release(); w_cand.release(); w_sel_rows.release(); w_extra_cnt.release();
+  w_extra_items.release(); w_fail_list.release(); w_counters.release(); w_qgroup.release(); w_out_count.release();
+  w_idx.release(); w_sel_bound.release(); w_queries.release(); w_stage.release(); w_bitmaps.release();
+  w_live.release(); w_member.release(); w_out_rows.release(); w_filters.release(); w_pairs.release();
+  w_pair_count.release(); w_gather.release();
+  pin_in.release(); pin_out.release(); pin_counters.release();
+  if (ev0) cudaEventDestroy(ev0);
+  if (ev1) cudaEventDestroy(ev1);
+  if (stream) cudaStreamDestroy(stream);
+}
+
+// Copies host metadata mirrors [row0, row0+count) to the device.
+int omr_store::push_meta(int64_t row0, int64_t count) {
+  if (count <= 0) return 0;
+  const size_t c = (size_t)count;
+  OMR_CUDA_OK(cudaMemcpyAsync(d_ws + row0, h_ws.data() + row0, c * 4, cudaMemcpyHostToDevice, stream));
+  OMR_CUDA_OK(cudaMemcpyAsync(d_user + row0, h_user.data() + row0, c * 4, cudaMemcpyHostToDevice, stream));
+  OMR_CUDA_OK(cudaMemcpyAsync(d_agent + row0, h_agent.data() + row0, c * 4, cudaMemcpyHostToDevice, stream));
+  OMR_CUDA_OK(cudaMemcpyAsync(d_kind + row0, h_kind.data() + row0, c * 2, cudaMemcpyHostToDevice, stream));
+  OMR_CUDA_OK(cudaMemcpyAsync(d_purpose + row0, h_purpose.data() + row0, c * 2, cudaMemcpyHostToDevice, stream));
+  OMR_CUDA_OK(cudaMemcpyAsync(d_conf + row0, h_conf.data() + row0, c * 4, cudaMemcpyHostToDevice, stream));
+  OMR_CUDA_OK(cudaMemcpyAsync(d_flags + row0, h_flags.data() + row0, c, cudaMemcpyHostToDevice, stream));
+  OMR_CUDA_OK(cudaMemcpyAsync(d_valid + row0, h_valid.data() + row0, c * 8, cudaMemcpyHostToDevice, stream));
+  OMR_CUDA_OK(cudaStreamSynchronize(stream));
+  live_dirty = true;
+  return 0;
+}
+
+int omr_store::push_flag(int64_t row) {
+  OMR_CUDA_OK(cudaMemcpy(d_flags + row, &h_flags[row], 1, cudaMemcpyHostToDevice));
+  live_dirty = true;
+  return 0;
+}
+
+// Streams `count` host vectors through a bounded staging buffer into rows [row0, row0+count).
+int omr_store::append(int64_t count, const float* vecs, int64_t row0) {
+  const int64_t chunk = std::max<int64_t>(1, (int64_t)(64u << 20) / ((int64_t)dim * 4));
+  int rc = w_stage.reserve((size_t)std::min(chunk, count) * dim);
+  if (rc) return rc;
+  for (int64_t off = 0; off < count; off += chunk) {
+    const int64_t c = std::min(chunk, count - off);
+    OMR_CUDA_OK(cudaMemcpyAsync(w_stage.p, vecs + off * dim, (size_t)c * dim * 4, cudaMemcpyHostToDevice, stream));
+    rc = launch_ingest_rows(w_stage.p, c, dim, pitch, row0 + off, d_bf16, d_f32, d_norm2, stream);
+    if (rc) return rc;
+    st_launches++;
+    OMR_CUDA_OK(cudaStreamSynchronize(stream));
+  }
+  return 0;
+}
+
+int omr_store::to_device_filter(const omr_filter& f, DeviceFilter* out, double* maxd) {
+  if (!f.workspace_id || !f.workspace_id[0]) return fail_msg(OMR_E_WORKSPACE, "memory: workspace_id is required");
+  DeviceFilter d{};
+  if (!ws_names.lookup(f.workspace_id, &d.workspace)) d.workspace = kNoSuchId;
+  auto scope = [&](const char* v, int mode, const Interner& in, uint32_t* id, int32_t* m) -> int {
+    if (mode < OMR_MATCH_ANY || mode > OMR_MATCH_NULL_OR_EQ) return fail_msg(OMR_E_INVALID, "memory: bad scope match mode %d", mode);
+    *m = mode;
+    *id = 0;
+    if (mode == OMR_MATCH_EQ || mode == OMR_MATCH_NULL_OR_EQ) {
+      if (!v) {  // value absent: EQ degrades to "no constraint", NULL_OR_EQ to "IS NULL", as the SQL does
+        *m = mode == OMR_MATCH_EQ ? OMR_MATCH_ANY : OMR_MATCH_NULL_ONLY;
+      } else if (!in.lookup(v, id)) {
+        *id = kNoSuchId;
+      }
+    }
+    return 0;
+  };
+  int rc = scope(f.virtual_user_id, f.user_mode, user_names, &d.user, &d.user_mode);
+  if (rc) return rc;
+  rc = scope(f.agent_id, f.agent_mode, agent_names, &d.agent, &d.agent_mode);
+  if (rc) return rc;
+  if (f.n_kinds > kMaxFilterSet || f.n_purposes > kMaxFilterSet)
+    return fail_msg(OMR_E_INVALID, "memory: at most %d kinds / purposes per filter", kMaxFilterSet);
+  d.n_kinds = f.n_kinds;
+  for (int i = 0; i < f.n_kinds; i++) {
+    uint32_t id;
+    d.kinds[i] = kind_names.lookup(f.kinds[i], &id) ? (uint16_t)id : (uint16_t)0xFFFF;
+  }
+  d.n_purposes = f.n_purposes;
+  for (int i = 0; i < f.n_purposes; i++) {
+    uint32_t id;
+    d.purposes[i] = purpose_names.lookup(f.purposes[i], &id) ? (uint16_t)id : (uint16_t)0xFFFF;
+  }
+  d.min_confidence = f.min_confidence;
+  d.now_us = f.now_us;
+  *out = d;
+  *maxd = (f.max_distance == f.max_distance && f.max_distance < 2.0) ? f.max_distance : INFINITY;
+  return 0;
+}
+
+// Bitmap of every live row (any workspace, no expiry test): the default when the caller of
+// omr_device_search passes no bitmaps.
+int omr_store::ensure_live(cudaStream_t st) {
+  int rc = w_live.reserve((size_t)words());
+  if (rc) return rc;
+  if (!live_dirty) return 0;
+  rc = w_filters.reserve(64);
+  if (rc) return rc;
+  DeviceFilter d{};
+  d.workspace = kAnyWorkspace;
+  d.min_confidence = -INFINITY;
+  d.now_us = INT64_MIN;
+  OMR_CUDA_OK(cudaMemcpyAsync(w_filters.p + 63, &d, sizeof d, cudaMemcpyHostToDevice, st));
+  OMR_CUDA_OK(cudaStreamSynchronize(st));  // `d` is a stack object
+  rc = launch_build_bitmaps(meta(), n, (int)words(), w_filters.p + 63, 1, w_live.p, st);
+  if (rc) return rc;
+  st_launches++;
+  live_dirty = false;
+  return 0;
+}
+
+int omr_store::device_search(const float* d_q, int nq, const uint32_t* d_bitmaps, const int32_t* d_qgroup,
+                             const double* d_maxdist, int k, int64_t* d_rows, double* d_dist, int32_t* d_count,
+                             cudaStream_t st) {
+  if (nq <= 0) return 0;
+  if (k <= 0 || k > 4096) return fail_msg(OMR_E_INVALID, "memory: k must be in 1..4096, got %d", k);
+  st_searches++;
+  st_queries += nq;
+  int rc;
+  if (n == 0) {
+    rc = launch_fill_empty(d_rows, d_dist, d_count, nq, k, st);
+    st_launches++;
+    return rc;
+  }
+  if (!d_bitmaps) {
+    rc = ensure_live(st);
+    if (rc) return rc;
+    d_bitmaps = w_live.p;
+    d_qgroup = nullptr;
+  }
+  const int n_tiles = (int)((n + kTileRows - 1) / kTileRows);
+  const int wpg = (int)words();
+  int K2 = cfg.rescore_width > 0 ? cfg.rescore_width : pow2ceil_i(std::max(32, 2 * k));
+  K2 = std::min(std::max(K2, k), 4096);
+  const int K2x = K2 + kExtraSlots;
+  int S = cfg.sub_bucket > 0 ? cfg.sub_bucket : (k <= 32 ? 256 : (k <= 128 ? 64 : 32));
+  int path = cfg.force_path > 0 ? cfg.force_path : (nq <= 8 ? 1 : 2);
+  const int qpad = path == 2 ? ((nq + kQueryTile - 1) / kQueryTile) * kQueryTile : std::max(nq, 8);
+  const int64_t kpq = (int64_t)n_tiles * (kTileRows / S) * 2;
+  last_path = path; last_S = S; last_K2 = K2;
+
+  if ((rc = w_qn.reserve((size_t)qpad * pitch))) return rc;
+  if ((rc = w_qnorm2.reserve((size_t)qpad))) return rc;
+  if ((rc = w_sel_rows.reserve((size_t)qpad * K2x))) return rc;
+  if ((rc = w_sel_dist.reserve((size_t)qpad * K2x))) return rc;
+  if ((rc = w_sel_bound.reserve((size_t)qpad))) return rc;
+  if ((rc = w_extra_cnt.reserve((size_t)qpad))) return rc;
+  if ((rc = w_extra_items.reserve((size_t)qpad * kExtraSlots))) return rc;
+  if ((rc = w_fail_list.reserve((size_t)qpad))) return rc;
+  if (path != 3 && (rc = w_cand.reserve((size_t)qpad * kpq))) return rc;
+
+  OMR_CUDA_OK(cudaMemsetAsync(w_counters.p, 0, 4 * sizeof(int32_t), st));
+  OMR_CUDA_OK(cudaMemsetAsync(w_extra_cnt.p, 0, (size_t)qpad * sizeof(int32_t), st));
+  int32_t* extra_total = w_counters.p;
+  int32_t* fail_count = w_counters.p + 1;
+  const ShardView sh = view();
+
+  rc = launch_prep_queries(d_q, nq, qpad, dim, pitch, w_qn.p, w_qnorm2.p, st);
+  if (rc) return rc;
+  st_launches++;
+
+  FinalizeArgs fa;
+  fa.nq = nq; fa.K2 = K2; fa.K2x = K2x; fa.k = k; fa.S = S;
+  fa.sel_rows = w_sel_rows.p; fa.sel_dist = w_sel_dist.p; fa.max_dist = d_maxdist; fa.sel_bound = w_sel_bound.p;
+  fa.cand_keys = w_cand.p; fa.keys_per_query = kpq; fa.margin = margin;
+  fa.bitmaps = d_bitmaps; fa.words_per_group = wpg; fa.query_group = d_qgroup;
+  fa.row_base = cfg.row_base; fa.row_stride = cfg.row_stride;
+  fa.out_rows = d_rows; fa.out_dist = d_dist; fa.out_count = d_count;
+  fa.extra_cnt = w_extra_cnt.p; fa.extra_items = w_extra_items.p; fa.extra_total = extra_total;
+  fa.fail_list = w_fail_list.p; fa.fail_count = fail_count;
+
+  int nfail = 0;
+  if (path == 3) {
+    rc = launch_iota(w_fail_list.p, nq, st);
+    if (rc) return rc;
+    st_launches++;
+    nfail = nq;
+  } else {
+    if (profiling) OMR_CUDA_OK(cudaEventRecord(ev0, st));
+    if (path == 1) {
+      // the streaming scorer takes 8 queries per pass over the matrix
+      for (int q0 = 0; q0 < nq; q0 += 8) {
+        const int c = std::min(8, nq - q0);
+        rc = launch_score_stream(sh, w_qn.p + (size_t)q0 * pitch, c, n_tiles, S, d_bitmaps, wpg,
+                                 d_qgroup ? d_qgroup + q0 : nullptr, w_cand.p + (size_t)q0 * kpq, num_sms, st);
+        if (rc) return rc;
+        st_launches++;
+      }
+    } else {
+      if (tmap_q_ptr != w_qn.p || tmap_q_rows != w_qn.n / pitch) {
+        rc = make_tmap(&tmap_q, w_qn.p, w_qn.n / pitch, kQueryTile);
+        if (rc) return rc;
+        tmap_q_ptr = w_qn.p;
+        tmap_q_rows = w_qn.n / pitch;
+      }
+      rc = launch_score_umma(tmap_q, tmap_rows_b, qpad / kQueryTile, n_tiles, pitch / kBlockK, S, d_bitmaps, wpg,
+                             d_qgroup, w_cand.p, num_sms, st);
+      if (rc) return rc;
+      st_launches++;
+    }
+    if (profiling) OMR_CUDA_OK(cudaEventRecord(ev1, st));
+    if ((rc = launch_select_keys(w_cand.p, nq, kpq, S, K2, K2x, w_sel_rows.p, w_sel_bound.p, st))) return rc;
+    if ((rc = launch_rescore(sh, d_q, w_qnorm2.p, nq, K2, K2x, w_sel_rows.p, w_sel_dist.p, st))) return rc;
+    if ((rc = launch_finalize(fa, st))) return rc;
+    if ((rc = launch_rescore_items(sh, d_q, w_qnorm2.p, K2x, w_extra_items.p, extra_total, w_sel_rows.p, w_sel_dist.p,
+                                   num_sms, st)))
+      return rc;
+    if ((rc = launch_finalize_extra(fa, st))) return rc;
+    st_launches += 5;
+    OMR_CUDA_OK(cudaMemcpyAsync(pin_counters.p, w_counters.p, 2 * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+    OMR_CUDA_OK(cudaStreamSynchronize(st));
+    st_rescued += pin_counters.p[0];
+    nfail = pin_counters.p[1];
+    if (profiling) {
+      float ms = 0.0f;
+      OMR_CUDA_OK(cudaEventElapsedTime(&ms, ev0, ev1));
+      scorer_ms_sum += ms;
+      scorer_timed++;
+    }
+  }
+  if (nfail > 0) {
+    // Exact fallback: score every eligible row of the failing queries in fp64.
+    st_fallback += nfail;
+    const int64_t n_pad = (int64_t)wpg * 32;
+    const int slots = (int)std::max<int64_t>(1, std::min<int64_t>(nfail, (int64_t)(256u << 20) / (n_pad * 8)));
+    if ((rc = w_exact.reserve((size_t)slots * n_pad))) return rc;
+    FinalizeArgs fx = fa;
+    fx.cand_keys = nullptr;
+    for (int s0 = 0; s0 < nfail; s0 += slots) {
+      const int c = std::min(slots, nfail - s0);
+      const int32_t* list = w_fail_list.p + s0;
+      if ((rc = launch_exact_scan(sh, d_q, w_qnorm2.p, list, c, d_bitmaps, wpg, d_qgroup, w_exact.p, st))) return rc;
+      if ((rc = launch_select_exact(w_exact.p, n_pad, list, c, K2, K2x, k, w_sel_rows.p, w_sel_dist.p, st))) return rc;
+      fx.qlist = list;
+      fx.nlist = c;
+      if ((rc = launch_finalize(fx, st))) return rc;
+      st_launches += 3;
+    }
+    OMR_CUDA_OK(cudaStreamSynchronize(st));
+  }
+  return 0;
+}
+
+void omr_store::fill_hit(omr_hit* h, int64_t grow, double dist) const {
+  const int64_t stride = cfg.row_stride > 0 ? cfg.row_stride : 1;
+  const int64_t local = (grow - cfg.row_base) / stride;
+  key_to(obs_id[local], h->observation_id);
+  key_to(entity_id[h_entity[local]], h->entity_id);
+  h->distance = dist;
+  h->row = grow;
+}
+
+int omr_store::host_search(const float* queries, int nq, const omr_filter* filters, int n_filters,
+                           const int32_t* query_filter, int k, omr_hit* hits, int32_t* counts, int64_t* soa_rows,
+                           double* soa_dist) {
+  if (nq <= 0) return 0;
+  if (n_filters <= 0 || !filters) return fail_msg(OMR_E_WORKSPACE, "memory: workspace_id is required");
+  int rc;
+  std::vector<DeviceFilter> df((size_t)n_filters);
+  std::vector<double> fmax((size_t)n_filters);
+  for (int i = 0; i < n_filters; i++)
+    if ((rc = to_device_filter(filters[i], &df[i], &fmax[i]))) return rc;
+  // staging layout in pinned memory: queries | query_group | max_dist
+  const size_t qbytes = (size_t)nq * dim * 4;
+  const size_t in_bytes = qbytes + (size_t)nq * 4 + (size_t)nq * 8 + 16;
+  if ((rc = pin_in.reserve(in_bytes))) return rc;
+  float* pq = reinterpret_cast<float*>(pin_in.p);
+  double* pm = reinterpret_cast<double*>(pin_in.p + ((qbytes + 7) & ~size_t(7)));
+  int32_t* pg = reinterpret_cast<int32_t*>(reinterpret_cast<uint8_t*>(pm) + (size_t)nq * 8);
+  memcpy(pq, queries, qbytes);
+  for (int i = 0; i < nq; i++) {
+    const int g = query_filter ? query_filter[i] : 0;
+    if (g < 0 || g >= n_filters) return fail_msg(OMR_E_INVALID, "memory: query %d names filter %d of %d", i, g, n_filters);
+    pg[i] = g;
+    pm[i] = fmax[g];
+  }
+  if ((rc = w_queries.reserve((size_t)nq * dim))) return rc;
+  if ((rc = w_qgroup.reserve((size_t)nq))) return rc;
+  if ((rc = w_maxdist.reserve((size_t)nq))) return rc;
+  if ((rc = w_filters.reserve((size_t)std::max(64, n_filters + 1)))) return rc;
+  if ((rc = w_bitmaps.reserve((size_t)n_filters * words()))) return rc;
+  if ((rc = w_out_rows.reserve((size_t)nq * k))) return rc;
+  if ((rc = w_out_dist.reserve((size_t)nq * k))) return rc;
+  if ((rc = w_out_count.reserve((size_t)nq))) return rc;
+  OMR_CUDA_OK(cudaMemcpyAsync(w_queries.p, pq, qbytes, cudaMemcpyHostToDevice, stream));
+  OMR_CUDA_OK(cudaMemcpyAsync(w_qgroup.p, pg, (size_t)nq * 4, cudaMemcpyHostToDevice, stream));
+  OMR_CUDA_OK(cudaMemcpyAsync(w_maxdist.p, pm, (size_t)nq * 8, cudaMemcpyHostToDevice, stream));
+  OMR_CUDA_OK(cudaMemcpyAsync(w_filters.p, df.data(), (size_t)n_filters * sizeof(DeviceFilter), cudaMemcpyHostToDevice, stream));
+  OMR_CUDA_OK(cudaStreamSynchronize(stream));  // df is pageable
+  if ((rc = launch_build_bitmaps(meta(), n, (int)words(), w_filters.p, n_filters, w_bitmaps.p, stream))) return rc;
+  st_launches++;
+  if ((rc = device_search(w_queries.p, nq, w_bitmaps.p, w_qgroup.p, w_maxdist.p, k, w_out_rows.p, w_out_dist.p,
+                          w_out_count.p, stream)))
+    return rc;
+  const size_t ob = (size_t)nq * k * 16 + (size_t)nq * 4;
+  if ((rc = pin_out.reserve(ob))) return rc;
+  int64_t* orow = reinterpret_cast<int64_t*>(pin_out.p);
+  double* odist = reinterpret_cast<double*>(pin_out.p + (size_t)nq * k * 8);
+  int32_t* ocnt = reinterpret_cast<int32_t*>(pin_out.p + (size_t)nq * k * 16);
+  OMR_CUDA_OK(cudaMemcpyAsync(orow, w_out_rows.p, (size_t)nq * k * 8, cudaMemcpyDeviceToHost, stream));
+  OMR_CUDA_OK(cudaMemcpyAsync(odist, w_out_dist.p, (size_t)nq * k * 8, cudaMemcpyDeviceToHost, stream));
+  OMR_CUDA_OK(cudaMemcpyAsync(ocnt, w_out_count.p, (size_t)nq * 4, cudaMemcpyDeviceToHost, stream));
+  OMR_CUDA_OK(cudaStreamSynchronize(stream));
+  if (soa_rows) {
+    memcpy(soa_rows, orow, (size_t)nq * k * 8);
+    memcpy(soa_dist, odist, (size_t)nq * k * 8);
+    memcpy(counts, ocnt, (size_t)nq * 4);
+    return 0;
+  }
+  for (int i = 0; i < nq; i++) {
+    counts[i] = ocnt[i];
+    for (int j = 0; j < ocnt[i]; j++) fill_hit(&hits[(size_t)i * k + j], orow[(size_t)i * k + j], odist[(size_t)i * k + j]);
+  }
+  return 0;
+}
+
+// ================================ C ABI =========================================
+
+extern "C" {
+
+const char* omr_last_error(void) { return g_err.c_str(); }
+
+int omr_open(const omr_config* cfg, omr_store** out) {
+  if (!cfg || !out) return fail_msg(OMR_E_INVALID, "memory: omr_open: null argument");
+  *out = nullptr;
+  if (cfg->dim < 1 || cfg->dim > OMR_MAX_DIM)
+    return fail_msg(OMR_E_DIM, "memory: embedding dimension %d outside 1..%d", cfg->dim, OMR_MAX_DIM);
+  if (cfg->capacity < 1) return fail_msg(OMR_E_INVALID, "memory: capacity must be positive");
+  if (cfg->sub_bucket != 0 && cfg->sub_bucket != 32 && cfg->sub_bucket != 64 && cfg->sub_bucket != 128 &&
+      cfg->sub_bucket != 256)
+    return fail_msg(OMR_E_INVALID, "memory: sub_bucket must be 0, 32, 64, 128 or 256");
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0)
+    return fail_msg(OMR_E_CUDA, "memory: gpu: no CUDA device (%s); this engine has no CPU fallback",
+                    e == cudaSuccess ? "device count is 0" : cudaGetErrorString(e));
+  if (cfg->device < 0 || cfg->device >= ndev) return fail_msg(OMR_E_INVALID, "memory: gpu: device %d of %d", cfg->device, ndev);
+  omr_store* s = new omr_store();
+  s->cfg = *cfg;
+  if (s->cfg.row_stride <= 0) s->cfg.row_stride = 1;
+  s->dim = cfg->dim;
+  s->pitch = ((cfg->dim + kBlockK - 1) / kBlockK) * kBlockK;
+  s->cap = ((cfg->capacity + kTileRows - 1) / kTileRows) * kTileRows;
+  if (s->cap > (int64_t)INT32_MAX - kTileRows) {
+    delete s;
+    return fail_msg(OMR_E_CAPACITY, "memory: a shard holds at most 2^31 rows");
+  }
+  s->margin = cfg->candidate_margin > 0 ? cfg->candidate_margin : 1e-3f;
+  int rc = s->open();
+  if (rc) {
+    s->destroy();
+    delete s;
+    return rc;
+  }
+  *out = s;
+  return OMR_OK;
+}
+
+void omr_close(omr_store* s) {
+  if (!s) return;
+  s->destroy();
+  delete s;
+}
+
+int64_t omr_count(const omr_store* s) { return s ? s->n : 0; }
+int64_t omr_bitmap_words(const omr_store* s) { return s ? s->words() : 0; }
+
+static void grow_host(omr_store* s, int64_t total) {
+  const size_t t = (size_t)total;
+  s->h_ws.resize(t); s->h_user.resize(t); s->h_agent.resize(t); s->h_entity.resize(t);
+  s->h_kind.resize(t); s->h_purpose.resize(t); s->h_conf.resize(t); s->h_flags.resize(t);
+  s->h_valid.resize(t); s->obs_id.resize(t);
+}
+
+static uint32_t entity_of(omr_store* s, const Key128& e) {
+  auto it = s->entity_idx.find(e);
+  if (it != s->entity_idx.end()) return it->second;
+  const uint32_t idx = (uint32_t)s->entity_id.size();
+  s->entity_id.push_back(e);
+  s->entity_latest.push_back(-1);
+  s->entity_rows.emplace_back();
+  s->entity_idx.emplace(e, idx);
+  return idx;
+}
+
+// A new embedded row becomes its entity's representative (the row UpdateEmbedding targets).
+static void attach_row(omr_store* s, int64_t row, uint32_t ent) {
+  s->h_entity[row] = ent;
+  s->entity_rows[ent].push_back(row);
+  const int64_t prev = s->entity_latest[ent];
+  if (prev >= 0 && prev != row) s->h_flags[prev] &= (uint8_t)~kRowEntityRep;
+  s->entity_latest[ent] = row;
+  s->h_flags[row] |= kRowEntityRep;
+}
+
+int omr_bulk_load(omr_store* s, const omr_bulk* b) {
+  if (!s || !b) return fail_msg(OMR_E_INVALID, "memory: omr_bulk_load: null argument");
+  if (b->n <= 0) return OMR_OK;
+  if (!b->vectors) return fail_msg(OMR_E_INVALID, "memory: omr_bulk_load: vectors is null");
+  std::lock_guard<std::mutex> lk(s->mu);
+  cudaSetDevice(s->cfg.device);
+  if (s->n + b->n > s->cfg.capacity) return fail_msg(OMR_E_CAPACITY, "memory: gpu store is full (%lld + %lld > %lld rows)",
+                                                     (long long)s->n, (long long)b->n, (long long)s->cfg.capacity);
+  auto table = [](Interner& in, const char* const* names, int cnt, const char* what, std::vector<uint32_t>* map) {
+    map->resize((size_t)std::max(cnt, 0));
+    for (int i = 0; i < cnt; i++) (*map)[i] = in.intern(names[i] ? names[i] : "");
+    (void)what;
+  };
+  std::vector<uint32_t> mws, muser, magent, mkind, mpurpose;
+  table(s->ws_names, b->workspaces, b->n_workspaces, "workspace", &mws);
+  table(s->user_names, b->users, b->n_users, "user", &muser);
+  table(s->agent_names, b->agents, b->n_agents, "agent", &magent);
+  table(s->kind_names, b->kinds, b->n_kinds, "kind", &mkind);
+  table(s->purpose_names, b->purposes, b->n_purposes, "purpose", &mpurpose);
+  const uint32_t default_ws = mws.empty() ? s->ws_names.intern("default") : mws[0];
+  const uint32_t default_kind = mkind.empty() ? s->kind_names.intern("") : mkind[0];
+  const uint32_t default_purpose = mpurpose.empty() ? s->purpose_names.intern("") : mpurpose[0];
+  const int64_t row0 = s->n;
+  grow_host(s, row0 + b->n);
+  for (int64_t i = 0; i < b->n; i++) {
+    const int64_t r = row0 + i;
+    auto pick = [&](const std::vector<uint32_t>& m, int64_t idx, uint32_t dflt, const char* what) -> int64_t {
+      if (idx < 0 || idx >= (int64_t)m.size()) {
+        fail_msg(OMR_E_INVALID, "memory: omr_bulk_load: row %lld %s index %lld outside table of %zu", (long long)i, what,
+                 (long long)idx, m.size());
+        return -1;
+      }
+      (void)dflt;
+      return m[(size_t)idx];
+    };
+    int64_t v;
+    if (b->workspace_idx) { if ((v = pick(mws, b->workspace_idx[i], 0, "workspace")) < 0) { grow_host(s, row0); return OMR_E_INVALID; } s->h_ws[r] = (uint32_t)v; }
+    else s->h_ws[r] = default_ws;
+    if (b->user_idx && b->user_idx[i] >= 0) { if ((v = pick(muser, b->user_idx[i], 0, "user")) < 0) { grow_host(s, row0); return OMR_E_INVALID; } s->h_user[r] = (uint32_t)v; }
+    else s->h_user[r] = 0;
+    if (b->agent_idx && b->agent_idx[i] >= 0) { if ((v = pick(magent, b->agent_idx[i], 0, "agent")) < 0) { grow_host(s, row0); return OMR_E_INVALID; } s->h_agent[r] = (uint32_t)v; }
+    else s->h_agent[r] = 0;
+    if (b->kind_idx) { if ((v = pick(mkind, b->kind_idx[i], 0, "kind")) < 0) { grow_host(s, row0); return OMR_E_INVALID; } s->h_kind[r] = (uint16_t)v; }
+    else s->h_kind[r] = (uint16_t)default_kind;
+    if (b->purpose_idx) { if ((v = pick(mpurpose, b->purpose_idx[i], 0, "purpose")) < 0) { grow_host(s, row0); return OMR_E_INVALID; } s->h_purpose[r] = (uint16_t)v; }
+    else s->h_purpose[r] = (uint16_t)default_purpose;
+    s->h_conf[r] = b->confidence ? b->confidence[i] : 1.0f;
+    s->h_flags[r] = b->flags ? (uint8_t)(b->flags[i] & 0x0F) : (uint8_t)(OMR_ROW_HAS_EMBEDDING | OMR_ROW_MUTABLE);
+    s->h_valid[r] = b->valid_until_us ? b->valid_until_us[i] : OMR_NO_EXPIRY;
+    s->obs_id[r] = b->observation_ids ? key_of(b->observation_ids + 16 * i) : key_from_index(r);
+  }
+  // identity maps (after validation, so a rejected batch leaves no trace)
+  for (int64_t i = 0; i < b->n; i++) {
+    const int64_t r = row0 + i;
+    s->obs_row[s->obs_id[r]] = r;
+    const Key128 e = b->entity_ids ? key_of(b->entity_ids + 16 * i) : s->obs_id[r];
+    attach_row(s, r, entity_of(s, e));
+  }
+  s->n = row0 + b->n;
+  int rc = s->push_meta(0, s->n);  // earlier rows may have lost their EntityRep bit
+  if (rc) return rc;
+  rc = s->append(b->n, b->vectors, row0);
+  if (rc) return rc;
+  s->live_dirty = true;
+  return OMR_OK;
+}
+
+int omr_upsert(omr_store* s, const omr_row* row, const float* vec, int32_t dim) {
+  if (!s || !row || !vec) return fail_msg(OMR_E_INVALID, "memory: omr_upsert: null argument");
+  if (dim != s->dim) return fail_msg(OMR_E_DIM, "memory: embedding dimension mismatch: got %d, store has %d", dim, s->dim);
+  if (!row->workspace_id || !row->workspace_id[0]) return fail_msg(OMR_E_WORKSPACE, "memory: workspace_id is required");
+  std::lock_guard<std::mutex> lk(s->mu);
+  cudaSetDevice(s->cfg.device);
+  const Key128 ok = key_of(row->observation_id);
+  int64_t r;
+  auto it = s->obs_row.find(ok);
+  const bool fresh = it == s->obs_row.end();
+  if (fresh) {
+    if (s->n + 1 > s->cfg.capacity) return fail_msg(OMR_E_CAPACITY, "memory: gpu store is full (%lld rows)", (long long)s->n);
+    r = s->n;
+    grow_host(s, r + 1);
+    s->obs_id[r] = ok;
+    s->h_flags[r] = 0;
+  } else {
+    r = it->second;
+  }
+  s->h_ws[r] = s->ws_names.intern(row->workspace_id);
+  s->h_user[r] = row->virtual_user_id ? s->user_names.intern(row->virtual_user_id) : 0;
+  s->h_agent[r] = row->agent_id ? s->agent_names.intern(row->agent_id) : 0;
+  s->h_kind[r] = (uint16_t)s->kind_names.intern(row->kind ? row->kind : "");
+  s->h_purpose[r] = (uint16_t)s->purpose_names.intern(row->purpose ? row->purpose : "");
+  s->h_conf[r] = row->confidence;
+  s->h_flags[r] = (uint8_t)((s->h_flags[r] & kRowEntityRep) | (row->flags & 0x0F) | OMR_ROW_HAS_EMBEDDING);
+  s->h_valid[r] = row->valid_until_us;
+  int64_t lo = r, hi = r;
+  if (fresh) {
+    s->obs_row[ok] = r;
+    const uint32_t ent = entity_of(s, key_of(row->entity_id));
+    const int64_t prev = s->entity_latest[ent];
+    attach_row(s, r, ent);
+    s->n = r + 1;
+    if (prev >= 0) lo = std::min(lo, prev);
+  }
+  int rc = s->push_meta(lo, hi - lo + 1);
+  if (rc) return rc;
+  return s->append(1, vec, r);
+}
+
+int omr_update_embedding(omr_store* s, const uint8_t entity_id[16], const float* vec, int32_t dim) {
+  if (!s || !entity_id || !vec) return fail_msg(OMR_E_INVALID, "memory: omr_update_embedding: null argument");
+  if (dim != s->dim) return fail_msg(OMR_E_DIM, "memory: embedding dimension mismatch: got %d, store has %d", dim, s->dim);
+  std::lock_guard<std::mutex> lk(s->mu);
+  cudaSetDevice(s->cfg.device);
+  auto it = s->entity_idx.find(key_of(entity_id));
+  if (it == s->entity_idx.end() || s->entity_latest[it->second] < 0) return fail_msg(OMR_E_NOT_FOUND, "memory: not found");
+  const int64_t r = s->entity_latest[it->second];
+  s->h_flags[r] |= OMR_ROW_HAS_EMBEDDING;
+  int rc = s->push_meta(r, 1);
+  if (rc) return rc;
+  return s->append(1, vec, r);
+}
+
+static int edit_rows(omr_store* s, const std::vector<int64_t>& rows, uint32_t set_mask, uint32_t clear_mask) {
+  for (int64_t r : rows) {
+    s->h_flags[r] = (uint8_t)((s->h_flags[r] | (set_mask & 0x4F)) & ~(clear_mask & 0x4F));
+    int rc = s->push_flag(r);
+    if (rc) return rc;
+  }
+  return OMR_OK;
+}
+
+int omr_set_row_flags(omr_store* s, const uint8_t observation_id[16], uint32_t set_mask, uint32_t clear_mask) {
+  if (!s || !observation_id) return fail_msg(OMR_E_INVALID, "memory: null argument");
+  std::lock_guard<std::mutex> lk(s->mu);
+  cudaSetDevice(s->cfg.device);
+  auto it = s->obs_row.find(key_of(observation_id));
+  if (it == s->obs_row.end()) return fail_msg(OMR_E_NOT_FOUND, "memory: not found");
+  return edit_rows(s, {it->second}, set_mask, clear_mask);
+}
+
+int omr_set_entity_flags(omr_store* s, const uint8_t entity_id[16], uint32_t set_mask, uint32_t clear_mask) {
+  if (!s || !entity_id) return fail_msg(OMR_E_INVALID, "memory: null argument");
+  std::lock_guard<std::mutex> lk(s->mu);
+  cudaSetDevice(s->cfg.device);
+  auto it = s->entity_idx.find(key_of(entity_id));
+  if (it == s->entity_idx.end()) return fail_msg(OMR_E_NOT_FOUND, "memory: not found");
+  return edit_rows(s, s->entity_rows[it->second], set_mask, clear_mask);
+}
+
+int omr_delete_entity(omr_store* s, const uint8_t entity_id[16]) {
+  return omr_set_entity_flags(s, entity_id, kRowDeleted, OMR_ROW_HAS_EMBEDDING);
+}
+
+int omr_set_valid_until(omr_store* s, const uint8_t observation_id[16], int64_t valid_until_us) {
+  if (!s || !observation_id) return fail_msg(OMR_E_INVALID, "memory: null argument");
+  std::lock_guard<std::mutex> lk(s->mu);
+  cudaSetDevice(s->cfg.device);
+  auto it = s->obs_row.find(key_of(observation_id));
+  if (it == s->obs_row.end()) return fail_msg(OMR_E_NOT_FOUND, "memory: not found");
+  s->h_valid[it->second] = valid_until_us;
+  OMR_CUDA_OK(cudaMemcpy(s->d_valid + it->second, &valid_until_us, 8, cudaMemcpyHostToDevice));
+  return OMR_OK;
+}
+
+int omr_set_confidence(omr_store* s, const uint8_t observation_id[16], float confidence) {
+  if (!s || !observation_id) return fail_msg(OMR_E_INVALID, "memory: null argument");
+  std::lock_guard<std::mutex> lk(s->mu);
+  cudaSetDevice(s->cfg.device);
+  auto it = s->obs_row.find(key_of(observation_id));
+  if (it == s->obs_row.end()) return fail_msg(OMR_E_NOT_FOUND, "memory: not found");
+  s->h_conf[it->second] = confidence;
+  OMR_CUDA_OK(cudaMemcpy(s->d_conf + it->second, &confidence, 4, cudaMemcpyHostToDevice));
+  return OMR_OK;
+}
+
+int omr_search(omr_store* s, const float* queries, int32_t nq, int32_t dim, const omr_filter* filters,
+               int32_t n_filters, const int32_t* query_filter, int32_t k, omr_hit* hits, int32_t* counts) {
+  if (!s || !queries || !hits || !counts) return fail_msg(OMR_E_INVALID, "memory: omr_search: null argument");
+  if (dim != s->dim)
+    return fail_msg(OMR_E_DIM, "memory: similar observations: different vector dimensions %d and %d", s->dim, dim);
+  if (k <= 0) k = 5;  // DefaultDuplicateCandidateLimit, internal/memory/types.go:137-141
+  std::lock_guard<std::mutex> lk(s->mu);
+  cudaSetDevice(s->cfg.device);
+  return s->host_search(queries, nq, filters, n_filters, query_filter, k, hits, counts);
+}
+
+int omr_search_rows(omr_store* s, const float* queries, int32_t nq, int32_t dim, const omr_filter* filters,
+                    int32_t n_filters, const int32_t* query_filter, int32_t k, int64_t* rows, double* distances,
+                    int32_t* counts) {
+  if (!s || !queries || !rows || !distances || !counts) return fail_msg(OMR_E_INVALID, "memory: omr_search_rows: null argument");
+  if (dim != s->dim)
+    return fail_msg(OMR_E_DIM, "memory: similar observations: different vector dimensions %d and %d", s->dim, dim);
+  if (k <= 0) k = 5;
+  std::lock_guard<std::mutex> lk(s->mu);
+  cudaSetDevice(s->cfg.device);
+  return s->host_search(queries, nq, filters, n_filters, query_filter, k, nullptr, counts, rows, distances);
+}
+
+int omr_cosine_ranked(omr_store* s, const float* query, int32_t dim, const omr_filter* filter, int32_t fanout,
+                      omr_hit* hits, int32_t* count) {
+  if (!s || !query || !filter || !hits || !count) return fail_msg(OMR_E_INVALID, "memory: omr_cosine_ranked: null argument");
+  if (dim != s->dim)
+    return fail_msg(OMR_E_DIM, "memory: hybrid retrieve: different vector dimensions %d and %d", s->dim, dim);
+  if (fanout <= 0) return fail_msg(OMR_E_INVALID, "memory: fanout must be positive");
+  const int over = 4 * fanout;  // `LIMIT $6 * 4`, store.go:260
+  if (over > 4096) return fail_msg(OMR_E_INVALID, "memory: fanout %d exceeds 1024", fanout);
+  std::lock_guard<std::mutex> lk(s->mu);
+  cudaSetDevice(s->cfg.device);
+  std::vector<omr_hit> ann((size_t)over);
+  int32_t got = 0;
+  omr_filter f = *filter;
+  f.max_distance = NAN;  // the recall arm has no distance cutoff
+  int rc = s->host_search(query, 1, &f, 1, nullptr, over, ann.data(), &got);
+  if (rc) return rc;
+  // cosine: DISTINCT ON (entity_id) nearest observation; cosine_ranked: ORDER BY cos_dist LIMIT fanout.
+  std::unordered_map<Key128, bool, Key128Hash> seen;
+  int out = 0;
+  for (int i = 0; i < got && out < fanout; i++) {
+    const Key128 e = key_of(ann[i].entity_id);
+    if (seen.emplace(e, true).second) hits[out++] = ann[i];
+  }
+  *count = out;
+  return OMR_OK;
+}
+
+int omr_device_build_bitmaps(omr_store* s, const omr_filter* filters, int32_t n_filters, uint32_t* d_bitmaps,
+                             void* stream) {
+  if (!s || !filters || !d_bitmaps || n_filters <= 0) return fail_msg(OMR_E_INVALID, "memory: omr_device_build_bitmaps: bad argument");
+  std::lock_guard<std::mutex> lk(s->mu);
+  cudaSetDevice(s->cfg.device);
+  std::vector<DeviceFilter> df((size_t)n_filters);
+  double unused;
+  int rc;
+  for (int i = 0; i < n_filters; i++)
+    if ((rc = s->to_device_filter(filters[i], &df[i], &unused))) return rc;
+  if ((rc = s->w_filters.reserve((size_t)std::max(64, n_filters + 1)))) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  OMR_CUDA_OK(cudaMemcpyAsync(s->w_filters.p, df.data(), (size_t)n_filters * sizeof(DeviceFilter), cudaMemcpyHostToDevice, st));
+  OMR_CUDA_OK(cudaStreamSynchronize(st));
+  rc = launch_build_bitmaps(s->meta(), s->n, (int)s->words(), s->w_filters.p, n_filters, d_bitmaps, st);
+  s->st_launches++;
+  return rc;
+}
+
+int omr_device_search(omr_store* s, const float* d_queries, int32_t nq, const uint32_t* d_bitmaps, int32_t n_groups,
+                      const int32_t* d_query_group, const double* d_max_distance, int32_t k, int64_t* d_rows,
+                      double* d_dist, int32_t* d_count, void* stream) {
+  if (!s || !d_queries || !d_rows || !d_dist || !d_count) return fail_msg(OMR_E_INVALID, "memory: omr_device_search: null argument");
+  (void)n_groups;
+  std::lock_guard<std::mutex> lk(s->mu);
+  cudaSetDevice(s->cfg.device);
+  return s->device_search(d_queries, nq, d_bitmaps, d_query_group, d_max_distance, k, d_rows, d_dist, d_count,
+                          (cudaStream_t)stream);
+}
+
+int omr_device_merge_topk(omr_store* s, const int64_t* d_in_rows, const double* d_in_dist, int32_t n_shards,
+                          int32_t nq, int32_t k, int64_t* d_rows, double* d_dist, int32_t* d_count, void* stream) {
+  if (!s || !d_in_rows || !d_in_dist || !d_rows || !d_dist || !d_count) return fail_msg(OMR_E_INVALID, "memory: omr_device_merge_topk: null argument");
+  std::lock_guard<std::mutex> lk(s->mu);
+  cudaSetDevice(s->cfg.device);
+  s->st_launches++;
+  return launch_merge_topk(d_in_rows, d_in_dist, n_shards, nq, k, d_rows, d_dist, d_count, (cudaStream_t)stream);
+}
+
+int omr_selfjoin(omr_store* s, const omr_selfjoin_opts* o, omr_pair* out, int64_t cap, int64_t* found) {
+  if (!s || !o || !found || (cap > 0 && !out)) return fail_msg(OMR_E_INVALID, "memory: omr_selfjoin: null argument");
+  if (!o->workspace_id || !o->workspace_id[0]) return fail_msg(OMR_E_WORKSPACE, "memory: workspace_id is required");
+  std::lock_guard<std::mutex> lk(s->mu);
+  cudaSetDevice(s->cfg.device);
+  *found = 0;
+  uint32_t ws;
+  if (!s->ws_names.lookup(o->workspace_id, &ws) || s->n == 0) return OMR_OK;
+  // Members: one row per entity of the workspace that carries a usable embedding.
+  std::vector<double> hnorm((size_t)s->n);
+  OMR_CUDA_OK(cudaMemcpy(hnorm.data(), s->d_norm2, (size_t)s->n * 8, cudaMemcpyDeviceToHost));
+  std::vector<int32_t> idx;
+  for (int64_t r = 0; r < s->n; r++) {
+    const uint8_t f = s->h_flags[r];
+    if (s->h_ws[r] != ws || !(f & OMR_ROW_HAS_EMBEDDING) || !(f & kRowEntityRep) || (f & kRowDeleted)) continue;
+    if (!(hnorm[r] > 0.0) || hnorm[r] != hnorm[r] || hnorm[r] > 1e300) continue;  // NaN similarity never passes `>= floor`
+    if (o->require_mutable && !(f & OMR_ROW_MUTABLE)) continue;
+    idx.push_back((int32_t)r);
+  }
+  const int64_t m = (int64_t)idx.size();
+  if (m < 2) return OMR_OK;
+  cudaStream_t st = s->stream;
+  int rc;
+  const bool identity = m == s->n;
+  const int64_t m_pad = ((m + kTileRows - 1) / kTileRows) * kTileRows;
+  CUtensorMap ta, tb;
+  if (identity) {
+    ta = s->tmap_rows_a;
+    tb = s->tmap_rows_b;
+  } else {
+    if ((rc = s->w_gather.reserve((size_t)m_pad * s->pitch))) return rc;
+    if ((rc = s->w_idx.reserve((size_t)m))) return rc;
+    OMR_CUDA_OK(cudaMemcpyAsync(s->w_idx.p, idx.data(), (size_t)m * 4, cudaMemcpyHostToDevice, st));
+    OMR_CUDA_OK(cudaMemsetAsync(s->w_gather.p + (size_t)m * s->pitch, 0, (size_t)(m_pad - m) * s->pitch * 2, st));
+    if ((rc = launch_gather_rows(s->view(), s->w_idx.p, m, s->w_gather.p, st))) return rc;
+    s->st_launches++;
+    if ((rc = s->make_tmap(&ta, s->w_gather.p, (uint64_t)m_pad, kQueryTile))) return rc;
+    if ((rc = s->make_tmap(&tb, s->w_gather.p, (uint64_t)m_pad, kTileRows))) return rc;
+  }
+  std::vector<uint32_t> member((size_t)(m_pad / 32), 0u);
+  for (int64_t i = 0; i < m; i++) member[(size_t)(i >> 5)] |= 1u << (i & 31);
+  if ((rc = s->w_member.reserve(member.size()))) return rc;
+  OMR_CUDA_OK(cudaMemcpyAsync(s->w_member.p, member.data(), member.size() * 4, cudaMemcpyHostToDevice, st));
+  if ((rc = s->w_pair_count.reserve(1))) return rc;
+  const double floor_d = (double)o->similarity_floor;  // float32 widened once, as Postgres does
+  const float thr = (float)(floor_d - (double)s->margin);
+  unsigned long long pcap = std::max<unsigned long long>(s->w_pairs.n, 1ull << 20);
+  unsigned long long cnt = 0;
+  for (int attempt = 0; attempt < 2; attempt++) {
+    if ((rc = s->w_pairs.reserve((size_t)pcap))) return rc;
+    OMR_CUDA_OK(cudaMemsetAsync(s->w_pair_count.p, 0, 8, st));
+    if ((rc = launch_selfjoin_umma(ta, tb, m, s->pitch / kBlockK, thr, s->w_member.p, s->w_pairs.p, pcap,
+                                   s->w_pair_count.p, s->num_sms, st)))
+      return rc;
+    s->st_launches++;
+    OMR_CUDA_OK(cudaMemcpyAsync(&cnt, s->w_pair_count.p, 8, cudaMemcpyDeviceToHost, st));
+    OMR_CUDA_OK(cudaStreamSynchronize(st));
+    if (cnt <= pcap) break;
+    if (attempt == 1) return fail_msg(OMR_E_CAPACITY, "memory: self-join candidate count kept growing");
+    pcap = cnt + (cnt >> 3);
+  }
+  if (cnt == 0) return OMR_OK;
+  if (!identity) {
+    if ((rc = launch_pair_remap(s->w_pairs.p, cnt, s->w_idx.p, st))) return rc;
+    s->st_launches++;
+  }
+  if ((rc = s->w_pair_sim.reserve((size_t)cnt))) return rc;
+  if ((rc = launch_pair_rescore(s->view(), s->w_pairs.p, cnt, s->w_pair_sim.p, st))) return rc;
+  s->st_launches++;
+  std::vector<PairCand> hp((size_t)cnt);
+  std::vector<double> hs((size_t)cnt);
+  OMR_CUDA_OK(cudaMemcpyAsync(hp.data(), s->w_pairs.p, (size_t)cnt * sizeof(PairCand), cudaMemcpyDeviceToHost, st));
+  OMR_CUDA_OK(cudaMemcpyAsync(hs.data(), s->w_pair_sim.p, (size_t)cnt * 8, cudaMemcpyDeviceToHost, st));
+  OMR_CUDA_OK(cudaStreamSynchronize(st));
+  struct P { double sim; int64_t c, d; };
+  std::vector<P> keep;
+  for (size_t i = 0; i < (size_t)cnt; i++) {
+    if (!(hs[i] >= floor_d)) continue;
+    const int64_t a = hp[i].a, b = hp[i].b;
+    if (o->require_same_kind && s->h_kind[a] != s->h_kind[b]) continue;
+    uint8_t ia[16], ib[16];
+    key_to(s->entity_id[s->h_entity[a]], ia);
+    key_to(s->entity_id[s->h_entity[b]], ib);
+    const int c = memcmp(ia, ib, 16);
+    if (c == 0) continue;
+    keep.push_back(c < 0 ? P{hs[i], a, b} : P{hs[i], b, a});
+  }
+  std::sort(keep.begin(), keep.end(), [](const P& x, const P& y) {
+    if (x.sim != y.sim) return x.sim > y.sim;
+    if (x.c != y.c) return x.c < y.c;
+    return x.d < y.d;
+  });
+  int64_t total = (int64_t)keep.size();
+  if (o->limit > 0) total = std::min<int64_t>(total, o->limit);
+  *found = total;
+  for (int64_t i = 0; i < std::min(total, cap); i++) {
+    omr_pair& p = out[i];
+    key_to(s->entity_id[s->h_entity[keep[i].c]], p.canonical_id);
+    key_to(s->entity_id[s->h_entity[keep[i].d]], p.dupe_id);
+    p.similarity = keep[i].sim;
+    p.canonical_row = s->cfg.row_base + keep[i].c * s->cfg.row_stride;
+    p.dupe_row = s->cfg.row_base + keep[i].d * s->cfg.row_stride;
+    p.kind = s->h_kind[keep[i].c];
+  }
+  return OMR_OK;
+}
+
+// Diagnostics: runs only query preparation + one scorer and returns the raw packed keys
+// ([nq][n_tiles * (256 / S) * 2] int32, host), so tests can check a scorer in isolation.
+int omr_debug_candidate_keys(omr_store* s, const float* queries, int32_t nq, int32_t path, int32_t S,
+                             int32_t* out_keys, int64_t out_len) {
+  if (!s || !queries || !out_keys) return fail_msg(OMR_E_INVALID, "memory: omr_debug_candidate_keys: null argument");
+  if (S != 32 && S != 64 && S != 128 && S != 256) return fail_msg(OMR_E_INVALID, "memory: bad sub-bucket %d", S);
+  if (path != 1 && path != 2) return fail_msg(OMR_E_INVALID, "memory: path must be 1 or 2");
+  std::lock_guard<std::mutex> lk(s->mu);
+  cudaSetDevice(s->cfg.device);
+  if (s->n == 0 || nq <= 0) return OMR_OK;
+  cudaStream_t st = s->stream;
+  int rc;
+  const int n_tiles = (int)((s->n + kTileRows - 1) / kTileRows);
+  const int64_t kpq = (int64_t)n_tiles * (kTileRows / S) * 2;
+  if (out_len < (int64_t)nq * kpq) return fail_msg(OMR_E_CAPACITY, "memory: need %lld keys", (long long)((int64_t)nq * kpq));
+  const int qpad = path == 2 ? ((nq + kQueryTile - 1) / kQueryTile) * kQueryTile : std::max(nq, 8);
+  if ((rc = s->w_queries.reserve((size_t)nq * s->dim))) return rc;
+  if ((rc = s->w_qn.reserve((size_t)qpad * s->pitch))) return rc;
+  if ((rc = s->w_qnorm2.reserve((size_t)qpad))) return rc;
+  if ((rc = s->w_cand.reserve((size_t)qpad * kpq))) return rc;
+  if ((rc = s->ensure_live(st))) return rc;
+  OMR_CUDA_OK(cudaMemcpyAsync(s->w_queries.p, queries, (size_t)nq * s->dim * 4, cudaMemcpyHostToDevice, st));
+  if ((rc = launch_prep_queries(s->w_queries.p, nq, qpad, s->dim, s->pitch, s->w_qn.p, s->w_qnorm2.p, st))) return rc;
+  if (path == 1) {
+    for (int q0 = 0; q0 < nq; q0 += 8) {
+      const int c = std::min(8, nq - q0);
+      if ((rc = launch_score_stream(s->view(), s->w_qn.p + (size_t)q0 * s->pitch, c, n_tiles, S, s->w_live.p,
+                                    (int)s->words(), nullptr, s->w_cand.p + (size_t)q0 * kpq, s->num_sms, st)))
+        return rc;
+    }
+  } else {
+    if (s->tmap_q_ptr != s->w_qn.p || s->tmap_q_rows != s->w_qn.n / s->pitch) {
+      if ((rc = s->make_tmap(&s->tmap_q, s->w_qn.p, s->w_qn.n / s->pitch, kQueryTile))) return rc;
+      s->tmap_q_ptr = s->w_qn.p;
+      s->tmap_q_rows = s->w_qn.n / s->pitch;
+    }
+    if ((rc = launch_score_umma(s->tmap_q, s->tmap_rows_b, qpad / kQueryTile, n_tiles, s->pitch / kBlockK, S,
+                                s->w_live.p, (int)s->words(), nullptr, s->w_cand.p, s->num_sms, st)))
+      return rc;
+  }
+  OMR_CUDA_OK(cudaMemcpyAsync(out_keys, s->w_cand.p, (size_t)nq * kpq * 4, cudaMemcpyDeviceToHost, st));
+  OMR_CUDA_OK(cudaStreamSynchronize(st));
+  return OMR_OK;
+}
+
+int omr_get_stats(const omr_store* s, omr_stats* out) {
+  if (!s || !out) return fail_msg(OMR_E_INVALID, "memory: null argument");
+  out->kernel_launches = s->st_launches.load();
+  out->searches = s->st_searches.load();
+  out->queries = s->st_queries.load();
+  out->rescued_rows = s->st_rescued.load();
+  out->fallback_queries = s->st_fallback.load();
+  out->last_path = s->last_path;
+  out->last_sub_bucket = s->last_S;
+  out->last_rescore_width = s->last_K2;
+  out->num_sms = s->num_sms;
+  out->scorer_ms_sum = s->scorer_ms_sum;
+  out->scorer_timed = s->scorer_timed;
+  return OMR_OK;
+}
+
+int omr_set_profiling(omr_store* s, int32_t on) {
+  if (!s) return fail_msg(OMR_E_INVALID, "memory: null argument");
+  std::lock_guard<std::mutex> lk(s->mu);
+  s->profiling = on != 0;
+  s->scorer_ms_sum = 0.0;
+  s->scorer_timed = 0;
+  return OMR_OK;
+}
+
+const char* omr_kind_name(const omr_store* s, uint32_t kind) {
+  if (!s || kind >= s->kind_names.names.size()) return "";
+  return s->kind_names.names[kind].c_str();
+}
+
+}  // extern "C"

@@ -1,0 +1,79 @@
+"""Row-sharded recall across the GPUs of one box.
+
+One process per GPU.  Rank r holds rows r, r+G, r+2G, ... of the store (round-robin, so every
+workspace spreads evenly), answers each query batch with its exact local top-k, and the per-rank
+answers are exchanged with ONE allgather of k x (float64 distance, int64 global row) per query over
+NCCL/NVLink; every rank then merges G*k -> k with the library's merge kernel.  The global top-k is
+exact because each shard returns its full local top-k.
+
+torch.distributed is plumbing here (process group + the collective); the scoring, selection and
+merge are the library's kernels.
+"""
+from __future__ import annotations
+
+from typing import Optional, Tuple
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+from .store import FilterSpec, GPUMemoryStore
+
+
+def shard_of(n_rows: int, rank: int, world: int) -> Tuple[int, int, int]:
+    """(rows on this rank, row_base, row_stride) for round-robin sharding of n_rows."""
+    return (n_rows - rank + world - 1) // world, rank, world
+
+
+def gather_candidates(rows: torch.Tensor, dist_: torch.Tensor, group=None) -> Tuple[torch.Tensor, torch.Tensor]:
+    """Allgather of per-rank [nq, k] answers into [G, nq, k] (works on any backend; gloo in CPU tests)."""
+    world = dist.get_world_size(group)
+    out_r = torch.empty((world,) + tuple(rows.shape), dtype=rows.dtype, device=rows.device)
+    out_d = torch.empty((world,) + tuple(dist_.shape), dtype=dist_.dtype, device=dist_.device)
+    dist.all_gather_into_tensor(out_r, rows.contiguous(), group=group)
+    dist.all_gather_into_tensor(out_d, dist_.contiguous(), group=group)
+    return out_r, out_d
+
+
+class ShardedRecall:
+    """The local shard plus the exchange step.  With no process group it is a single shard."""
+
+    def __init__(self, dim: int, n_rows_total: int, device: int, group=None, **store_kw):
+        self.group = group
+        live = dist.is_available() and dist.is_initialized()
+        self.rank = dist.get_rank(group) if live else 0
+        self.world = dist.get_world_size(group) if live else 1
+        n_local, base, stride = shard_of(n_rows_total, self.rank, self.world)
+        self.store = GPUMemoryStore(dim, max(1, n_local), device=device, row_base=base, row_stride=stride, **store_kw)
+        self.device = torch.device("cuda", device)
+        self._buf = {}
+
+    def _buffers(self, nq: int, k: int):
+        key = (nq, k)
+        if key not in self._buf:
+            d = self.device
+            self._buf[key] = dict(
+                lr=torch.empty((nq, k), dtype=torch.int64, device=d), ld=torch.empty((nq, k), dtype=torch.float64, device=d),
+                lc=torch.empty(nq, dtype=torch.int32, device=d),
+                gr=torch.empty((self.world, nq, k), dtype=torch.int64, device=d),
+                gd=torch.empty((self.world, nq, k), dtype=torch.float64, device=d),
+                r=torch.empty((nq, k), dtype=torch.int64, device=d), d=torch.empty((nq, k), dtype=torch.float64, device=d),
+                c=torch.empty(nq, dtype=torch.int32, device=d))
+        return self._buf[key]
+
+    def search_device(self, d_queries: torch.Tensor, k: int, d_bitmaps=None, d_query_group=None, d_max_distance=None):
+        """Global top-k for device-resident queries; returns (rows, dist, count) device tensors."""
+        nq = d_queries.shape[0]
+        b = self._buffers(nq, k)
+        stream = torch.cuda.current_stream(self.device).cuda_stream
+        self.store.device_search(d_queries, k, b["lr"], b["ld"], b["lc"], d_bitmaps, 0, d_query_group,
+                                 d_max_distance, stream)
+        if self.world == 1:
+            return b["lr"], b["ld"], b["lc"]
+        dist.all_gather_into_tensor(b["gr"], b["lr"], group=self.group)
+        dist.all_gather_into_tensor(b["gd"], b["ld"], group=self.group)
+        self.store.device_merge_topk(b["gr"], b["gd"], self.world, nq, k, b["r"], b["d"], b["c"], stream)
+        return b["r"], b["d"], b["c"]
+
+    def close(self):
+        self.store.close()

@@ -1,0 +1,343 @@
+"""Host-side mirror of the reference's store interface for the recall path.
+
+`GPUMemoryStore` carries the methods of Go's ``memory.Store`` that reach pgvector
+(internal/memory/types.go:231-332) with the same names, argument meaning and error
+behaviour, so the parity tests read like the reference's own tests:
+
+    FindSimilarObservations   -> find_similar_observations   (store_read.go:243-306)
+    UpdateEmbedding           -> update_embedding            (store_write.go:557-578)
+    UpdateObservationEmbedding-> upsert                      (store_write.go:580-600)
+    cosine arm of RetrieveHybrid -> cosine_ranked            (store.go:240-272)
+    RunEntityDuplicateCandidates -> run_entity_duplicate_candidates
+                                  (internal/memory/postgres/consolidation_prefilter.go:176-203)
+
+Everything here is a thin layer over the C ABI (include/omnia_recall.h); the arithmetic runs
+in libomnia_recall.so on the GPU and nowhere else.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import uuid as _uuid
+from dataclasses import dataclass
+from typing import Dict, List, Optional, Sequence, Union
+
+import numpy as np
+
+from . import _lib as L
+
+SCOPE_WORKSPACE_ID = "workspace_id"        # internal/memory/store.go:35
+SCOPE_VIRTUAL_USER_ID = "virtual_user_id"  # internal/memory/store.go:41
+SCOPE_AGENT_ID = "agent_id"                # internal/memory/store.go:47
+
+DEFAULT_DUPLICATE_CANDIDATE_LIMIT = 5      # internal/memory/types.go:137-141
+DEFAULT_AUTO_SUPERSEDE_SIMILARITY = 0.95
+DEFAULT_SURFACE_DUPLICATE_SIMILARITY = 0.85
+
+IdLike = Union[str, bytes, _uuid.UUID, int]
+
+
+def id_bytes(v: IdLike) -> bytes:
+    if isinstance(v, _uuid.UUID):
+        return v.bytes
+    if isinstance(v, bytes):
+        if len(v) != 16:
+            raise ValueError("uuid bytes must have length 16")
+        return v
+    if isinstance(v, int):
+        return int(v).to_bytes(16, "big")
+    return _uuid.UUID(str(v)).bytes
+
+
+def id_str(b) -> str:
+    return str(_uuid.UUID(bytes=bytes(b)))
+
+
+@dataclass
+class SimilarObservation:  # internal/memory/types.go:126-131 (Content stays in Postgres)
+    observation_id: str
+    entity_id: str
+    similarity: float
+    row: int
+
+
+@dataclass
+class DuplicatePair:
+    """One bucket of RunEntityDuplicateCandidates: Key "dupe:<canonical>:<dupe>", Stats.similarity."""
+    canonical_id: str
+    dupe_id: str
+    similarity: float
+    kind: str
+    canonical_row: int
+    dupe_row: int
+
+    @property
+    def key(self) -> str:
+        return f"dupe:{self.canonical_id}:{self.dupe_id}"
+
+
+def _cstr(s: Optional[str]) -> Optional[bytes]:
+    return None if s is None else s.encode()
+
+
+def _str_array(items: Sequence[str]):
+    arr = (C.c_char_p * max(1, len(items)))()
+    for i, s in enumerate(items):
+        arr[i] = s.encode()
+    return arr
+
+
+class FilterSpec:
+    """Reference row a8 -- the WHERE clause of a recall query.  Keeps its C strings alive."""
+
+    def __init__(self, workspace_id: str, virtual_user_id: Optional[str] = None, user_mode: Optional[int] = None,
+                 agent_id: Optional[str] = None, agent_mode: Optional[int] = None, kinds: Sequence[str] = (),
+                 purposes: Sequence[str] = (), min_confidence: float = 0.0, max_distance: float = float("nan"),
+                 now_us: int = 0):
+        # single-tier default: a nil scope value means "no constraint" (store.go:252-253)
+        if user_mode is None:
+            user_mode = L.MATCH_EQ if virtual_user_id is not None else L.MATCH_ANY
+        if agent_mode is None:
+            agent_mode = L.MATCH_EQ if agent_id is not None else L.MATCH_ANY
+        self._kinds = _str_array(kinds)
+        self._purposes = _str_array(purposes)
+        self.c = L.Filter(_cstr(workspace_id), _cstr(virtual_user_id), user_mode, _cstr(agent_id), agent_mode,
+                          C.cast(self._kinds, L.c_str_p), len(kinds), C.cast(self._purposes, L.c_str_p),
+                          len(purposes), float(min_confidence), float(max_distance), int(now_us))
+
+    @staticmethod
+    def from_scope(scope: Dict[str, str], **kw) -> "FilterSpec":
+        return FilterSpec(scope.get(SCOPE_WORKSPACE_ID, ""), scope.get(SCOPE_VIRTUAL_USER_ID) or None, None,
+                          scope.get(SCOPE_AGENT_ID) or None, None, **kw)
+
+
+def _filters_array(filters: Sequence[FilterSpec]):
+    arr = (L.Filter * len(filters))()
+    for i, f in enumerate(filters):
+        arr[i] = f.c
+    return arr
+
+
+class GPUMemoryStore:
+    def __init__(self, dim: int, capacity: int, device: int = 0, row_base: int = 0, row_stride: int = 1,
+                 candidate_margin: float = 0.0, sub_bucket: int = 0, rescore_width: int = 0, force_path: int = 0):
+        self._lib = L.load()
+        self.dim = int(dim)
+        self.capacity = int(capacity)
+        self._h = C.c_void_p()
+        cfg = L.Config(self.dim, int(device), self.capacity, int(row_base), int(row_stride), float(candidate_margin),
+                       int(sub_bucket), int(rescore_width), int(force_path))
+        L.check(self._lib.omr_open(C.byref(cfg), C.byref(self._h)))
+
+    # -- lifecycle -------------------------------------------------------------
+    def close(self) -> None:
+        if getattr(self, "_h", None) is not None and self._h:
+            self._lib.omr_close(self._h)
+            self._h = C.c_void_p()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    @property
+    def handle(self) -> C.c_void_p:
+        return self._h
+
+    def __len__(self) -> int:
+        return int(self._lib.omr_count(self._h))
+
+    def stats(self) -> L.Stats:
+        st = L.Stats()
+        L.check(self._lib.omr_get_stats(self._h, C.byref(st)))
+        return st
+
+    def set_profiling(self, on: bool) -> None:
+        L.check(self._lib.omr_set_profiling(self._h, int(on)))
+
+    def bitmap_words(self) -> int:
+        return int(self._lib.omr_bitmap_words(self._h))
+
+    # -- ingest ----------------------------------------------------------------
+    def bulk_load(self, vectors: np.ndarray, *, observation_ids: Optional[np.ndarray] = None,
+                  entity_ids: Optional[np.ndarray] = None, workspaces: Sequence[str] = ("default",),
+                  workspace_idx: Optional[np.ndarray] = None, users: Sequence[str] = (),
+                  user_idx: Optional[np.ndarray] = None, agents: Sequence[str] = (),
+                  agent_idx: Optional[np.ndarray] = None, kinds: Sequence[str] = (),
+                  kind_idx: Optional[np.ndarray] = None, purposes: Sequence[str] = (),
+                  purpose_idx: Optional[np.ndarray] = None, confidence: Optional[np.ndarray] = None,
+                  flags: Optional[np.ndarray] = None, valid_until_us: Optional[np.ndarray] = None) -> None:
+        v = np.ascontiguousarray(vectors, np.float32)
+        if v.ndim != 2 or v.shape[1] != self.dim:
+            raise L.RecallError(L.E_DIM, f"memory: embedding dimension mismatch: got {v.shape[-1]}, store has {self.dim}")
+        n = v.shape[0]
+        keep = [v]
+
+        def arr(a, dt, width=None):
+            if a is None:
+                return None
+            a = np.ascontiguousarray(a, dt)
+            if a.shape[0] != n or (width and a.reshape(n, -1).shape[1] != width):
+                raise ValueError("bulk_load: array length mismatch")
+            keep.append(a)
+            return a.ctypes.data
+
+        tabs = [_str_array(t) for t in (workspaces, users, agents, kinds, purposes)]
+        b = L.Bulk(n, v.ctypes.data, arr(observation_ids, np.uint8, 16), arr(entity_ids, np.uint8, 16),
+                   C.cast(tabs[0], L.c_str_p), len(workspaces), arr(workspace_idx, np.uint32),
+                   C.cast(tabs[1], L.c_str_p), len(users), arr(user_idx, np.int32),
+                   C.cast(tabs[2], L.c_str_p), len(agents), arr(agent_idx, np.int32),
+                   C.cast(tabs[3], L.c_str_p), len(kinds), arr(kind_idx, np.uint16),
+                   C.cast(tabs[4], L.c_str_p), len(purposes), arr(purpose_idx, np.uint16),
+                   arr(confidence, np.float32), arr(flags, np.uint8), arr(valid_until_us, np.int64))
+        L.check(self._lib.omr_bulk_load(self._h, C.byref(b)))
+
+    def upsert(self, observation_id: IdLike, entity_id: IdLike, scope: Dict[str, str], embedding, *,
+               kind: str = "", purpose: str = "", confidence: float = 1.0,
+               flags: int = L.ROW_HAS_EMBEDDING | L.ROW_MUTABLE, valid_until_us: int = L.NO_EXPIRY) -> None:
+        """UpdateObservationEmbedding (store_write.go:580-600) plus the metadata the filter reads."""
+        v = np.ascontiguousarray(embedding, np.float32).reshape(-1)
+        r = L.Row()
+        C.memmove(r.observation_id, id_bytes(observation_id), 16)
+        C.memmove(r.entity_id, id_bytes(entity_id), 16)
+        r.workspace_id = _cstr(scope.get(SCOPE_WORKSPACE_ID, ""))
+        r.virtual_user_id = _cstr(scope.get(SCOPE_VIRTUAL_USER_ID) or None)
+        r.agent_id = _cstr(scope.get(SCOPE_AGENT_ID) or None)
+        r.kind, r.purpose = kind.encode(), purpose.encode()
+        r.confidence, r.flags, r.valid_until_us = float(confidence), int(flags), int(valid_until_us)
+        L.check(self._lib.omr_upsert(self._h, C.byref(r), v.ctypes.data, v.shape[0]))
+
+    def update_embedding(self, entity_id: IdLike, embedding) -> None:
+        """UpdateEmbedding (store_write.go:557-578)."""
+        v = np.ascontiguousarray(embedding, np.float32).reshape(-1)
+        L.check(self._lib.omr_update_embedding(self._h, id_bytes(entity_id), v.ctypes.data, v.shape[0]))
+
+    def set_row_flags(self, observation_id: IdLike, set_mask: int = 0, clear_mask: int = 0) -> None:
+        L.check(self._lib.omr_set_row_flags(self._h, id_bytes(observation_id), set_mask, clear_mask))
+
+    def forget(self, entity_id: IdLike) -> None:
+        """Soft delete: forgotten = true (store_delete.go:30-57)."""
+        L.check(self._lib.omr_set_entity_flags(self._h, id_bytes(entity_id), L.ROW_FORGOTTEN, 0))
+
+    def supersede(self, observation_id: IdLike) -> None:
+        L.check(self._lib.omr_set_row_flags(self._h, id_bytes(observation_id), L.ROW_SUPERSEDED, 0))
+
+    def set_valid_until(self, observation_id: IdLike, valid_until_us: int) -> None:
+        L.check(self._lib.omr_set_valid_until(self._h, id_bytes(observation_id), int(valid_until_us)))
+
+    def set_confidence(self, observation_id: IdLike, confidence: float) -> None:
+        L.check(self._lib.omr_set_confidence(self._h, id_bytes(observation_id), float(confidence)))
+
+    def delete_entity(self, entity_id: IdLike) -> None:
+        L.check(self._lib.omr_delete_entity(self._h, id_bytes(entity_id)))
+
+    # -- recall ----------------------------------------------------------------
+    def search(self, queries, filters: Sequence[FilterSpec], k: int, query_filter: Optional[np.ndarray] = None):
+        """Batched `ORDER BY embedding <=> q LIMIT k`.  Returns (rows [nq,k] int64 (-1 pad),
+        distances [nq,k] float64 (inf pad), counts [nq], hits ndarray of L.Hit)."""
+        q = np.ascontiguousarray(queries, np.float32)
+        if q.ndim == 1:
+            q = q[None, :]
+        nq = q.shape[0]
+        kk = k if k > 0 else DEFAULT_DUPLICATE_CANDIDATE_LIMIT
+        hits = (L.Hit * (nq * kk))()
+        counts = np.zeros(nq, np.int32)
+        qf = None if query_filter is None else np.ascontiguousarray(query_filter, np.int32)
+        fa = _filters_array(filters)
+        L.check(self._lib.omr_search(self._h, q.ctypes.data, nq, q.shape[1], fa, len(filters),
+                                     None if qf is None else qf.ctypes.data, k, hits, counts.ctypes.data))
+        rows = np.full((nq, kk), -1, np.int64)
+        dist = np.full((nq, kk), np.inf, np.float64)
+        for i in range(nq):
+            for j in range(int(counts[i])):
+                h = hits[i * kk + j]
+                rows[i, j], dist[i, j] = h.row, h.distance
+        return rows, dist, counts, hits
+
+    def search_rows(self, queries, filters: Sequence[FilterSpec], k: int, query_filter: Optional[np.ndarray] = None,
+                    out=None):
+        """omr_search_rows: the same recall with array results only (rows, distances, counts)."""
+        q = np.ascontiguousarray(queries, np.float32)
+        if q.ndim == 1:
+            q = q[None, :]
+        nq = q.shape[0]
+        kk = k if k > 0 else DEFAULT_DUPLICATE_CANDIDATE_LIMIT
+        rows, dist, counts = out if out is not None else (np.empty((nq, kk), np.int64), np.empty((nq, kk), np.float64),
+                                                          np.empty(nq, np.int32))
+        qf = None if query_filter is None else np.ascontiguousarray(query_filter, np.int32)
+        fa = _filters_array(filters)
+        L.check(self._lib.omr_search_rows(self._h, q.ctypes.data, nq, q.shape[1], fa, len(filters),
+                                          None if qf is None else qf.ctypes.data, k, rows.ctypes.data,
+                                          dist.ctypes.data, counts.ctypes.data))
+        return rows, dist, counts
+
+    def find_similar_observations(self, scope: Dict[str, str], query_embedding, k: int,
+                                  min_similarity: float, now_us: int = 0) -> List[SimilarObservation]:
+        """FindSimilarObservations (store_read.go:243-306): most similar first, similarity >= min."""
+        if not scope.get(SCOPE_WORKSPACE_ID):
+            raise L.RecallError(L.E_WORKSPACE, "memory: workspace_id is required")
+        kk = k if k > 0 else DEFAULT_DUPLICATE_CANDIDATE_LIMIT
+        f = FilterSpec.from_scope(scope, max_distance=1.0 - float(min_similarity), now_us=now_us)
+        _, _, counts, hits = self.search(np.asarray(query_embedding, np.float32)[None, :], [f], kk)
+        return [SimilarObservation(id_str(hits[j].observation_id), id_str(hits[j].entity_id),
+                                   1.0 - hits[j].distance, hits[j].row) for j in range(int(counts[0]))]
+
+    def cosine_ranked(self, flt: FilterSpec, query_embedding, fanout: int):
+        """cosine_ann -> cosine -> cosine_ranked (store.go:240-272): [(entity_id, cos_dist, cos_rn)]."""
+        q = np.ascontiguousarray(query_embedding, np.float32).reshape(-1)
+        hits = (L.Hit * max(1, fanout))()
+        cnt = C.c_int32(0)
+        L.check(self._lib.omr_cosine_ranked(self._h, q.ctypes.data, q.shape[0], C.byref(flt.c), fanout, hits,
+                                            C.byref(cnt)))
+        return [(id_str(hits[i].entity_id), hits[i].distance, i + 1) for i in range(cnt.value)]
+
+    # -- consolidation -----------------------------------------------------------
+    def run_entity_duplicate_candidates(self, workspace_id: str, similarity_floor: float = 0.85,
+                                        max_buckets_per_pass: int = 100, require_same_kind: bool = True,
+                                        require_mutable: bool = True) -> List[DuplicatePair]:
+        """RunEntityDuplicateCandidates (consolidation_prefilter.go:176-203; defaults worker.go:432-451)."""
+        opts = L.SelfJoinOpts(_cstr(workspace_id), float(similarity_floor), int(max_buckets_per_pass),
+                              int(require_same_kind), int(require_mutable))
+        cap = max_buckets_per_pass if max_buckets_per_pass > 0 else 1 << 16
+        while True:
+            out = (L.Pair * max(1, cap))()
+            found = C.c_int64(0)
+            L.check(self._lib.omr_selfjoin(self._h, C.byref(opts), out, cap, C.byref(found)))
+            if found.value <= cap:
+                break
+            cap = int(found.value)
+        return [DuplicatePair(id_str(p.canonical_id), id_str(p.dupe_id), p.similarity,
+                              (self._lib.omr_kind_name(self._h, p.kind) or b"").decode(), p.canonical_row, p.dupe_row)
+                for p in out[:found.value]]
+
+    def debug_candidate_keys(self, queries, path: int, S: int) -> np.ndarray:
+        q = np.ascontiguousarray(queries, np.float32)
+        nq = q.shape[0]
+        n_tiles = (len(self) + 255) // 256
+        out = np.empty((nq, n_tiles * (256 // S) * 2), np.int32)
+        L.check(self._lib.omr_debug_candidate_keys(self._h, q.ctypes.data, nq, path, S, out.ctypes.data, out.size))
+        return out
+
+    # -- device-pointer path (torch tensors are only carriers of device memory) -------
+    def device_build_bitmaps(self, filters: Sequence[FilterSpec], out_tensor, stream: int = 0) -> None:
+        fa = _filters_array(filters)
+        L.check(self._lib.omr_device_build_bitmaps(self._h, fa, len(filters), out_tensor.data_ptr(), stream))
+
+    def device_search(self, d_queries, k: int, d_rows, d_dist, d_count, d_bitmaps=None, n_groups: int = 0,
+                      d_query_group=None, d_max_distance=None, stream: int = 0) -> None:
+        nq = d_queries.shape[0]
+        p = lambda t: None if t is None else t.data_ptr()
+        L.check(self._lib.omr_device_search(self._h, d_queries.data_ptr(), nq, p(d_bitmaps), n_groups, p(d_query_group),
+                                            p(d_max_distance), k, d_rows.data_ptr(), d_dist.data_ptr(),
+                                            d_count.data_ptr(), stream))
+
+    def device_merge_topk(self, d_in_rows, d_in_dist, n_shards: int, nq: int, k: int, d_rows, d_dist, d_count,
+                          stream: int = 0) -> None:
+        L.check(self._lib.omr_device_merge_topk(self._h, d_in_rows.data_ptr(), d_in_dist.data_ptr(), n_shards, nq, k,
+                                                d_rows.data_ptr(), d_dist.data_ptr(), d_count.data_ptr(), stream))

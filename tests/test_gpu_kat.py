@@ -1,0 +1,182 @@
+"""The reference's own known-answer cases at the `<=>` boundary, run through the CUDA engine.
+Each test transcribes a Go test (cited) against GPUMemoryStore, whose methods mirror memory.Store."""
+import math
+import uuid
+
+import numpy as np
+import pytest
+
+from omnia_b200 import (GPUMemoryStore, FilterSpec, RecallError, NotFound, SCOPE_WORKSPACE_ID,
+                        SCOPE_VIRTUAL_USER_ID, SCOPE_AGENT_ID, MATCH_NULL_ONLY, MATCH_NULL_OR_EQ,
+                        ROW_HAS_EMBEDDING, ROW_MUTABLE)
+
+pytestmark = pytest.mark.gpu
+DIM = 1536
+WS1 = "00000000-0000-0000-0000-000000000001"   # testWorkspace1
+WS2 = "00000000-0000-0000-0000-000000000002"
+
+
+def repeat_float(v, n=DIM):
+    return np.full(n, v, np.float32)
+
+
+def one_hot(pos, n=DIM):
+    out = np.zeros(n, np.float32)
+    out[pos] = 1.0
+    return out
+
+
+def new_store(**kw):
+    return GPUMemoryStore(DIM, 4096, **kw)
+
+
+def save(store, scope, vec, **kw):
+    oid, eid = uuid.uuid4(), uuid.uuid4()
+    store.upsert(oid, eid, scope, vec, **kw)
+    return str(oid), str(eid)
+
+
+@pytest.mark.parametrize("path", [0, 1, 2, 3])
+def test_find_similar_ranks_by_cosine(path):
+    # store_test.go:422-442
+    with new_store(force_path=path) as s:
+        scope = {SCOPE_WORKSPACE_ID: WS1}
+        near, _ = save(s, scope, repeat_float(0.1), kind="preference", confidence=0.9)
+        far, _ = save(s, scope, repeat_float(0.9), kind="fact", confidence=0.9)
+        m = s.find_similar_observations(scope, repeat_float(0.1), 5, 0.5)
+        assert m, "require.NotEmpty"
+        assert m[0].similarity > 0.99
+        # both rows are parallel to the query: an exact tie in exact arithmetic
+        assert {x.observation_id for x in m} == {near, far}
+        assert abs(m[0].similarity - 1.0) < 1e-12 and abs(m[1].similarity - 1.0) < 1e-12
+
+
+@pytest.mark.parametrize("path", [0, 2, 3])
+def test_find_similar_honours_threshold(path):
+    # store_test.go:891-905
+    with new_store(force_path=path) as s:
+        scope = {SCOPE_WORKSPACE_ID: WS1}
+        oid, _ = save(s, scope, one_hot(0), kind="fact", confidence=0.9)
+        assert s.find_similar_observations(scope, one_hot(100), 5, 0.5) == []
+        got = s.find_similar_observations(scope, one_hot(100), 5, 0.0)     # d <= maxDistance is inclusive
+        assert [x.observation_id for x in got] == [oid] and got[0].similarity == 0.0
+
+
+def test_dimension_mismatch_is_an_error_not_a_panic():
+    # hnsw_ef_search_test.go:126-144
+    with new_store() as s:
+        scope = {SCOPE_WORKSPACE_ID: WS1}
+        save(s, scope, one_hot(1))
+        wrong = np.array([1, 2, 3], np.float32)
+        with pytest.raises(RecallError, match="different vector dimensions"):
+            s.find_similar_observations(scope, wrong, 5, 0.5)
+        with pytest.raises(RecallError, match="different vector dimensions"):
+            s.cosine_ranked(FilterSpec(WS1), wrong, 50)
+        with pytest.raises(RecallError):
+            s.upsert(uuid.uuid4(), uuid.uuid4(), scope, wrong)
+
+
+def test_workspace_required_and_default_k():
+    with new_store() as s:
+        with pytest.raises(RecallError, match="workspace_id is required"):   # store.go:60
+            s.find_similar_observations({}, one_hot(0), 5, 0.5)
+        scope = {SCOPE_WORKSPACE_ID: WS1}
+        for _ in range(9):
+            save(s, scope, one_hot(0))
+        assert len(s.find_similar_observations(scope, one_hot(0), 0, 0.5)) == 5   # types.go:137-141
+
+
+@pytest.mark.parametrize("path", [0, 1, 2, 3])
+def test_workspace_isolation_with_foreign_rows_at_distance_zero(path):
+    # hnsw_ef_search_test.go:167-187
+    with new_store(force_path=path) as s:
+        q = one_hot(7)
+        for _ in range(60):
+            save(s, {SCOPE_WORKSPACE_ID: WS2}, q, kind="fact", confidence=0.9)
+        target = np.zeros(DIM, np.float32)
+        target[7] = target[8] = 0.7071
+        _, eid = save(s, {SCOPE_WORKSPACE_ID: WS1}, target, kind="fact", confidence=0.9)
+        got = s.cosine_ranked(FilterSpec(WS1), q, 50)
+        assert [e for e, _, _ in got] == [eid]
+        assert abs(got[0][1] - (1 - math.sqrt(0.5))) < 1e-6 and got[0][2] == 1
+        # and the foreign rows are visible from their own workspace only
+        assert len(s.cosine_ranked(FilterSpec(WS2), q, 100)) == 60
+
+
+def test_scope_modes_user_and_agent():
+    # store.go:250-258 (nil = no constraint) and retrieve_multi_tier.go:313-328 (IS NULL / IS NULL OR =)
+    with new_store() as s:
+        v = one_hot(3)
+        rows = {}
+        for name, user, agent in [("none", None, None), ("u5", "u5", None), ("u6", "u6", None),
+                                  ("u5a9", "u5", "a9"), ("a9", None, "a9")]:
+            scope = {SCOPE_WORKSPACE_ID: WS1}
+            if user: scope[SCOPE_VIRTUAL_USER_ID] = user
+            if agent: scope[SCOPE_AGENT_ID] = agent
+            rows[save(s, scope, v)[0]] = name
+        def names(f):
+            _, _, cnt, hits = s.search(v[None, :], [f], 10)
+            from omnia_b200.store import id_str
+            return sorted(rows[id_str(hits[j].observation_id)] for j in range(int(cnt[0])))
+        assert names(FilterSpec(WS1)) == sorted(rows.values())
+        assert names(FilterSpec(WS1, "u5")) == ["u5", "u5a9"]
+        assert names(FilterSpec(WS1, "u5", None, "a9")) == ["u5a9"]
+        assert names(FilterSpec(WS1, None, MATCH_NULL_ONLY, None, MATCH_NULL_ONLY)) == ["none"]
+        assert names(FilterSpec(WS1, "u5", MATCH_NULL_OR_EQ, None, MATCH_NULL_ONLY)) == ["none", "u5"]
+        assert names(FilterSpec(WS1, "u5", MATCH_NULL_OR_EQ, "a9", MATCH_NULL_OR_EQ)) == ["a9", "none", "u5", "u5a9"]
+        assert names(FilterSpec(WS1, "nobody")) == []
+
+
+def test_row_state_edits_change_eligibility():
+    # forgotten / superseded / valid_until / confidence / kind (store.go:84-86, 250-258; appendix A)
+    with new_store() as s:
+        scope = {SCOPE_WORKSPACE_ID: WS1}
+        v = one_hot(5)
+        ids = [save(s, scope, v, kind=("fact" if i != 5 else "preference")) for i in range(7)]
+        def count(**kw):
+            return len(s.find_similar_observations(scope, v, 50, 0.5, **kw))
+        assert count() == 7
+        s.forget(ids[1][1]);                      assert count() == 6     # store_delete.go:42
+        s.supersede(ids[2][0]);                   assert count() == 5     # consolidation_writes.go:65
+        s.set_valid_until(ids[3][0], 1000)
+        assert count(now_us=999) == 5 and count(now_us=1000) == 4         # valid_until > now(), strict
+        s.set_confidence(ids[4][0], 0.3)
+        f = FilterSpec(WS1, min_confidence=0.5, max_distance=0.5, now_us=0)
+        assert int(s.search(v[None, :], [f], 50)[2][0]) == 4
+        f = FilterSpec(WS1, kinds=["preference"], now_us=0)
+        assert int(s.search(v[None, :], [f], 50)[2][0]) == 1
+        s.delete_entity(ids[5][1]);               assert int(s.search(v[None, :], [f], 50)[2][0]) == 0
+        with pytest.raises(NotFound):
+            s.forget(uuid.uuid4())                                         # store.go:69 ErrNotFound
+
+
+def test_update_embedding_targets_latest_observation_and_zero_vectors_never_match():
+    # store_write.go:557-578; pgvector returns NaN for a zero vector, which fails every `<=` cutoff
+    with new_store() as s:
+        scope = {SCOPE_WORKSPACE_ID: WS1}
+        eid = uuid.uuid4()
+        o1, o2 = uuid.uuid4(), uuid.uuid4()
+        s.upsert(o1, eid, scope, one_hot(1))
+        s.upsert(o2, eid, scope, one_hot(2))
+        s.update_embedding(eid, one_hot(9))
+        got = s.find_similar_observations(scope, one_hot(9), 5, 0.9)
+        assert [g.observation_id for g in got] == [str(o2)]
+        assert [g.observation_id for g in s.find_similar_observations(scope, one_hot(1), 5, 0.9)] == [str(o1)]
+        s.upsert(uuid.uuid4(), uuid.uuid4(), scope, np.zeros(DIM, np.float32))
+        assert len(s.find_similar_observations(scope, one_hot(9), 50, -1.0)) == 2
+        assert s.find_similar_observations(scope, np.zeros(DIM, np.float32), 50, -1.0) == []
+
+
+def test_cosine_arm_keeps_nearest_observation_per_entity():
+    # store.go:261-272
+    with new_store() as s:
+        scope = {SCOPE_WORKSPACE_ID: WS1}
+        def mix(c):
+            v = np.zeros(DIM, np.float32); v[0] = c; v[1] = math.sqrt(1 - c * c); return v
+        e10, e11, e12 = uuid.uuid4(), uuid.uuid4(), uuid.uuid4()
+        for e, c in [(e10, 0.9), (e10, 0.5), (e11, 0.8), (e12, 0.95), (e12, 0.1)]:
+            s.upsert(uuid.uuid4(), e, scope, mix(c))
+        got = s.cosine_ranked(FilterSpec(WS1), one_hot(0), 50)
+        assert [(e, rn) for e, _, rn in got] == [(str(e12), 1), (str(e10), 2), (str(e11), 3)]
+        assert np.allclose([d for _, d, _ in got], [0.05, 0.1, 0.2], atol=1e-6)
+        assert len(s.cosine_ranked(FilterSpec(WS1), one_hot(0), 2)) == 2          # LIMIT fanout

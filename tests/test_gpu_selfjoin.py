@@ -1,0 +1,68 @@
+"""Consolidation near-duplicate self-join (reference a11) vs the oracle: identical pair sets at
+the stated threshold, uuid-ordered canonical/dupe assignment, predicates, ORDER BY / LIMIT."""
+import numpy as np
+import pytest
+
+from omnia_b200 import GPUMemoryStore, synth, ROW_HAS_EMBEDDING, ROW_MUTABLE
+from omnia_b200.store import id_bytes
+from oracle import oracle as O
+
+pytestmark = pytest.mark.gpu
+
+
+def gpu_pairs(store, ws, floor, limit=0, **kw):
+    out = store.run_entity_duplicate_candidates(ws, floor, limit, **kw)
+    return [(p.canonical_row, p.dupe_row, p.similarity) for p in out], out
+
+
+@pytest.mark.parametrize("n,dim", [(4096, 256), (3000, 1536), (700, 100)])
+def test_planted_duplicates_pair_set_is_identical(n, dim):
+    corpus, planted = synth.planted_dups(n, dim, n_pairs=40)
+    rng = np.random.default_rng(11)
+    ids = rng.integers(0, 256, (n, 16)).astype(np.uint8)          # random uuids: order unrelated to rows
+    kind = rng.integers(0, 2, n).astype(np.uint16)
+    flags = np.full(n, ROW_HAS_EMBEDDING | ROW_MUTABLE, np.uint8)
+    flags[rng.random(n) < 0.05] &= ~np.uint8(ROW_MUTABLE)
+    with GPUMemoryStore(dim, n) as s:
+        s.bulk_load(corpus, observation_ids=ids, entity_ids=ids, kinds=["a", "b"], kind_idx=kind, flags=flags)
+        for floor in (0.92, 0.85):
+            got, _ = gpu_pairs(s, "default", floor)
+            a, b, sim = O.selfjoin(corpus, None, kind, flags, ids, floor, variant=O.VARIANT_F64)
+            want = {(int(x), int(y)) for x, y in zip(a, b)}
+            assert {(c, d) for c, d, _ in got} == want, f"floor {floor}"
+            assert len(want) > 0
+            gs = {(c, d): v for c, d, v in got}
+            for x, y, v in zip(a, b, sim):
+                assert abs(gs[(int(x), int(y))] - v) < 1e-9
+            assert all(got[i][2] >= got[i + 1][2] for i in range(len(got) - 1))   # ORDER BY similarity DESC
+        # predicates off -> a superset; LIMIT truncates after the ordering
+        all_pairs, _ = gpu_pairs(s, "default", 0.92, require_same_kind=False, require_mutable=False)
+        a2, b2, _ = O.selfjoin(corpus, None, kind, flags, ids, 0.92, False, False, variant=O.VARIANT_F64)
+        assert {(c, d) for c, d, _ in all_pairs} == {(int(x), int(y)) for x, y in zip(a2, b2)}
+        top3, objs = gpu_pairs(s, "default", 0.92, limit=3, require_same_kind=False, require_mutable=False)
+        assert top3 == all_pairs[:3]
+        assert objs[0].key.startswith("dupe:") and bytes(id_bytes(objs[0].canonical_id)) < bytes(id_bytes(objs[0].dupe_id))
+
+
+def test_selfjoin_is_scoped_to_one_workspace_and_float32_floor():
+    dim = 64
+    base = synth.gauss_unit(1, dim)[0]
+    def mix(c, seed):
+        r = synth.gauss_unit(1, dim, seed=seed)[0].astype(np.float64)
+        a = base.astype(np.float64); r -= r.dot(a) * a; r /= np.linalg.norm(r)
+        return (c * a + np.sqrt(1 - c * c) * r).astype(np.float32)
+    corpus = np.stack([base, mix(0.99, 2), mix(0.99, 3), base, mix(0.5, 4)])
+    ws = np.array([0, 0, 1, 1, 0], np.uint32)
+    with GPUMemoryStore(dim, 16) as s:
+        s.bulk_load(corpus, workspaces=["w0", "w1"], workspace_idx=ws)
+        p0, _ = gpu_pairs(s, "w0", 0.9)
+        p1, _ = gpu_pairs(s, "w1", 0.9)
+        assert {(c, d) for c, d, _ in p0} == {(0, 1)} and {(c, d) for c, d, _ in p1} == {(2, 3)}
+        assert gpu_pairs(s, "nope", 0.9)[0] == []
+        # (double)(float)0.99 = 0.99000000953...: a pair at exactly 0.99 (to fp rounding) may fall either
+        # side, but the oracle and the engine must agree
+        a, b, _ = O.selfjoin(corpus[:2], None, np.zeros(2, np.uint16),
+                             np.full(2, ROW_HAS_EMBEDDING | ROW_MUTABLE, np.uint8),
+                             np.array([[0] * 15 + [0], [0] * 15 + [1]], np.uint8), 0.99, variant=O.VARIANT_F64)
+        g, _ = gpu_pairs(s, "w0", 0.99)
+        assert len(g) == len(a)
