@@ -212,6 +212,26 @@ OMR_API int omr_device_search(omr_store* s, const float* d_queries, int32_t nq, 
 OMR_API int omr_device_merge_topk(omr_store* s, const int64_t* d_in_rows, const double* d_in_dist, int32_t n_shards,
                           int32_t nq, int32_t k, int64_t* d_rows, double* d_dist, int32_t* d_count, void* stream);
 
+/* ---- allocation-free exact top-k ------------------------------------------------
+ * No counterpart in the reference.  For hosts that cannot allocate device memory while they
+ * serve (all of HBM already belongs to another framework's pool; a latency-critical thread
+ * that must not take cudaMalloc's device-wide stall; a fixed start-up memory budget): the
+ * exact `ORDER BY row <=> query LIMIT k` of ONE query over the caller's own fp32 matrix
+ * d_rows [n][row_pitch] (first `dim` floats of each row are the vector), with the caller's
+ * result buffers d_out_rows [k] (-1 pad), d_out_dist [k] (+inf pad) and d_out_count [1].
+ * Rows without a cosine (zero vectors) never rank.  The one-distance-per-row scratch is a fixed
+ * array inside the library (OMR_NOALLOC_MAX_ROWS * 8 + 256 bytes, resident on every GPU that
+ * loads the library until exit), so n and k are capped and a larger request is refused with
+ * OMR_E_CAPACITY.  The call makes no cudaMalloc / cudaFree and calls no allocating routine.
+ * All calls on a GPU share that array: calls whose GPU work overlaps race, so serialise them.
+ * The first call on each device resolves the array's address; make it before any stream
+ * capture on that device.  Work is enqueued on `stream`; results are ready when it drains. */
+#define OMR_NOALLOC_MAX_ROWS 524288
+#define OMR_NOALLOC_MAX_K 128
+OMR_API int omr_exact_topk_noalloc(const float* d_rows, int64_t n, int32_t dim, int64_t row_pitch,
+                                   const float* d_query, int32_t k, int64_t* d_out_rows, double* d_out_dist,
+                                   int32_t* d_out_count, void* stream);
+
 /* ---- introspection ---------------------------------------------------------------*/
 typedef struct omr_stats {
   int64_t kernel_launches;   /* kernels this store has enqueued */

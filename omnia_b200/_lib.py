@@ -15,6 +15,7 @@ ROW_FORGOTTEN, ROW_SUPERSEDED, ROW_HAS_EMBEDDING, ROW_MUTABLE = 1, 2, 4, 8
 MATCH_ANY, MATCH_NULL_ONLY, MATCH_EQ, MATCH_NULL_OR_EQ = 0, 1, 2, 3
 NO_EXPIRY = 2**63 - 1
 MAX_DIM = 2000
+NOALLOC_MAX_ROWS, NOALLOC_MAX_K = 524288, 128
 
 c_str_p = C.POINTER(C.c_char_p)
 
@@ -98,6 +99,8 @@ SIGNATURES = {
                                     C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "omr_device_merge_topk": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_void_p,
                                         C.c_void_p, C.c_void_p, C.c_void_p]),
+    "omr_exact_topk_noalloc": (C.c_int, [C.c_void_p, C.c_int64, C.c_int32, C.c_int64, C.c_void_p, C.c_int32, C.c_void_p,
+                                         C.c_void_p, C.c_void_p, C.c_void_p]),
     "omr_get_stats": (C.c_int, [C.c_void_p, C.POINTER(Stats)]),
     "omr_set_profiling": (C.c_int, [C.c_void_p, C.c_int32]),
     "omr_kind_name": (C.c_char_p, [C.c_void_p, C.c_uint32]),

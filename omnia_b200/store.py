@@ -341,3 +341,14 @@ class GPUMemoryStore:
                           stream: int = 0) -> None:
         L.check(self._lib.omr_device_merge_topk(self._h, d_in_rows.data_ptr(), d_in_dist.data_ptr(), n_shards, nq, k,
                                                 d_rows.data_ptr(), d_dist.data_ptr(), d_count.data_ptr(), stream))
+
+
+def exact_topk_noalloc(d_rows, d_query, k: int, d_out_rows, d_out_dist, d_out_count, stream: int = 0) -> None:
+    """omr_exact_topk_noalloc: exact top-k of one query over a caller-owned fp32 device matrix with no
+    device allocation (for hosts that cannot call cudaMalloc while serving).  Arguments are device
+    tensors the caller already owns; at most NOALLOC_MAX_ROWS rows and NOALLOC_MAX_K results, more is
+    refused with RecallError.  Calls on one GPU share a fixed scratch array: do not overlap them."""
+    n, pitch = d_rows.shape[0], d_rows.stride(0)
+    L.check(L.load().omr_exact_topk_noalloc(d_rows.data_ptr(), n, d_query.shape[-1], pitch, d_query.data_ptr(), k,
+                                            d_out_rows.data_ptr(), d_out_dist.data_ptr(), d_out_count.data_ptr(),
+                                            stream))
