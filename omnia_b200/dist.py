@@ -30,8 +30,9 @@ def gather_candidates(rows: torch.Tensor, dist_: torch.Tensor, group=None) -> Tu
     world = dist.get_world_size(group)
     out_r = torch.empty((world,) + tuple(rows.shape), dtype=rows.dtype, device=rows.device)
     out_d = torch.empty((world,) + tuple(dist_.shape), dtype=dist_.dtype, device=dist_.device)
-    dist.all_gather_into_tensor(out_r, rows.contiguous(), group=group)
-    dist.all_gather_into_tensor(out_d, dist_.contiguous(), group=group)
+    # list-of-views form: every backend accepts it (gloo rejects the stacked into_tensor layout)
+    dist.all_gather(list(out_r.unbind(0)), rows.contiguous(), group=group)
+    dist.all_gather(list(out_d.unbind(0)), dist_.contiguous(), group=group)
     return out_r, out_d
 
 

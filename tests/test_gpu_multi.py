@@ -1,0 +1,23 @@
+"""Row-sharded recall over NCCL on real GPUs (needs >= 2 devices; skipped on a 1-GPU box, where
+tests/test_gpu_merge.py covers the same merge with G stores on one device and tests/test_dist_gloo.py
+covers the plumbing)."""
+import subprocess
+import sys
+from pathlib import Path
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+ROOT = Path(__file__).resolve().parent.parent
+
+
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_nccl_sharded_recall_matches_oracle(world):
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
+           "--master-addr", "127.0.0.1", "--master-port", str(29600 + world), str(ROOT / "scripts" / "dist_check.py")]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    assert r.stdout.count(": ok") == 3
