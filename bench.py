@@ -188,7 +188,7 @@ def main():
 
     t_setup = time.perf_counter()
     shard = synth.gauss_unit(N_ROWS, DIM, rank=rank, world=world)
-    sr = ShardedRecall(DIM, N_ROWS, local_rank)
+    sr = ShardedRecall(DIM, N_ROWS, local_rank, force_path=int(os.environ.get("OMNIA_BENCH_PATH", 0)))
     sr.store.bulk_load(shard)
     # query batches: perturbed copies of stored rows, identical on every rank
     hq = []

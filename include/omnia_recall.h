@@ -72,7 +72,8 @@ typedef struct omr_config {
   float candidate_margin;   /* bf16 stage safety margin in cosine units; <= 0 -> 1e-3 */
   int32_t sub_bucket;       /* 0 = choose from k; else 32 / 64 / 128 / 256 */
   int32_t rescore_width;    /* 0 = choose from k; candidates rescored exactly per query */
-  int32_t force_path;       /* 0 auto, 1 streaming scorer, 2 tensor-core scorer, 3 exact scan only */
+  int32_t force_path;       /* 0 auto, 1 streaming scorer, 2 tensor-core scorer (one CTA per tile),
+                               3 exact scan only, 4 tensor-core scorer with CTA pairs (cta_group::2) */
 } omr_config;
 
 OMR_API int omr_open(const omr_config* cfg, omr_store** out);
@@ -208,9 +209,11 @@ OMR_API int omr_device_search(omr_store* s, const float* d_queries, int32_t nq, 
                       const int32_t* d_query_group, const double* d_max_distance, int32_t k, int64_t* d_rows,
                       double* d_dist, int32_t* d_count, void* stream);
 /* Row-sharded stores: merges the G per-shard answers gathered into [G][nq][k]
- * (the gather itself is an NCCL allgather done by the host code). */
+ * (the gather itself is an NCCL allgather done by the host code).
+ * shard_stride = elements between consecutive shards' [nq][k] blocks (0 = nq*k), so rows and
+ * distances packed into ONE gathered buffer [G][2][nq][k] can be merged in place. */
 OMR_API int omr_device_merge_topk(omr_store* s, const int64_t* d_in_rows, const double* d_in_dist, int32_t n_shards,
-                          int32_t nq, int32_t k, int64_t* d_rows, double* d_dist, int32_t* d_count, void* stream);
+                          int32_t nq, int32_t k, int64_t shard_stride, int64_t* d_rows, double* d_dist, int32_t* d_count, void* stream);
 
 /* ---- allocation-free exact top-k ------------------------------------------------
  * No counterpart in the reference.  For hosts that cannot allocate device memory while they
@@ -252,10 +255,13 @@ OMR_API int omr_get_stats(const omr_store* s, omr_stats* out);
 OMR_API int omr_set_profiling(omr_store* s, int32_t on);
 OMR_API const char* omr_kind_name(const omr_store* s, uint32_t kind);
 /* Test hook, no reference counterpart: runs query preparation and ONE approximate scorer
- * (path 1 = streaming, 2 = tensor-core) over every live row and returns the raw packed
+ * (path 1 = streaming, 2 = tensor-core, 4 = tensor-core with CTA pairs) over every live row and returns the raw packed
  * candidate keys, [nq][ceil(n/256) * (256/S) * 2] int32 on the host.  A key is the
  * order-preserving int32 image of the bf16-accurate cosine with its low 8 bits replaced by
  * the row's offset inside its S-row sub-bucket; INT32_MIN = no eligible row. */
+/* Test hook: per-query clock64 stamps [nq][8] of the fused post-processing kernel's phases from the
+ * last search (only recorded when the store was opened with OMR_POST_TIMING=1 in the environment). */
+OMR_API int omr_debug_post_timing(omr_store* s, int64_t* out, int32_t nq);
 OMR_API int omr_debug_candidate_keys(omr_store* s, const float* queries, int32_t nq, int32_t path, int32_t S,
                                      int32_t* out_keys, int64_t out_len);
 

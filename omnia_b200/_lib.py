@@ -97,13 +97,14 @@ SIGNATURES = {
     "omr_device_build_bitmaps": (C.c_int, [C.c_void_p, C.POINTER(Filter), C.c_int32, C.c_void_p, C.c_void_p]),
     "omr_device_search": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p,
                                     C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
-    "omr_device_merge_topk": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_void_p,
+    "omr_device_merge_topk": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_int64, C.c_void_p,
                                         C.c_void_p, C.c_void_p, C.c_void_p]),
     "omr_exact_topk_noalloc": (C.c_int, [C.c_void_p, C.c_int64, C.c_int32, C.c_int64, C.c_void_p, C.c_int32, C.c_void_p,
                                          C.c_void_p, C.c_void_p, C.c_void_p]),
     "omr_get_stats": (C.c_int, [C.c_void_p, C.POINTER(Stats)]),
     "omr_set_profiling": (C.c_int, [C.c_void_p, C.c_int32]),
     "omr_kind_name": (C.c_char_p, [C.c_void_p, C.c_uint32]),
+    "omr_debug_post_timing": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32]),
     "omr_debug_candidate_keys": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_void_p,
                                            C.c_int64]),
 }

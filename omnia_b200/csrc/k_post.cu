@@ -1,0 +1,519 @@
+// Fused per-query post-processing: candidate selection, exact rescore, ORDER BY / LIMIT /
+// cutoff, exactness certificate and suspect-sub-bucket rescue in ONE kernel, one block per
+// query.  It replaces the select_keys -> rescore -> finalize -> rescore(items) ->
+// finalize_extra chain of k_select.cu (kept for K2 > 256 and as the exact fallback's tail)
+// and removes every intermediate global buffer between the scorer and the answer.
+//
+// Reference semantics implemented here: `ORDER BY o.embedding <=> $1 LIMIT $6` with the
+// `<= $5` cutoff (internal/memory/store_read.go:266-280), distances computed with pgvector's
+// cosine_distance formula in fp64 from the fp32 master rows.
+//
+// Selection without histograms (packed keys of one query crowd into a handful of exponent
+// bins, which serialises shared-memory atomics): every thread keeps the maximum of its own
+// strided slice of keys; the K2-th largest of those 512 maxima, M, is a lower bound of the
+// true K2-th largest key, so "all keys >= M" is a superset of the top K2 and, for keys in
+// random order, only a few entries larger.  All of them are rescored; every key that is not
+// collected is < M, which is the bound the certificate uses.
+#include "kernels.cuh"
+
+namespace omr {
+
+namespace {
+
+constexpr int kPostThreads = 512;
+constexpr int kCandCap = 384;     // collected keys per query (>= K2, K2 <= 256)
+constexpr int kSortCap = 2048;    // candidates + rescued rows that can be merged in-block
+constexpr int kSuspectCap = 32;   // suspect sub-buckets per query
+
+__device__ __forceinline__ double warp_sum_d(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+struct PostSmem {
+  int32_t lmax[kPostThreads];
+  int32_t ckey[kCandCap];
+  int32_t cidx[kCandCap];
+  int32_t suspects[kSuspectCap];
+  double sd[kSortCap];
+  int32_t sr[kSortCap];
+  int32_t n_cand, n_suspect, n_extra, fail;
+};
+
+__device__ __forceinline__ bool item_less(double da, int32_t ra, double db, int32_t rb) {
+  return da < db || (da == db && ra < rb);
+}
+
+// ascending bitonic sort of (sd, sr)[0, P), P a power of two
+__device__ void sort_items(double* sd, int32_t* sr, int P) {
+  for (int size = 2; size <= P; size <<= 1) {
+    for (int stride = size >> 1; stride > 0; stride >>= 1) {
+      __syncthreads();
+      for (int i = threadIdx.x; i < (P >> 1); i += kPostThreads) {
+        const int lo = 2 * i - (i & (stride - 1)), hi = lo + stride;
+        const bool up = ((lo & size) == 0);
+        const double da = sd[lo], db = sd[hi];
+        const int32_t ra = sr[lo], rb = sr[hi];
+        if (item_less(db, rb, da, ra) == up) {
+          sd[lo] = db; sr[lo] = rb;
+          sd[hi] = da; sr[hi] = ra;
+        }
+      }
+    }
+  }
+  __syncthreads();
+}
+
+// exact cosine distance of one row to the block's query (fp64 copy in shared memory); whole warp.
+// Loads are issued six 16-byte requests at a time per lane before any math, so one row of 1536
+// floats costs two HBM round trips instead of twelve.
+__device__ __forceinline__ double exact_distance(const ShardView& sh, int64_t row, const double* qd, double qn2,
+                                                 int lane) {
+  const float4* m4 = reinterpret_cast<const float4*>(sh.rows_f32 + row * sh.pitch);
+  double acc = 0.0;
+  const int n4 = sh.pitch >> 2;  // a multiple of 16
+  for (int base = 0; base < n4; base += 32 * 6) {
+    float4 a[6];
+#pragma unroll
+    for (int j = 0; j < 6; j++) {
+      const int i = base + j * 32 + lane;
+      a[j] = i < n4 ? __ldg(m4 + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+#pragma unroll
+    for (int j = 0; j < 6; j++) {
+      const int i = base + j * 32 + lane;
+      if (i < n4) {
+        const double* b = qd + 4 * i;
+        acc = fma((double)a[j].x, b[0], acc);
+        acc = fma((double)a[j].y, b[1], acc);
+        acc = fma((double)a[j].z, b[2], acc);
+        acc = fma((double)a[j].w, b[3], acc);
+      }
+    }
+  }
+  acc = warp_sum_d(acc);
+  double s = acc / sqrt(qn2 * sh.norm2[row]);
+  s = s > 1.0 ? 1.0 : (s < -1.0 ? -1.0 : s);
+  const double d = 1.0 - s;
+  return (d == d) ? d : INFINITY;  // NaN (zero-norm query) never ranks
+}
+
+// descending bitonic sort of one value per lane, shuffles only
+__device__ __forceinline__ int32_t warp_sort_desc(int32_t v, int lane) {
+#pragma unroll
+  for (int size = 2; size <= 32; size <<= 1) {
+#pragma unroll
+    for (int stride = size >> 1; stride > 0; stride >>= 1) {
+      const int32_t o = __shfl_xor_sync(0xffffffffu, v, stride);
+      const bool lower = (lane & stride) == 0;           // this lane keeps the "first" element of the pair
+      const bool desc = (lane & size) == 0;              // direction of this bitonic block
+      const bool take_max = lower == desc;
+      v = take_max ? max(v, o) : min(v, o);
+    }
+  }
+  return v;
+}
+
+// ascending (distance, row) sort of one item per lane, shuffles only
+__device__ __forceinline__ void warp_sort_items(double& d, int32_t& r, int lane) {
+#pragma unroll
+  for (int size = 2; size <= 32; size <<= 1) {
+#pragma unroll
+    for (int stride = size >> 1; stride > 0; stride >>= 1) {
+      const double od = __shfl_xor_sync(0xffffffffu, d, stride);
+      const int32_t orr = __shfl_xor_sync(0xffffffffu, r, stride);
+      const bool lower = (lane & stride) == 0;
+      const bool asc = (lane & size) == 0;
+      const bool other_less = od < d || (od == d && orr < r);
+      const bool take_other = (lower == asc) ? other_less : !other_less && !(od == d && orr == r);
+      if (take_other) {
+        d = od;
+        r = orr;
+      }
+    }
+  }
+}
+
+// Exact distances of up to two rows at once: twelve 16-byte loads in flight per lane.
+__device__ __forceinline__ void exact_distance2(const ShardView& sh, int64_t row0, int64_t row1, bool two,
+                                                const double* qd, double qn2, int lane, double& d0, double& d1) {
+  const float4* m0 = reinterpret_cast<const float4*>(sh.rows_f32 + row0 * sh.pitch);
+  const float4* m1 = reinterpret_cast<const float4*>(sh.rows_f32 + row1 * sh.pitch);
+  double a0 = 0.0, a1 = 0.0;
+  const int n4 = sh.pitch >> 2;
+  for (int base = 0; base < n4; base += 32 * 6) {
+    float4 x[6], y[6];
+#pragma unroll
+    for (int j = 0; j < 6; j++) {
+      const int i = base + j * 32 + lane;
+      const bool in = i < n4;
+      x[j] = in ? __ldg(m0 + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+      y[j] = (in && two) ? __ldg(m1 + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+#pragma unroll
+    for (int j = 0; j < 6; j++) {
+      const int i = base + j * 32 + lane;
+      if (i < n4) {
+        const double* b = qd + 4 * i;
+        const double b0 = b[0], b1 = b[1], b2 = b[2], b3 = b[3];
+        a0 = fma((double)x[j].x, b0, a0);
+        a0 = fma((double)x[j].y, b1, a0);
+        a0 = fma((double)x[j].z, b2, a0);
+        a0 = fma((double)x[j].w, b3, a0);
+        a1 = fma((double)y[j].x, b0, a1);
+        a1 = fma((double)y[j].y, b1, a1);
+        a1 = fma((double)y[j].z, b2, a1);
+        a1 = fma((double)y[j].w, b3, a1);
+      }
+    }
+  }
+  a0 = warp_sum_d(a0);
+  a1 = warp_sum_d(a1);
+  auto fin = [&](double acc, int64_t row) {
+    double s = acc / sqrt(qn2 * sh.norm2[row]);
+    s = s > 1.0 ? 1.0 : (s < -1.0 ? -1.0 : s);
+    const double d = 1.0 - s;
+    return (d == d) ? d : INFINITY;
+  };
+  d0 = fin(a0, row0);
+  d1 = two ? fin(a1, row1) : INFINITY;
+}
+
+__global__ void __launch_bounds__(kPostThreads) post_kernel(PostArgs a) {
+  extern __shared__ __align__(16) uint8_t raw[];
+  double* qd = reinterpret_cast<double*>(raw);                       // [pitch]
+  PostSmem& sm = *reinterpret_cast<PostSmem*>(raw + (size_t)a.sh.pitch * sizeof(double));
+  const int q = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  auto stamp = [&](int phase) {
+    if (a.timing && tid == 0) a.timing[(int64_t)q * 8 + phase] = clock64();
+  };
+  stamp(0);
+  const int32_t* keys = a.cand_keys + (int64_t)q * a.keys_per_query;
+  const int64_t kpq = a.keys_per_query;
+
+  for (int i = tid; i < a.sh.pitch; i += kPostThreads)
+    qd[i] = i < a.sh.dim ? (double)a.q[(int64_t)q * a.sh.dim + i] : 0.0;
+  if (tid == 0) {
+    sm.n_cand = 0;
+    sm.n_suspect = 0;
+    sm.n_extra = 0;
+    sm.fail = 0;
+  }
+  // ---- pass 1: per-thread maximum over a strided slice (int4 = 4 keys per load).  A query's key
+  // row starts 8-byte aligned; `head` scalar keys bring the vector body to 16 bytes.
+  const int head = (int)min((int64_t)((4 - (((int64_t)q * kpq) & 3)) & 3), kpq);
+  const int4* k4 = reinterpret_cast<const int4*>(keys + head);
+  const int64_t n4 = (kpq - head) >> 2;
+  const int64_t tail0 = head + (n4 << 2);
+  int32_t lm = kKeyNone;
+  for (int64_t i0 = tid; i0 < n4; i0 += 8 * kPostThreads) {
+    int4 v[8];
+#pragma unroll
+    for (int j = 0; j < 8; j++) {
+      const int64_t i = i0 + (int64_t)j * kPostThreads;
+      v[j] = i < n4 ? __ldg(k4 + i) : make_int4(kKeyNone, kKeyNone, kKeyNone, kKeyNone);
+    }
+#pragma unroll
+    for (int j = 0; j < 8; j++) lm = max(max(lm, v[j].x), max(v[j].y, max(v[j].z, v[j].w)));
+  }
+  if (tid < head) lm = max(lm, keys[tid]);
+  for (int64_t i = tail0 + tid; i < kpq; i += kPostThreads) lm = max(lm, keys[i]);
+  stamp(1);  // pass 1 done
+  if (a.K2 <= 64) {
+    // each warp sorts its 32 maxima with shuffles; warp 0 then pops the K2 largest heads of the
+    // 16 sorted lists (one list per lane) to find the K2-th largest overall
+    sm.lmax[tid] = warp_sort_desc(lm, lane);
+    __syncthreads();
+    if (warp == 0) {
+      int pos = 0;                                  // lanes 0..15: cursor into list `lane`
+      int32_t headv = lane < kPostThreads / 32 ? sm.lmax[lane * 32] : kKeyNone;
+      int32_t kth = kKeyNone;
+      for (int t = 0; t < a.K2; t++) {
+        int32_t best = headv;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) best = max(best, __shfl_xor_sync(0xffffffffu, best, o));
+        kth = best;
+        const unsigned who = __ballot_sync(0xffffffffu, headv == best && lane < kPostThreads / 32);
+        if (best == kKeyNone) break;
+        if (lane == __ffs(who) - 1) {
+          pos++;
+          headv = pos < 32 ? sm.lmax[lane * 32 + pos] : kKeyNone;
+        }
+      }
+      if (lane == 0) sm.lmax[0] = kth;
+    }
+    __syncthreads();
+  } else {
+    sm.lmax[tid] = lm;
+    // descending bitonic sort of the 512 maxima
+    for (int size = 2; size <= kPostThreads; size <<= 1) {
+      for (int stride = size >> 1; stride > 0; stride >>= 1) {
+        __syncthreads();
+        if (tid < (kPostThreads >> 1)) {
+          const int lo = 2 * tid - (tid & (stride - 1)), hi = lo + stride;
+          const bool up = ((lo & size) == 0);
+          const int32_t x = sm.lmax[lo], y = sm.lmax[hi];
+          if ((y > x) == up) {
+            sm.lmax[lo] = y;
+            sm.lmax[hi] = x;
+          }
+        }
+      }
+    }
+    __syncthreads();
+    if (tid == 0) sm.lmax[0] = sm.lmax[a.K2 - 1];
+    __syncthreads();
+  }
+  stamp(2);  // maxima sorted
+  int32_t M = sm.lmax[0];
+  if (M == kKeyNone) M = kKeyNone + 1;  // fewer than K2 threads saw an eligible row: take every valid key
+  // ---- pass 2: collect every key >= M
+  auto collect = [&](int32_t kv, int64_t idx) {
+    if (kv >= M) {
+      const int pos = atomicAdd(&sm.n_cand, 1);
+      if (pos < kCandCap) {
+        sm.ckey[pos] = kv;
+        sm.cidx[pos] = (int32_t)idx;
+      }
+    }
+  };
+  for (int64_t i0 = tid; i0 < n4; i0 += 8 * kPostThreads) {
+    int4 v[8];
+#pragma unroll
+    for (int j = 0; j < 8; j++) {
+      const int64_t i = i0 + (int64_t)j * kPostThreads;
+      v[j] = i < n4 ? __ldg(k4 + i) : make_int4(kKeyNone, kKeyNone, kKeyNone, kKeyNone);
+    }
+#pragma unroll
+    for (int j = 0; j < 8; j++) {
+      const int64_t i = i0 + (int64_t)j * kPostThreads;
+      collect(v[j].x, head + 4 * i);
+      collect(v[j].y, head + 4 * i + 1);
+      collect(v[j].z, head + 4 * i + 2);
+      collect(v[j].w, head + 4 * i + 3);
+    }
+  }
+  if (tid < head) collect(keys[tid], tid);
+  for (int64_t i = tail0 + tid; i < kpq; i += kPostThreads) collect(keys[i], i);
+  __syncthreads();
+  stamp(3);  // pass 2 done
+  const bool overflow = sm.n_cand > kCandCap;
+  int nc = overflow ? kCandCap : sm.n_cand;
+  int P = 1;
+  while (P < nc) P <<= 1;
+  if (P < 2) P = 2;
+  const double qn2 = a.qnorm2[q];
+  // ---- exact rescore: each warp takes candidates c and c + 16 together
+  constexpr int kWarps = kPostThreads / 32;
+  for (int c = warp; c < P; c += 2 * kWarps) {
+    const int c1 = c + kWarps;
+    double d0 = INFINITY, d1 = INFINITY;
+    int32_t r0 = INT32_MAX, r1 = INT32_MAX;
+    if (c < nc) {
+      r0 = (sm.cidx[c] >> 1) * a.S + (sm.ckey[c] & 0xFF);
+      const bool two = c1 < nc;
+      if (two) r1 = (sm.cidx[c1] >> 1) * a.S + (sm.ckey[c1] & 0xFF);
+      exact_distance2(a.sh, r0, two ? r1 : r0, two, qd, qn2, lane, d0, d1);
+    }
+    if (lane == 0) {
+      sm.sd[c] = d0;
+      sm.sr[c] = r0;
+      if (c1 < P) {
+        sm.sd[c1] = d1;
+        sm.sr[c1] = r1;
+      }
+    }
+  }
+  __syncthreads();
+  stamp(4);  // rescored
+  if (P <= 32) {
+    if (warp == 0) {
+      double d = lane < P ? sm.sd[lane] : INFINITY;
+      int32_t r = lane < P ? sm.sr[lane] : INT32_MAX;
+      warp_sort_items(d, r, lane);
+      if (lane < P) {
+        sm.sd[lane] = d;
+        sm.sr[lane] = r;
+      }
+    }
+    __syncthreads();
+  } else {
+    sort_items(sm.sd, sm.sr, P);
+  }
+  const double maxd = a.max_dist ? a.max_dist[q] : INFINITY;
+  int found;
+  {
+    int lo = 0, hi = P < a.k ? P : a.k;
+    while (lo < hi) {
+      const int mid = (lo + hi) >> 1;
+      if (sm.sd[mid] <= maxd && sm.sd[mid] < INFINITY) lo = mid + 1; else hi = mid;
+    }
+    found = lo;
+  }
+  for (int i = tid; i < a.k; i += kPostThreads) {
+    const bool ok = i < found;
+    a.out_rows[(int64_t)q * a.k + i] = ok ? a.row_base + (int64_t)sm.sr[i] * a.row_stride : -1;
+    a.out_dist[(int64_t)q * a.k + i] = ok ? sm.sd[i] : INFINITY;
+  }
+  if (tid == 0) a.out_count[q] = found;
+
+  // ---- certificate (see finalize_kernel in k_select.cu for the argument)
+  double tau;
+  if (found >= a.k) tau = 1.0 - sm.sd[a.k - 1];
+  else if (maxd < INFINITY) tau = 1.0 - maxd;
+  else tau = -INFINITY;
+  const float thr = (float)(tau - (double)a.margin) - 1e-7f;
+  // Every key that was not collected is < M.  If M itself still clears thr, some of those keys
+  // might belong in the answer: top up with every key in [thr, M) and rescore them too.
+  if (tid == 0 && overflow) sm.fail = 1;
+  if (!overflow && M > kKeyNone + 1 && key_score_upper(M) >= thr) {
+    const int nc0 = nc;
+    auto topup = [&](int32_t kv, int64_t idx) {
+      if (kv < M && kv != kKeyNone && key_score_upper(kv) >= thr) {
+        const int pos = atomicAdd(&sm.n_cand, 1);
+        if (pos < kCandCap) {
+          sm.ckey[pos] = kv;
+          sm.cidx[pos] = (int32_t)idx;
+        }
+      }
+    };
+    for (int64_t i = tid; i < n4; i += kPostThreads) {
+      const int4 v = __ldg(k4 + i);
+      topup(v.x, head + 4 * i);
+      topup(v.y, head + 4 * i + 1);
+      topup(v.z, head + 4 * i + 2);
+      topup(v.w, head + 4 * i + 3);
+    }
+    if (tid < head) topup(keys[tid], tid);
+    for (int64_t i = tail0 + tid; i < kpq; i += kPostThreads) topup(keys[i], i);
+    __syncthreads();
+    if (sm.n_cand > kCandCap) {
+      if (tid == 0) sm.fail = 1;
+    } else if (sm.n_cand > nc0) {
+      // append the new rows behind the sorted candidates and sort again (rows are distinct: one key each)
+      const int nc1 = sm.n_cand;
+      for (int c = nc0 + warp; c < nc1; c += kPostThreads / 32) {
+        const int32_t row = (sm.cidx[c] >> 1) * a.S + (sm.ckey[c] & 0xFF);
+        const double d = exact_distance(a.sh, row, qd, qn2, lane);
+        if (lane == 0) {
+          sm.sd[c] = d;
+          sm.sr[c] = row;
+        }
+      }
+      int P1 = 2;
+      while (P1 < nc1) P1 <<= 1;
+      __syncthreads();
+      for (int i = nc1 + tid; i < P1; i += kPostThreads) {
+        sm.sd[i] = INFINITY;
+        sm.sr[i] = INT32_MAX;
+      }
+      sort_items(sm.sd, sm.sr, P1);
+      int lo = 0, hi = P1 < a.k ? P1 : a.k;
+      while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        if (sm.sd[mid] <= maxd && sm.sd[mid] < INFINITY) lo = mid + 1; else hi = mid;
+      }
+      found = lo;
+      for (int i = tid; i < a.k; i += kPostThreads) {
+        const bool ok = i < found;
+        a.out_rows[(int64_t)q * a.k + i] = ok ? a.row_base + (int64_t)sm.sr[i] * a.row_stride : -1;
+        a.out_dist[(int64_t)q * a.k + i] = ok ? sm.sd[i] : INFINITY;
+      }
+      if (tid == 0) a.out_count[q] = found;
+      nc = nc1;
+    }
+  }
+  stamp(5);  // sorted, written, topped up
+  const int64_t nsb = kpq >> 1;
+  for (int64_t sb = tid; sb < nsb; sb += kPostThreads) {
+    const int32_t k2 = keys[2 * sb + 1];
+    if (k2 != kKeyNone && key_score_upper(k2) >= thr) {
+      const int pos = atomicAdd(&sm.n_suspect, 1);
+      if (pos < kSuspectCap) sm.suspects[pos] = (int32_t)sb;
+    }
+  }
+  __syncthreads();
+  stamp(6);  // certificate pass done
+  const int nsus = sm.n_suspect;
+  if (nsus > kSuspectCap) {
+    if (tid == 0) sm.fail = 1;
+  } else if (nsus > 0) {
+    // ---- rescue: rescore every eligible row of each suspect sub-bucket, merge, re-emit
+    const uint32_t* bm = a.bitmaps + (int64_t)(a.query_group ? a.query_group[q] : 0) * a.words_per_group;
+    const int total = nsus * a.S;
+    for (int t = tid; t < total; t += kPostThreads) {   // list the eligible rows first ...
+      const int64_t row = (int64_t)sm.suspects[t / a.S] * a.S + (t % a.S);
+      if ((bm[row >> 5] >> (row & 31)) & 1u) {
+        const int pos = nc + atomicAdd(&sm.n_extra, 1);
+        if (pos < kSortCap) sm.sr[pos] = (int32_t)row;
+      }
+    }
+    __syncthreads();
+    const int ne = sm.n_extra;
+    if (nc + ne > kSortCap) {
+      if (tid == 0) sm.fail = 1;
+    } else {
+      for (int c = nc + warp; c < nc + ne; c += 2 * kWarps) {   // ... then rescore them two per warp
+        const int c1 = c + kWarps;
+        const bool two = c1 < nc + ne;
+        double d0, d1;
+        exact_distance2(a.sh, sm.sr[c], two ? sm.sr[c1] : sm.sr[c], two, qd, qn2, lane, d0, d1);
+        if (lane == 0) {
+          sm.sd[c] = d0;
+          if (two) sm.sd[c1] = d1;
+        }
+      }
+      __syncthreads();
+      int P2 = 2;
+      while (P2 < nc + ne) P2 <<= 1;
+      // the first nc entries are the sorted candidates, but sorting moved padding inside [0, P):
+      // after sort_items the real entries are the first nc (padding sorts last), so this layout holds
+      for (int i = nc + ne + tid; i < P2; i += kPostThreads) {
+        sm.sd[i] = INFINITY;
+        sm.sr[i] = INT32_MAX;
+      }
+      sort_items(sm.sd, sm.sr, P2);
+      if (tid == 0) {
+        int f2 = 0;
+        int32_t prev = -1;
+        for (int i = 0; i < P2 && f2 < a.k; i++) {
+          if (!(sm.sd[i] <= maxd) || !(sm.sd[i] < INFINITY)) break;
+          if (sm.sr[i] == prev) continue;  // a suspect sub-bucket's keyed rows appear twice
+          prev = sm.sr[i];
+          a.out_rows[(int64_t)q * a.k + f2] = a.row_base + (int64_t)sm.sr[i] * a.row_stride;
+          a.out_dist[(int64_t)q * a.k + f2] = sm.sd[i];
+          f2++;
+        }
+        a.out_count[q] = f2;
+        for (int i = f2; i < a.k; i++) {
+          a.out_rows[(int64_t)q * a.k + i] = -1;
+          a.out_dist[(int64_t)q * a.k + i] = INFINITY;
+        }
+        atomicAdd(a.rescued_total, ne);
+      }
+    }
+  }
+  __syncthreads();
+  stamp(7);
+  if (tid == 0 && sm.fail) a.fail_list[atomicAdd(a.fail_count, 1)] = q;
+}
+
+}  // namespace
+
+bool post_fused_supported(int K2, int k) { return K2 <= 256 && k <= 256; }
+
+int launch_post(const PostArgs& a, cudaStream_t st) {
+  if (a.nq <= 0) return 0;
+  const size_t smem = (size_t)a.sh.pitch * sizeof(double) + sizeof(PostSmem);
+  static bool attr_done = false;
+  if (smem > 48 * 1024 && !attr_done) {
+    OMR_CUDA_OK(cudaFuncSetAttribute(post_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+    attr_done = true;
+  }
+  post_kernel<<<a.nq, kPostThreads, smem, st>>>(a);
+  OMR_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+}  // namespace omr

@@ -121,6 +121,7 @@ struct KernelArgs {
   int n_b_tiles;   // 256-row tiles of the store
   int64_t n_work;  // total (a tile, b tile) work items
   int k_blocks;
+  int nq;          // real queries; tiles are padded with zero queries beyond it
   // recall
   const uint32_t* bitmaps;
   int words_per_group;
@@ -247,7 +248,7 @@ __global__ void __launch_bounds__(kNumThreads, 1)
       const uint32_t as = it & 1, aphase = (it >> 1) & 1;
       if (!kSelfJoin) {
         const int q = a_tile * kQueryTile + t_local;
-        const int g = args.query_group ? __ldg(args.query_group + q) : 0;
+        const int g = (args.query_group && q < args.nq) ? __ldg(args.query_group + q) : 0;
         te.bitmap_row = args.bitmaps + (int64_t)g * args.words_per_group;
         te.out = args.cand_keys + (int64_t)q * args.keys_per_query;
         te.begin_tile();
@@ -260,6 +261,7 @@ __global__ void __launch_bounds__(kNumThreads, 1)
 #pragma unroll 1
       for (int c = 0; c < kTileRows / 32; c += 2) {
         uint32_t v0[32], v1[32];
+        __syncwarp();  // the epilogue's data-dependent branches must reconverge before a .sync.aligned load
         ptx::tmem_ld_32x32(lane_addr + as * kTileRows + c * 32, v0);
         ptx::tmem_ld_32x32(lane_addr + as * kTileRows + (c + 1) * 32, v1);
         ptx::tmem_ld_wait();
@@ -281,8 +283,174 @@ __global__ void __launch_bounds__(kNumThreads, 1)
   if (warp == 2) ptx::tmem_dealloc(tmem_base, kTmemCols);
 }
 
+// ---------------------------------------------------------------------------------------
+// 2-CTA variant of the recall scorer.  A cluster of two CTAs (one TPC) works on a 256-query x
+// 256-row tile: each CTA loads ITS 128 queries (A) and ITS half of the 256 rows (B), the leader
+// issues one M=256 tcgen05.mma.cta_group::2 per K step, and each CTA's epilogue drains its own
+// 128 TMEM lanes.  Per SM and K block this moves 32 KB through L2->smem instead of 48 KB, and
+// the smaller stage allows a 6-deep TMA pipeline.
+constexpr int kStages2 = 6;
+constexpr int kHalfBBytes = (kTileRows / 2) * kBlockK * 2;  // 16 KB
+constexpr int kStageBytes2 = kABytes + kHalfBBytes;         // 32 KB per CTA
+struct __align__(8) PipeBarriers2 {
+  uint64_t full[kStages2];
+  uint64_t empty[kStages2];
+  uint64_t tmem_full[2];
+  uint64_t tmem_empty[2];
+  uint32_t tmem_base;
+};
+constexpr int kSmemBytes2 = kStages2 * kStageBytes2 + (int)sizeof(PipeBarriers2) + 1024;
+
 template <int S>
-int launch_recall_s(const CUtensorMap& tmap_q, const CUtensorMap& tmap_rows, int n_qtiles, int n_tiles, int k_blocks,
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kNumThreads, 1)
+    score_umma2_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_rows,
+                       const KernelArgs<false, S> args) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem_a = smem;
+  uint8_t* smem_b = smem + kStages2 * kABytes;
+  PipeBarriers2* bars = reinterpret_cast<PipeBarriers2*>(smem + kStages2 * kStageBytes2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = ptx::cluster_ctarank();
+  const bool leader = rank == 0;
+  const int64_t cluster = ptx::cluster_id_x(), n_clusters = ptx::cluster_nctaid_x();
+
+  ptx::cluster_sync_all();  // both CTAs resident before the paired TMEM allocation
+  if (warp == 0 && lane == 0) {
+    ptx::tma_prefetch_desc(&tmap_q);
+    ptx::tma_prefetch_desc(&tmap_rows);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int i = 0; i < kStages2; i++) {
+      ptx::mbar_init(&bars->full[i], 2);    // both CTAs' producers arrive on the leader's barrier
+      ptx::mbar_init(&bars->empty[i], 1);   // multicast commit arrives in each CTA
+    }
+    for (int i = 0; i < 2; i++) {
+      ptx::mbar_init(&bars->tmem_full[i], 1);
+      ptx::mbar_init(&bars->tmem_empty[i], 256);  // the epilogue threads of both CTAs (leader's copy is used)
+    }
+    ptx::fence_barrier_init();
+  }
+  if (warp == 2) ptx::tmem_alloc_2sm(&bars->tmem_base, kTmemCols);
+  ptx::tc_fence_before_sync();
+  ptx::cluster_sync_all();
+  ptx::tc_fence_after_sync();
+  const uint32_t tmem_base = bars->tmem_base;
+
+  if (warp == 0) {
+    // ---------------- TMA producer (one per CTA) ----------------
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int64_t w = cluster; w < args.n_work; w += n_clusters) {
+        const int b_tile = (int)(w / args.n_a_tiles), a_tile = (int)(w % args.n_a_tiles);
+        for (int kb = 0; kb < args.k_blocks; kb++) {
+          ptx::mbar_wait(&bars->empty[stage], phase ^ 1);
+          if (leader) ptx::mbar_arrive_expect_tx(&bars->full[stage], 2 * kStageBytes2);
+          else ptx::mbar_arrive_cluster(&bars->full[stage], 0);
+          ptx::tma_load_2d_2sm(smem_a + stage * kABytes, &tmap_q, &bars->full[stage], kb * kBlockK,
+                               a_tile * 2 * kQueryTile + (int)rank * kQueryTile, ptx::kEvictLast);
+          ptx::tma_load_2d_2sm(smem_b + stage * kHalfBBytes, &tmap_rows, &bars->full[stage], kb * kBlockK,
+                               b_tile * kTileRows + (int)rank * (kTileRows / 2), ptx::kEvictNormal);
+          if (++stage == kStages2) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+      }
+    }
+  } else if (warp == 1 && leader) {
+    // ---------------- MMA issuer (leader CTA only) ----------------
+    constexpr uint32_t idesc = ptx::make_idesc_bf16(2 * kQueryTile, kTileRows);
+    int stage = 0;
+    uint32_t phase = 0, it = 0;
+    for (int64_t w = cluster; w < args.n_work; w += n_clusters, it++) {
+      const uint32_t as = it & 1, aphase = (it >> 1) & 1;
+      ptx::mbar_wait(&bars->tmem_empty[as], aphase ^ 1);
+      ptx::tc_fence_after_sync();
+      for (int kb = 0; kb < args.k_blocks; kb++) {
+        ptx::mbar_wait(&bars->full[stage], phase);
+        ptx::tc_fence_after_sync();
+        if (lane == 0) {
+          const uint64_t da = ptx::make_smem_desc_sw128(ptx::smem_u32(smem_a + stage * kABytes));
+          const uint64_t db = ptx::make_smem_desc_sw128(ptx::smem_u32(smem_b + stage * kHalfBBytes));
+#pragma unroll
+          for (int k = 0; k < kBlockK / 16; k++)
+            ptx::umma_bf16_2sm(tmem_base + as * kTileRows, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
+          ptx::umma_commit_2sm(&bars->empty[stage]);
+          if (kb == args.k_blocks - 1) ptx::umma_commit_2sm(&bars->tmem_full[as]);
+        }
+        __syncwarp();
+        if (++stage == kStages2) {
+          stage = 0;
+          phase ^= 1;
+        }
+      }
+    }
+  } else if (warp >= kEpilogueWarp0) {
+    // ---------------- epilogue (both CTAs, own TMEM lanes) ----------------
+    const int quarter = warp & 3;
+    const int t_local = quarter * 32 + lane;
+    const uint32_t lane_addr = tmem_base + ((uint32_t)(quarter * 32) << 16);
+    uint32_t it = 0;
+    Top2Epilogue<S> te;
+    for (int64_t w = cluster; w < args.n_work; w += n_clusters, it++) {
+      const int b_tile = (int)(w / args.n_a_tiles), a_tile = (int)(w % args.n_a_tiles);
+      const uint32_t as = it & 1, aphase = (it >> 1) & 1;
+      const int q = a_tile * 2 * kQueryTile + (int)rank * kQueryTile + t_local;
+      const int g = (args.query_group && q < args.nq) ? __ldg(args.query_group + q) : 0;
+      te.bitmap_row = args.bitmaps + (int64_t)g * args.words_per_group;
+      te.out = args.cand_keys + (int64_t)q * args.keys_per_query;
+      te.begin_tile();
+      ptx::mbar_wait(&bars->tmem_full[as], aphase);
+      ptx::tc_fence_after_sync();
+#pragma unroll 1
+      for (int c = 0; c < kTileRows / 32; c += 2) {
+        uint32_t v0[32], v1[32];
+        __syncwarp();
+        ptx::tmem_ld_32x32(lane_addr + as * kTileRows + c * 32, v0);
+        ptx::tmem_ld_32x32(lane_addr + as * kTileRows + (c + 1) * 32, v1);
+        ptx::tmem_ld_wait();
+        te.chunk(b_tile, c, v0);
+        te.chunk(b_tile, c + 1, v1);
+      }
+      ptx::tc_fence_before_sync();
+      ptx::mbar_arrive_cluster(&bars->tmem_empty[as], 0);
+    }
+  }
+
+  ptx::tc_fence_before_sync();
+  ptx::cluster_sync_all();
+  if (warp == 2) ptx::tmem_dealloc_2sm(tmem_base, kTmemCols);
+}
+
+template <int S>
+int launch_recall2_s(const CUtensorMap& tmap_q, const CUtensorMap& tmap_rows_half, int nq, int n_qtiles256, int n_tiles,
+                     int k_blocks, const uint32_t* bitmaps, int words_per_group, const int32_t* query_group,
+                     int32_t* cand_keys, int num_sms, cudaStream_t st) {
+  KernelArgs<false, S> a{};
+  a.n_a_tiles = n_qtiles256;
+  a.n_b_tiles = n_tiles;
+  a.n_work = (int64_t)n_qtiles256 * n_tiles;
+  a.k_blocks = k_blocks;
+  a.nq = nq;
+  a.bitmaps = bitmaps;
+  a.words_per_group = words_per_group;
+  a.query_group = query_group;
+  a.cand_keys = cand_keys;
+  a.keys_per_query = (int64_t)n_tiles * (kTileRows / S) * 2;
+  auto kern = score_umma2_kernel<S>;
+  OMR_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes2));
+  int64_t clusters = num_sms / 2;
+  if (clusters > a.n_work) clusters = a.n_work;
+  kern<<<(unsigned)(2 * clusters), kNumThreads, kSmemBytes2, st>>>(tmap_q, tmap_rows_half, a);
+  OMR_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+template <int S>
+int launch_recall_s(const CUtensorMap& tmap_q, const CUtensorMap& tmap_rows, int nq, int n_qtiles, int n_tiles, int k_blocks,
                     const uint32_t* bitmaps, int words_per_group, const int32_t* query_group, int32_t* cand_keys,
                     int num_sms, cudaStream_t st) {
   KernelArgs<false, S> a{};
@@ -290,6 +458,7 @@ int launch_recall_s(const CUtensorMap& tmap_q, const CUtensorMap& tmap_rows, int
   a.n_b_tiles = n_tiles;
   a.n_work = (int64_t)n_qtiles * n_tiles;
   a.k_blocks = k_blocks;
+  a.nq = nq;
   a.bitmaps = bitmaps;
   a.words_per_group = words_per_group;
   a.query_group = query_group;
@@ -308,15 +477,29 @@ int launch_recall_s(const CUtensorMap& tmap_q, const CUtensorMap& tmap_rows, int
 
 int score_umma_smem_bytes() { return kSmemBytes; }
 
-int launch_score_umma(const CUtensorMap& tmap_q, const CUtensorMap& tmap_rows, int n_qtiles, int n_tiles,
+int launch_score_umma(const CUtensorMap& tmap_q, const CUtensorMap& tmap_rows, int nq, int n_qtiles, int n_tiles,
                       int k_blocks, int S, const uint32_t* bitmaps, int words_per_group,
                       const int32_t* query_group, int32_t* cand_keys, int num_sms, cudaStream_t st) {
   if (n_qtiles <= 0 || n_tiles <= 0) return 0;
   switch (S) {
-    case 32: return launch_recall_s<32>(tmap_q, tmap_rows, n_qtiles, n_tiles, k_blocks, bitmaps, words_per_group, query_group, cand_keys, num_sms, st);
-    case 64: return launch_recall_s<64>(tmap_q, tmap_rows, n_qtiles, n_tiles, k_blocks, bitmaps, words_per_group, query_group, cand_keys, num_sms, st);
-    case 128: return launch_recall_s<128>(tmap_q, tmap_rows, n_qtiles, n_tiles, k_blocks, bitmaps, words_per_group, query_group, cand_keys, num_sms, st);
-    case 256: return launch_recall_s<256>(tmap_q, tmap_rows, n_qtiles, n_tiles, k_blocks, bitmaps, words_per_group, query_group, cand_keys, num_sms, st);
+    case 32: return launch_recall_s<32>(tmap_q, tmap_rows, nq, n_qtiles, n_tiles, k_blocks, bitmaps, words_per_group, query_group, cand_keys, num_sms, st);
+    case 64: return launch_recall_s<64>(tmap_q, tmap_rows, nq, n_qtiles, n_tiles, k_blocks, bitmaps, words_per_group, query_group, cand_keys, num_sms, st);
+    case 128: return launch_recall_s<128>(tmap_q, tmap_rows, nq, n_qtiles, n_tiles, k_blocks, bitmaps, words_per_group, query_group, cand_keys, num_sms, st);
+    case 256: return launch_recall_s<256>(tmap_q, tmap_rows, nq, n_qtiles, n_tiles, k_blocks, bitmaps, words_per_group, query_group, cand_keys, num_sms, st);
+  }
+  return fail_msg(-2, "sub-bucket size must be 32, 64, 128 or 256, got %d", S);
+}
+
+// tmap_rows_half: the row matrix with a 128-row box (each CTA of a pair loads half a row tile).
+int launch_score_umma2(const CUtensorMap& tmap_q, const CUtensorMap& tmap_rows_half, int nq, int n_qtiles256, int n_tiles,
+                       int k_blocks, int S, const uint32_t* bitmaps, int words_per_group,
+                       const int32_t* query_group, int32_t* cand_keys, int num_sms, cudaStream_t st) {
+  if (n_qtiles256 <= 0 || n_tiles <= 0) return 0;
+  switch (S) {
+    case 32: return launch_recall2_s<32>(tmap_q, tmap_rows_half, nq, n_qtiles256, n_tiles, k_blocks, bitmaps, words_per_group, query_group, cand_keys, num_sms, st);
+    case 64: return launch_recall2_s<64>(tmap_q, tmap_rows_half, nq, n_qtiles256, n_tiles, k_blocks, bitmaps, words_per_group, query_group, cand_keys, num_sms, st);
+    case 128: return launch_recall2_s<128>(tmap_q, tmap_rows_half, nq, n_qtiles256, n_tiles, k_blocks, bitmaps, words_per_group, query_group, cand_keys, num_sms, st);
+    case 256: return launch_recall2_s<256>(tmap_q, tmap_rows_half, nq, n_qtiles256, n_tiles, k_blocks, bitmaps, words_per_group, query_group, cand_keys, num_sms, st);
   }
   return fail_msg(-2, "sub-bucket size must be 32, 64, 128 or 256, got %d", S);
 }

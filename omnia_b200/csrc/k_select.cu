@@ -426,7 +426,8 @@ __global__ void __launch_bounds__(1024) select_exact_kernel(const double* __rest
 
 __global__ void __launch_bounds__(256) merge_topk_kernel(const int64_t* __restrict__ in_rows,
                                                          const double* __restrict__ in_dist, int G, int nq, int k,
-                                                         int P, int64_t* __restrict__ out_rows,
+                                                         int64_t shard_stride, int P,
+                                                         int64_t* __restrict__ out_rows,
                                                          double* __restrict__ out_dist,
                                                          int32_t* __restrict__ out_count) {
   extern __shared__ __align__(16) uint8_t msm[];
@@ -438,8 +439,8 @@ __global__ void __launch_bounds__(256) merge_topk_kernel(const int64_t* __restri
     double d = INFINITY;
     if (i < G * k) {
       const int g = i / k, j = i % k;
-      r = in_rows[((int64_t)g * nq + q) * k + j];
-      d = in_dist[((int64_t)g * nq + q) * k + j];
+      r = in_rows[(int64_t)g * shard_stride + (int64_t)q * k + j];
+      d = in_dist[(int64_t)g * shard_stride + (int64_t)q * k + j];
     }
     sd[i] = r >= 0 ? d : INFINITY;
     sr[i] = r >= 0 ? r : INT64_MAX;
@@ -626,15 +627,16 @@ int launch_select_exact(const double* dist, int64_t n, const int32_t* slot_query
   return 0;
 }
 
-int launch_merge_topk(const int64_t* in_rows, const double* in_dist, int G, int nq, int k, int64_t* out_rows,
-                      double* out_dist, int32_t* out_count, cudaStream_t st) {
+int launch_merge_topk(const int64_t* in_rows, const double* in_dist, int G, int nq, int k, int64_t shard_stride,
+                      int64_t* out_rows, double* out_dist, int32_t* out_count, cudaStream_t st) {
   if (nq <= 0) return 0;
   const int P = pow2ceil(G * k);
   const size_t smem = (size_t)P * 16;
   if (smem > 200 * 1024) return fail_msg(-2, "merge of %d shards x k=%d exceeds the 12800-entry limit", G, k);
   if (smem > 48 * 1024)
     OMR_CUDA_OK(cudaFuncSetAttribute(merge_topk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  merge_topk_kernel<<<nq, 256, smem, st>>>(in_rows, in_dist, G, nq, k, P, out_rows, out_dist, out_count);
+  if (shard_stride <= 0) shard_stride = (int64_t)nq * k;
+  merge_topk_kernel<<<nq, 256, smem, st>>>(in_rows, in_dist, G, nq, k, shard_stride, P, out_rows, out_dist, out_count);
   OMR_CUDA_OK(cudaGetLastError());
   return 0;
 }

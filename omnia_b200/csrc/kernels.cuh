@@ -21,9 +21,12 @@ int launch_build_bitmaps(RowMetaView meta, int64_t n, int words_per_group, const
 int launch_score_stream(const ShardView& sh, const __nv_bfloat16* qn, int nq, int n_tiles, int S,
                         const uint32_t* bitmaps, int words_per_group, const int32_t* query_group,
                         int32_t* cand_keys, int num_sms, cudaStream_t st);
-int launch_score_umma(const CUtensorMap& tmap_q, const CUtensorMap& tmap_rows, int n_qtiles, int n_tiles,
+int launch_score_umma(const CUtensorMap& tmap_q, const CUtensorMap& tmap_rows, int nq, int n_qtiles, int n_tiles,
                       int k_blocks, int S, const uint32_t* bitmaps, int words_per_group,
                       const int32_t* query_group, int32_t* cand_keys, int num_sms, cudaStream_t st);
+int launch_score_umma2(const CUtensorMap& tmap_q, const CUtensorMap& tmap_rows_half, int nq, int n_qtiles256, int n_tiles,
+                       int k_blocks, int S, const uint32_t* bitmaps, int words_per_group,
+                       const int32_t* query_group, int32_t* cand_keys, int num_sms, cudaStream_t st);
 int score_umma_smem_bytes();
 
 // ---- select / exact rescore / finalize (k_select.cu) -------------------------
@@ -66,6 +69,32 @@ struct FinalizeArgs {
 int launch_finalize(const FinalizeArgs& a, cudaStream_t st);
 int launch_finalize_extra(const FinalizeArgs& a, cudaStream_t st);
 
+// Fused replacement of select_keys -> rescore -> finalize -> rescore_items -> finalize_extra
+// (k_post.cu): one block per query, no intermediate global buffers.  K2 <= 256.
+struct PostArgs {
+  ShardView sh;
+  const float* q = nullptr;            // [nq][dim] fp32 queries as given
+  const double* qnorm2 = nullptr;
+  const int32_t* cand_keys = nullptr;
+  int64_t keys_per_query = 0;
+  int nq = 0, S = 256, K2 = 32, k = 10;
+  const double* max_dist = nullptr;
+  float margin = 0.0f;
+  const uint32_t* bitmaps = nullptr;
+  int words_per_group = 0;
+  const int32_t* query_group = nullptr;
+  int64_t row_base = 0, row_stride = 1;
+  int64_t* out_rows = nullptr;
+  double* out_dist = nullptr;
+  int32_t* out_count = nullptr;
+  int32_t* fail_list = nullptr;
+  int32_t* fail_count = nullptr;
+  int32_t* rescued_total = nullptr;
+  long long* timing = nullptr;          // optional [nq][8] clock64 stamps per phase (diagnostics)
+};
+bool post_fused_supported(int K2, int k);
+int launch_post(const PostArgs& a, cudaStream_t st);
+
 // Exact fallback: distances of `nslots` queries (indices in slot_query) to every row.
 int launch_exact_scan(const ShardView& sh, const float* q, const double* qnorm2, const int32_t* slot_query,
                       int nslots, const uint32_t* bitmaps, int words_per_group, const int32_t* query_group,
@@ -74,8 +103,8 @@ int launch_select_exact(const double* dist, int64_t n, const int32_t* slot_query
                         int32_t* sel_rows, double* sel_dist, cudaStream_t st);
 
 // Multi-GPU: merge G gathered per-shard results [G][nq][k] into [nq][k].
-int launch_merge_topk(const int64_t* in_rows, const double* in_dist, int G, int nq, int k, int64_t* out_rows,
-                      double* out_dist, int32_t* out_count, cudaStream_t st);
+int launch_merge_topk(const int64_t* in_rows, const double* in_dist, int G, int nq, int k, int64_t shard_stride,
+                      int64_t* out_rows, double* out_dist, int32_t* out_count, cudaStream_t st);
 
 // ---- near-duplicate self-join (k_score_umma.cu / k_select.cu) ----------------
 struct PairCand {

@@ -198,6 +198,9 @@ struct omr_store {
   size_t tmap_q_rows = 0;
   const void* tmap_q_ptr = nullptr;
   bool live_dirty = true;
+  bool post_timing = false;  // OMR_POST_TIMING=1: per-phase clock stamps of the fused post kernel
+  DevBuf<long long> w_timing;
+  bool legacy_post = false;  // OMR_LEGACY_POST=1: use the unfused select/rescore/finalize chain
 
   std::atomic<int64_t> st_launches{0}, st_searches{0}, st_queries{0}, st_rescued{0}, st_fallback{0};
   // optional device timing of the dominant kernel (the approximate scorer), for bench.py's roofline
@@ -423,20 +426,33 @@ int omr_store::device_search(const float* d_q, int nq, const uint32_t* d_bitmaps
   int K2 = cfg.rescore_width > 0 ? cfg.rescore_width : pow2ceil_i(std::max(32, 2 * k));
   K2 = std::min(std::max(K2, k), 4096);
   const int K2x = K2 + kExtraSlots;
-  int S = cfg.sub_bucket > 0 ? cfg.sub_bucket : (k <= 32 ? 256 : (k <= 128 ? 64 : 32));
-  int path = cfg.force_path > 0 ? cfg.force_path : (nq <= 8 ? 1 : 2);
-  const int qpad = path == 2 ? ((nq + kQueryTile - 1) / kQueryTile) * kQueryTile : std::max(nq, 8);
+  int S = cfg.sub_bucket > 0 ? cfg.sub_bucket : (k <= 32 ? 128 : (k <= 128 ? 64 : 32));
+  // Measured on B200 (profiles/r01_configs_single_gpu.jsonl): the TMA-fed tensor-core scorer streams the
+  // matrix at ~6.7 TB/s for any batch up to ~128 queries, above the LDG-based streaming scorer for
+  // every batch but a single query.
+  int path = cfg.force_path > 0 ? cfg.force_path : (nq <= 1 ? 1 : 2);
+  // Expected rescued rows per query ~ k^2 S^2 / (2n).  When even the smallest sub-bucket cannot keep
+  // that small (large k on a small store), the two-stage scheme has nothing to offer: scan exactly.
+  if (cfg.sub_bucket == 0 && path != 3) {
+    while (S > 32 && (double)k * k * S * S / (2.0 * (double)n) > 256.0) S >>= 1;
+    if (cfg.force_path == 0 && (double)k * k * S * S / (2.0 * (double)n) > 256.0) path = 3;
+  }
+  const int qtile = path == 4 ? 2 * kQueryTile : kQueryTile;
+  const int qpad = (path == 2 || path == 4) ? ((nq + qtile - 1) / qtile) * qtile : std::max(nq, 8);
   const int64_t kpq = (int64_t)n_tiles * (kTileRows / S) * 2;
   last_path = path; last_S = S; last_K2 = K2;
 
+  const bool fused = path != 3 && !legacy_post && post_fused_supported(K2, k);
   if ((rc = w_qn.reserve((size_t)qpad * pitch))) return rc;
   if ((rc = w_qnorm2.reserve((size_t)qpad))) return rc;
-  if ((rc = w_sel_rows.reserve((size_t)qpad * K2x))) return rc;
-  if ((rc = w_sel_dist.reserve((size_t)qpad * K2x))) return rc;
-  if ((rc = w_sel_bound.reserve((size_t)qpad))) return rc;
-  if ((rc = w_extra_cnt.reserve((size_t)qpad))) return rc;
-  if ((rc = w_extra_items.reserve((size_t)qpad * kExtraSlots))) return rc;
   if ((rc = w_fail_list.reserve((size_t)qpad))) return rc;
+  if ((rc = w_extra_cnt.reserve((size_t)qpad))) return rc;
+  if (!fused) {
+    if ((rc = w_sel_rows.reserve((size_t)qpad * K2x))) return rc;
+    if ((rc = w_sel_dist.reserve((size_t)qpad * K2x))) return rc;
+    if ((rc = w_sel_bound.reserve((size_t)qpad))) return rc;
+    if ((rc = w_extra_items.reserve((size_t)qpad * kExtraSlots))) return rc;
+  }
   if (path != 3 && (rc = w_cand.reserve((size_t)qpad * kpq))) return rc;
 
   OMR_CUDA_OK(cudaMemsetAsync(w_counters.p, 0, 4 * sizeof(int32_t), st));
@@ -483,20 +499,41 @@ int omr_store::device_search(const float* d_q, int nq, const uint32_t* d_bitmaps
         tmap_q_ptr = w_qn.p;
         tmap_q_rows = w_qn.n / pitch;
       }
-      rc = launch_score_umma(tmap_q, tmap_rows_b, qpad / kQueryTile, n_tiles, pitch / kBlockK, S, d_bitmaps, wpg,
-                             d_qgroup, w_cand.p, num_sms, st);
+      if (path == 4)
+        rc = launch_score_umma2(tmap_q, tmap_rows_a, nq, qpad / (2 * kQueryTile), n_tiles, pitch / kBlockK, S, d_bitmaps, wpg,
+                                d_qgroup, w_cand.p, num_sms, st);
+      else
+        rc = launch_score_umma(tmap_q, tmap_rows_b, nq, qpad / kQueryTile, n_tiles, pitch / kBlockK, S, d_bitmaps, wpg,
+                               d_qgroup, w_cand.p, num_sms, st);
       if (rc) return rc;
       st_launches++;
     }
     if (profiling) OMR_CUDA_OK(cudaEventRecord(ev1, st));
-    if ((rc = launch_select_keys(w_cand.p, nq, kpq, S, K2, K2x, w_sel_rows.p, w_sel_bound.p, st))) return rc;
-    if ((rc = launch_rescore(sh, d_q, w_qnorm2.p, nq, K2, K2x, w_sel_rows.p, w_sel_dist.p, st))) return rc;
-    if ((rc = launch_finalize(fa, st))) return rc;
-    if ((rc = launch_rescore_items(sh, d_q, w_qnorm2.p, K2x, w_extra_items.p, extra_total, w_sel_rows.p, w_sel_dist.p,
-                                   num_sms, st)))
-      return rc;
-    if ((rc = launch_finalize_extra(fa, st))) return rc;
-    st_launches += 5;
+    if (fused) {
+      PostArgs pa;
+      pa.sh = sh; pa.q = d_q; pa.qnorm2 = w_qnorm2.p; pa.cand_keys = w_cand.p; pa.keys_per_query = kpq;
+      // the fused kernel tops its candidate list up adaptively, so its first pass can be narrow
+      pa.nq = nq; pa.S = S; pa.K2 = cfg.rescore_width > 0 ? K2 : std::min(K2, std::max(16, k + 6)); pa.k = k; pa.max_dist = d_maxdist; pa.margin = margin;
+      pa.bitmaps = d_bitmaps; pa.words_per_group = wpg; pa.query_group = d_qgroup;
+      pa.row_base = cfg.row_base; pa.row_stride = cfg.row_stride;
+      pa.out_rows = d_rows; pa.out_dist = d_dist; pa.out_count = d_count;
+      pa.fail_list = w_fail_list.p; pa.fail_count = fail_count; pa.rescued_total = extra_total;
+      if (post_timing) {
+        if ((rc = w_timing.reserve((size_t)qpad * 8))) return rc;
+        pa.timing = w_timing.p;
+      }
+      if ((rc = launch_post(pa, st))) return rc;
+      st_launches += 1;
+    } else {
+      if ((rc = launch_select_keys(w_cand.p, nq, kpq, S, K2, K2x, w_sel_rows.p, w_sel_bound.p, st))) return rc;
+      if ((rc = launch_rescore(sh, d_q, w_qnorm2.p, nq, K2, K2x, w_sel_rows.p, w_sel_dist.p, st))) return rc;
+      if ((rc = launch_finalize(fa, st))) return rc;
+      if ((rc = launch_rescore_items(sh, d_q, w_qnorm2.p, K2x, w_extra_items.p, extra_total, w_sel_rows.p, w_sel_dist.p,
+                                     num_sms, st)))
+        return rc;
+      if ((rc = launch_finalize_extra(fa, st))) return rc;
+      st_launches += 5;
+    }
     OMR_CUDA_OK(cudaMemcpyAsync(pin_counters.p, w_counters.p, 2 * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
     OMR_CUDA_OK(cudaStreamSynchronize(st));
     st_rescued += pin_counters.p[0];
@@ -511,6 +548,10 @@ int omr_store::device_search(const float* d_q, int nq, const uint32_t* d_bitmaps
   if (nfail > 0) {
     // Exact fallback: score every eligible row of the failing queries in fp64.
     st_fallback += nfail;
+    if ((rc = w_sel_rows.reserve((size_t)qpad * K2x))) return rc;   // the fallback's tail uses the candidate-slot layout
+    if ((rc = w_sel_dist.reserve((size_t)qpad * K2x))) return rc;
+    fa.sel_rows = w_sel_rows.p;
+    fa.sel_dist = w_sel_dist.p;
     const int64_t n_pad = (int64_t)wpg * 32;
     const int slots = (int)std::max<int64_t>(1, std::min<int64_t>(nfail, (int64_t)(256u << 20) / (n_pad * 8)));
     if ((rc = w_exact.reserve((size_t)slots * n_pad))) return rc;
@@ -636,6 +677,8 @@ int omr_open(const omr_config* cfg, omr_store** out) {
     return fail_msg(OMR_E_CAPACITY, "memory: a shard holds at most 2^31 rows");
   }
   s->margin = cfg->candidate_margin > 0 ? cfg->candidate_margin : 1e-3f;
+  if (const char* e = getenv("OMR_LEGACY_POST")) s->legacy_post = e[0] == '1';
+  if (const char* e = getenv("OMR_POST_TIMING")) s->post_timing = e[0] == '1';
   int rc = s->open();
   if (rc) {
     s->destroy();
@@ -939,12 +982,13 @@ int omr_device_search(omr_store* s, const float* d_queries, int32_t nq, const ui
 }
 
 int omr_device_merge_topk(omr_store* s, const int64_t* d_in_rows, const double* d_in_dist, int32_t n_shards,
-                          int32_t nq, int32_t k, int64_t* d_rows, double* d_dist, int32_t* d_count, void* stream) {
+                          int32_t nq, int32_t k, int64_t shard_stride, int64_t* d_rows, double* d_dist, int32_t* d_count, void* stream) {
   if (!s || !d_in_rows || !d_in_dist || !d_rows || !d_dist || !d_count) return fail_msg(OMR_E_INVALID, "memory: omr_device_merge_topk: null argument");
   std::lock_guard<std::mutex> lk(s->mu);
   cudaSetDevice(s->cfg.device);
   s->st_launches++;
-  return launch_merge_topk(d_in_rows, d_in_dist, n_shards, nq, k, d_rows, d_dist, d_count, (cudaStream_t)stream);
+  return launch_merge_topk(d_in_rows, d_in_dist, n_shards, nq, k, shard_stride, d_rows, d_dist, d_count,
+                           (cudaStream_t)stream);
 }
 
 int omr_selfjoin(omr_store* s, const omr_selfjoin_opts* o, omr_pair* out, int64_t cap, int64_t* found) {
@@ -1060,7 +1104,7 @@ int omr_debug_candidate_keys(omr_store* s, const float* queries, int32_t nq, int
                              int32_t* out_keys, int64_t out_len) {
   if (!s || !queries || !out_keys) return fail_msg(OMR_E_INVALID, "memory: omr_debug_candidate_keys: null argument");
   if (S != 32 && S != 64 && S != 128 && S != 256) return fail_msg(OMR_E_INVALID, "memory: bad sub-bucket %d", S);
-  if (path != 1 && path != 2) return fail_msg(OMR_E_INVALID, "memory: path must be 1 or 2");
+  if (path != 1 && path != 2 && path != 4) return fail_msg(OMR_E_INVALID, "memory: path must be 1, 2 or 4");
   std::lock_guard<std::mutex> lk(s->mu);
   cudaSetDevice(s->cfg.device);
   if (s->n == 0 || nq <= 0) return OMR_OK;
@@ -1069,7 +1113,8 @@ int omr_debug_candidate_keys(omr_store* s, const float* queries, int32_t nq, int
   const int n_tiles = (int)((s->n + kTileRows - 1) / kTileRows);
   const int64_t kpq = (int64_t)n_tiles * (kTileRows / S) * 2;
   if (out_len < (int64_t)nq * kpq) return fail_msg(OMR_E_CAPACITY, "memory: need %lld keys", (long long)((int64_t)nq * kpq));
-  const int qpad = path == 2 ? ((nq + kQueryTile - 1) / kQueryTile) * kQueryTile : std::max(nq, 8);
+  const int qtile = path == 4 ? 2 * kQueryTile : kQueryTile;
+  const int qpad = path != 1 ? ((nq + qtile - 1) / qtile) * qtile : std::max(nq, 8);
   if ((rc = s->w_queries.reserve((size_t)nq * s->dim))) return rc;
   if ((rc = s->w_qn.reserve((size_t)qpad * s->pitch))) return rc;
   if ((rc = s->w_qnorm2.reserve((size_t)qpad))) return rc;
@@ -1090,9 +1135,13 @@ int omr_debug_candidate_keys(omr_store* s, const float* queries, int32_t nq, int
       s->tmap_q_ptr = s->w_qn.p;
       s->tmap_q_rows = s->w_qn.n / s->pitch;
     }
-    if ((rc = launch_score_umma(s->tmap_q, s->tmap_rows_b, qpad / kQueryTile, n_tiles, s->pitch / kBlockK, S,
-                                s->w_live.p, (int)s->words(), nullptr, s->w_cand.p, s->num_sms, st)))
-      return rc;
+    if (path == 4)
+      rc = launch_score_umma2(s->tmap_q, s->tmap_rows_a, nq, qpad / (2 * kQueryTile), n_tiles, s->pitch / kBlockK, S,
+                              s->w_live.p, (int)s->words(), nullptr, s->w_cand.p, s->num_sms, st);
+    else
+      rc = launch_score_umma(s->tmap_q, s->tmap_rows_b, nq, qpad / kQueryTile, n_tiles, s->pitch / kBlockK, S,
+                             s->w_live.p, (int)s->words(), nullptr, s->w_cand.p, s->num_sms, st);
+    if (rc) return rc;
   }
   OMR_CUDA_OK(cudaMemcpyAsync(out_keys, s->w_cand.p, (size_t)nq * kpq * 4, cudaMemcpyDeviceToHost, st));
   OMR_CUDA_OK(cudaStreamSynchronize(st));
@@ -1112,6 +1161,15 @@ int omr_get_stats(const omr_store* s, omr_stats* out) {
   out->num_sms = s->num_sms;
   out->scorer_ms_sum = s->scorer_ms_sum;
   out->scorer_timed = s->scorer_timed;
+  return OMR_OK;
+}
+
+int omr_debug_post_timing(omr_store* s, int64_t* out, int32_t nq) {
+  if (!s || !out) return fail_msg(OMR_E_INVALID, "memory: null argument");
+  std::lock_guard<std::mutex> lk(s->mu);
+  cudaSetDevice(s->cfg.device);
+  if (!s->w_timing.p || s->w_timing.n < (size_t)nq * 8) return fail_msg(OMR_E_INVALID, "memory: post timing was not recorded (set OMR_POST_TIMING=1)");
+  OMR_CUDA_OK(cudaMemcpy(out, s->w_timing.p, (size_t)nq * 8 * sizeof(long long), cudaMemcpyDeviceToHost));
   return OMR_OK;
 }
 

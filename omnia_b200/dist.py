@@ -53,11 +53,13 @@ class ShardedRecall:
         key = (nq, k)
         if key not in self._buf:
             d = self.device
+            # rows and distances of one rank live in ONE buffer [2][nq][k] (int64 / float64 views), so the
+            # exchange is a single allgather into [G][2][nq][k]
+            local = torch.empty((2, nq, k), dtype=torch.int64, device=d)
+            gathered = torch.empty((self.world, 2, nq, k), dtype=torch.int64, device=d)
             self._buf[key] = dict(
-                lr=torch.empty((nq, k), dtype=torch.int64, device=d), ld=torch.empty((nq, k), dtype=torch.float64, device=d),
-                lc=torch.empty(nq, dtype=torch.int32, device=d),
-                gr=torch.empty((self.world, nq, k), dtype=torch.int64, device=d),
-                gd=torch.empty((self.world, nq, k), dtype=torch.float64, device=d),
+                local=local, lr=local[0], ld=local[1].view(torch.float64),
+                lc=torch.empty(nq, dtype=torch.int32, device=d), gathered=gathered,
                 r=torch.empty((nq, k), dtype=torch.int64, device=d), d=torch.empty((nq, k), dtype=torch.float64, device=d),
                 c=torch.empty(nq, dtype=torch.int32, device=d))
         return self._buf[key]
@@ -71,9 +73,10 @@ class ShardedRecall:
                                  d_max_distance, stream)
         if self.world == 1:
             return b["lr"], b["ld"], b["lc"]
-        dist.all_gather_into_tensor(b["gr"], b["lr"], group=self.group)
-        dist.all_gather_into_tensor(b["gd"], b["ld"], group=self.group)
-        self.store.device_merge_topk(b["gr"], b["gd"], self.world, nq, k, b["r"], b["d"], b["c"], stream)
+        dist.all_gather_into_tensor(b["gathered"], b["local"], group=self.group)
+        g = b["gathered"]
+        self.store.device_merge_topk(g[:, 0], g[:, 1].view(torch.float64), self.world, nq, k, b["r"], b["d"], b["c"],
+                                     stream, shard_stride=2 * nq * k)
         return b["r"], b["d"], b["c"]
 
     def close(self):

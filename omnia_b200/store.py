@@ -338,9 +338,10 @@ class GPUMemoryStore:
                                             d_count.data_ptr(), stream))
 
     def device_merge_topk(self, d_in_rows, d_in_dist, n_shards: int, nq: int, k: int, d_rows, d_dist, d_count,
-                          stream: int = 0) -> None:
+                          stream: int = 0, shard_stride: int = 0) -> None:
         L.check(self._lib.omr_device_merge_topk(self._h, d_in_rows.data_ptr(), d_in_dist.data_ptr(), n_shards, nq, k,
-                                                d_rows.data_ptr(), d_dist.data_ptr(), d_count.data_ptr(), stream))
+                                                shard_stride, d_rows.data_ptr(), d_dist.data_ptr(),
+                                                d_count.data_ptr(), stream))
 
 
 def exact_topk_noalloc(d_rows, d_query, k: int, d_out_rows, d_out_dist, d_out_count, stream: int = 0) -> None:
