@@ -208,6 +208,17 @@ OMR_API int omr_device_build_bitmaps(omr_store* s, const omr_filter* filters, in
 OMR_API int omr_device_search(omr_store* s, const float* d_queries, int32_t nq, const uint32_t* d_bitmaps, int32_t n_groups,
                       const int32_t* d_query_group, const double* d_max_distance, int32_t k, int64_t* d_rows,
                       double* d_dist, int32_t* d_count, void* stream);
+/* Pipelined form of omr_device_search, for servers that keep the GPU busy with back-to-back
+ * batches: _begin enqueues the batch on an internal stream (ordered after what `stream` already
+ * holds) and returns at once; _finish(ticket) waits for that batch, runs the exact fallback if a
+ * certificate failed, and orders `stream` after the results.  Up to two batches may be in flight, so
+ * the select / rescore tail of batch i runs underneath the scorer of batch i+1.  Inputs, bitmaps and
+ * outputs of a batch must stay untouched between its _begin and its _finish. */
+OMR_API int omr_device_search_begin(omr_store* s, const float* d_queries, int32_t nq, const uint32_t* d_bitmaps,
+                                    int32_t n_groups, const int32_t* d_query_group, const double* d_max_distance,
+                                    int32_t k, int64_t* d_rows, double* d_dist, int32_t* d_count, void* stream,
+                                    int32_t* ticket);
+OMR_API int omr_device_search_finish(omr_store* s, int32_t ticket);
 /* Row-sharded stores: merges the G per-shard answers gathered into [G][nq][k]
  * (the gather itself is an NCCL allgather done by the host code).
  * shard_stride = elements between consecutive shards' [nq][k] blocks (0 = nq*k), so rows and

@@ -97,6 +97,10 @@ SIGNATURES = {
     "omr_device_build_bitmaps": (C.c_int, [C.c_void_p, C.POINTER(Filter), C.c_int32, C.c_void_p, C.c_void_p]),
     "omr_device_search": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p,
                                     C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "omr_device_search_begin": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p,
+                                          C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                          C.POINTER(C.c_int32)]),
+    "omr_device_search_finish": (C.c_int, [C.c_void_p, C.c_int32]),
     "omr_device_merge_topk": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_int64, C.c_void_p,
                                         C.c_void_p, C.c_void_p, C.c_void_p]),
     "omr_exact_topk_noalloc": (C.c_int, [C.c_void_p, C.c_int64, C.c_int32, C.c_int64, C.c_void_p, C.c_int32, C.c_void_p,

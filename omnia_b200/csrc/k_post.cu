@@ -20,9 +20,8 @@ namespace omr {
 
 namespace {
 
-constexpr int kPostThreads = 512;
+constexpr int kPostThreads = 256;
 constexpr int kCandCap = 384;     // collected keys per query (>= K2, K2 <= 256)
-constexpr int kSortCap = 2048;    // candidates + rescued rows that can be merged in-block
 constexpr int kSuspectCap = 32;   // suspect sub-buckets per query
 
 __device__ __forceinline__ double warp_sum_d(double v) {
@@ -31,13 +30,13 @@ __device__ __forceinline__ double warp_sum_d(double v) {
   return v;
 }
 
+// Fixed part of the block's shared memory; the fp64 query copy and the (distance, row) sort arrays
+// follow it and are sized at launch (sort_cap = candidates + rescued rows that can be merged in-block).
 struct PostSmem {
   int32_t lmax[kPostThreads];
   int32_t ckey[kCandCap];
   int32_t cidx[kCandCap];
   int32_t suspects[kSuspectCap];
-  double sd[kSortCap];
-  int32_t sr[kSortCap];
   int32_t n_cand, n_suspect, n_extra, fail;
 };
 
@@ -180,10 +179,13 @@ __device__ __forceinline__ void exact_distance2(const ShardView& sh, int64_t row
   d1 = two ? fin(a1, row1) : INFINITY;
 }
 
-__global__ void __launch_bounds__(kPostThreads) post_kernel(PostArgs a) {
+__global__ void __launch_bounds__(kPostThreads, 2) post_kernel(PostArgs a) {
   extern __shared__ __align__(16) uint8_t raw[];
   double* qd = reinterpret_cast<double*>(raw);                       // [pitch]
-  PostSmem& sm = *reinterpret_cast<PostSmem*>(raw + (size_t)a.sh.pitch * sizeof(double));
+  double* sd_base = qd + a.sh.pitch;                                 // [sort_cap]
+  int32_t* sr_base = reinterpret_cast<int32_t*>(sd_base + a.sort_cap);   // [sort_cap]
+  PostSmem& sm = *reinterpret_cast<PostSmem*>(sr_base + a.sort_cap);
+  const int kSortCap = a.sort_cap;
   const int q = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   auto stamp = [&](int phase) {
     if (a.timing && tid == 0) a.timing[(int64_t)q * 8 + phase] = clock64();
@@ -317,11 +319,11 @@ __global__ void __launch_bounds__(kPostThreads) post_kernel(PostArgs a) {
       exact_distance2(a.sh, r0, two ? r1 : r0, two, qd, qn2, lane, d0, d1);
     }
     if (lane == 0) {
-      sm.sd[c] = d0;
-      sm.sr[c] = r0;
+      sd_base[c] = d0;
+      sr_base[c] = r0;
       if (c1 < P) {
-        sm.sd[c1] = d1;
-        sm.sr[c1] = r1;
+        sd_base[c1] = d1;
+        sr_base[c1] = r1;
       }
     }
   }
@@ -329,17 +331,17 @@ __global__ void __launch_bounds__(kPostThreads) post_kernel(PostArgs a) {
   stamp(4);  // rescored
   if (P <= 32) {
     if (warp == 0) {
-      double d = lane < P ? sm.sd[lane] : INFINITY;
-      int32_t r = lane < P ? sm.sr[lane] : INT32_MAX;
+      double d = lane < P ? sd_base[lane] : INFINITY;
+      int32_t r = lane < P ? sr_base[lane] : INT32_MAX;
       warp_sort_items(d, r, lane);
       if (lane < P) {
-        sm.sd[lane] = d;
-        sm.sr[lane] = r;
+        sd_base[lane] = d;
+        sr_base[lane] = r;
       }
     }
     __syncthreads();
   } else {
-    sort_items(sm.sd, sm.sr, P);
+    sort_items(sd_base, sr_base, P);
   }
   const double maxd = a.max_dist ? a.max_dist[q] : INFINITY;
   int found;
@@ -347,20 +349,20 @@ __global__ void __launch_bounds__(kPostThreads) post_kernel(PostArgs a) {
     int lo = 0, hi = P < a.k ? P : a.k;
     while (lo < hi) {
       const int mid = (lo + hi) >> 1;
-      if (sm.sd[mid] <= maxd && sm.sd[mid] < INFINITY) lo = mid + 1; else hi = mid;
+      if (sd_base[mid] <= maxd && sd_base[mid] < INFINITY) lo = mid + 1; else hi = mid;
     }
     found = lo;
   }
   for (int i = tid; i < a.k; i += kPostThreads) {
     const bool ok = i < found;
-    a.out_rows[(int64_t)q * a.k + i] = ok ? a.row_base + (int64_t)sm.sr[i] * a.row_stride : -1;
-    a.out_dist[(int64_t)q * a.k + i] = ok ? sm.sd[i] : INFINITY;
+    a.out_rows[(int64_t)q * a.k + i] = ok ? a.row_base + (int64_t)sr_base[i] * a.row_stride : -1;
+    a.out_dist[(int64_t)q * a.k + i] = ok ? sd_base[i] : INFINITY;
   }
   if (tid == 0) a.out_count[q] = found;
 
   // ---- certificate (see finalize_kernel in k_select.cu for the argument)
   double tau;
-  if (found >= a.k) tau = 1.0 - sm.sd[a.k - 1];
+  if (found >= a.k) tau = 1.0 - sd_base[a.k - 1];
   else if (maxd < INFINITY) tau = 1.0 - maxd;
   else tau = -INFINITY;
   const float thr = (float)(tau - (double)a.margin) - 1e-7f;
@@ -397,28 +399,28 @@ __global__ void __launch_bounds__(kPostThreads) post_kernel(PostArgs a) {
         const int32_t row = (sm.cidx[c] >> 1) * a.S + (sm.ckey[c] & 0xFF);
         const double d = exact_distance(a.sh, row, qd, qn2, lane);
         if (lane == 0) {
-          sm.sd[c] = d;
-          sm.sr[c] = row;
+          sd_base[c] = d;
+          sr_base[c] = row;
         }
       }
       int P1 = 2;
       while (P1 < nc1) P1 <<= 1;
       __syncthreads();
       for (int i = nc1 + tid; i < P1; i += kPostThreads) {
-        sm.sd[i] = INFINITY;
-        sm.sr[i] = INT32_MAX;
+        sd_base[i] = INFINITY;
+        sr_base[i] = INT32_MAX;
       }
-      sort_items(sm.sd, sm.sr, P1);
+      sort_items(sd_base, sr_base, P1);
       int lo = 0, hi = P1 < a.k ? P1 : a.k;
       while (lo < hi) {
         const int mid = (lo + hi) >> 1;
-        if (sm.sd[mid] <= maxd && sm.sd[mid] < INFINITY) lo = mid + 1; else hi = mid;
+        if (sd_base[mid] <= maxd && sd_base[mid] < INFINITY) lo = mid + 1; else hi = mid;
       }
       found = lo;
       for (int i = tid; i < a.k; i += kPostThreads) {
         const bool ok = i < found;
-        a.out_rows[(int64_t)q * a.k + i] = ok ? a.row_base + (int64_t)sm.sr[i] * a.row_stride : -1;
-        a.out_dist[(int64_t)q * a.k + i] = ok ? sm.sd[i] : INFINITY;
+        a.out_rows[(int64_t)q * a.k + i] = ok ? a.row_base + (int64_t)sr_base[i] * a.row_stride : -1;
+        a.out_dist[(int64_t)q * a.k + i] = ok ? sd_base[i] : INFINITY;
       }
       if (tid == 0) a.out_count[q] = found;
       nc = nc1;
@@ -446,7 +448,7 @@ __global__ void __launch_bounds__(kPostThreads) post_kernel(PostArgs a) {
       const int64_t row = (int64_t)sm.suspects[t / a.S] * a.S + (t % a.S);
       if ((bm[row >> 5] >> (row & 31)) & 1u) {
         const int pos = nc + atomicAdd(&sm.n_extra, 1);
-        if (pos < kSortCap) sm.sr[pos] = (int32_t)row;
+        if (pos < kSortCap) sr_base[pos] = (int32_t)row;
       }
     }
     __syncthreads();
@@ -458,10 +460,10 @@ __global__ void __launch_bounds__(kPostThreads) post_kernel(PostArgs a) {
         const int c1 = c + kWarps;
         const bool two = c1 < nc + ne;
         double d0, d1;
-        exact_distance2(a.sh, sm.sr[c], two ? sm.sr[c1] : sm.sr[c], two, qd, qn2, lane, d0, d1);
+        exact_distance2(a.sh, sr_base[c], two ? sr_base[c1] : sr_base[c], two, qd, qn2, lane, d0, d1);
         if (lane == 0) {
-          sm.sd[c] = d0;
-          if (two) sm.sd[c1] = d1;
+          sd_base[c] = d0;
+          if (two) sd_base[c1] = d1;
         }
       }
       __syncthreads();
@@ -470,19 +472,19 @@ __global__ void __launch_bounds__(kPostThreads) post_kernel(PostArgs a) {
       // the first nc entries are the sorted candidates, but sorting moved padding inside [0, P):
       // after sort_items the real entries are the first nc (padding sorts last), so this layout holds
       for (int i = nc + ne + tid; i < P2; i += kPostThreads) {
-        sm.sd[i] = INFINITY;
-        sm.sr[i] = INT32_MAX;
+        sd_base[i] = INFINITY;
+        sr_base[i] = INT32_MAX;
       }
-      sort_items(sm.sd, sm.sr, P2);
+      sort_items(sd_base, sr_base, P2);
       if (tid == 0) {
         int f2 = 0;
         int32_t prev = -1;
         for (int i = 0; i < P2 && f2 < a.k; i++) {
-          if (!(sm.sd[i] <= maxd) || !(sm.sd[i] < INFINITY)) break;
-          if (sm.sr[i] == prev) continue;  // a suspect sub-bucket's keyed rows appear twice
-          prev = sm.sr[i];
-          a.out_rows[(int64_t)q * a.k + f2] = a.row_base + (int64_t)sm.sr[i] * a.row_stride;
-          a.out_dist[(int64_t)q * a.k + f2] = sm.sd[i];
+          if (!(sd_base[i] <= maxd) || !(sd_base[i] < INFINITY)) break;
+          if (sr_base[i] == prev) continue;  // a suspect sub-bucket's keyed rows appear twice
+          prev = sr_base[i];
+          a.out_rows[(int64_t)q * a.k + f2] = a.row_base + (int64_t)sr_base[i] * a.row_stride;
+          a.out_dist[(int64_t)q * a.k + f2] = sd_base[i];
           f2++;
         }
         a.out_count[q] = f2;
@@ -505,12 +507,10 @@ bool post_fused_supported(int K2, int k) { return K2 <= 256 && k <= 256; }
 
 int launch_post(const PostArgs& a, cudaStream_t st) {
   if (a.nq <= 0) return 0;
-  const size_t smem = (size_t)a.sh.pitch * sizeof(double) + sizeof(PostSmem);
-  static bool attr_done = false;
-  if (smem > 48 * 1024 && !attr_done) {
-    OMR_CUDA_OK(cudaFuncSetAttribute(post_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
-    attr_done = true;
-  }
+  if (a.sort_cap < kCandCap || (a.sort_cap & 1)) return fail_msg(-1, "post kernel sort capacity %d is too small", a.sort_cap);
+  const size_t smem = (size_t)a.sh.pitch * sizeof(double) + (size_t)a.sort_cap * 12 + sizeof(PostSmem);
+  if (smem > 48 * 1024)
+    OMR_CUDA_OK(cudaFuncSetAttribute(post_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   post_kernel<<<a.nq, kPostThreads, smem, st>>>(a);
   OMR_CUDA_OK(cudaGetLastError());
   return 0;

@@ -10,6 +10,7 @@
 // + the scope bitmap.  Queries live in shared memory for the whole kernel; the
 // only global writes are two packed keys per (query, sub-bucket).
 #include "kernels.cuh"
+#include "ptx.cuh"
 
 namespace omr {
 
@@ -136,6 +137,185 @@ __global__ void __launch_bounds__(256, 2)
   }
 }
 
+
+// ---------------------------------------------------------------------------------------
+// Single-query scorer with bulk-copy staging.  One producer thread streams the matrix through a
+// ring of shared-memory stages with cp.async.bulk (a tile's rows are contiguous in memory, so no
+// tensor map is needed); eight consumer warps each take one row of a stage at a time, with the
+// query held in registers.  The copy engine keeps ~150 KB in flight per SM, which is what it
+// takes to reach HBM speed; the LDG-based kernel above tops out lower because its loads are
+// bounded by registers.
+constexpr int kBulkMaxStages = 6;
+constexpr int kBulkConsumerWarps = 8;
+constexpr int kBulkThreads = (kBulkConsumerWarps + 1) * 32;
+
+struct __align__(8) BulkBarriers {
+  uint64_t full[kBulkMaxStages];
+  uint64_t empty[kBulkMaxStages];
+};
+
+// CHUNKS = 16-byte chunks per lane per row = ceil(pitch / 256); R = rows a warp scores together
+// (a stage holds 8*R rows), which gives the FMA and shuffle chains R-way instruction parallelism.
+template <int CHUNKS, int R>
+__global__ void __launch_bounds__(kBulkThreads, 1)
+    score_stream1_kernel(const __nv_bfloat16* __restrict__ rows, int pitch, int n_tiles, int n_stages,
+                         const __nv_bfloat16* __restrict__ qn, int S, const uint32_t* __restrict__ bitmaps,
+                         int words_per_group, const int32_t* __restrict__ query_group,
+                         int32_t* __restrict__ cand_keys) {
+  extern __shared__ __align__(128) uint8_t bsm[];
+  constexpr int kRowsPerStage = kBulkConsumerWarps * R;
+  const int stage_bytes = kRowsPerStage * pitch * 2;
+  BulkBarriers* bars = reinterpret_cast<BulkBarriers*>(bsm + (size_t)n_stages * stage_bytes);
+  int32_t* part = reinterpret_cast<int32_t*>(bars + 1);  // [kBulkConsumerWarps][2] partial top-2 of a sub-bucket
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (tid == 0) {
+    for (int i = 0; i < n_stages; i++) {
+      ptx::mbar_init(&bars->full[i], 1);
+      ptx::mbar_init(&bars->empty[i], kBulkConsumerWarps);
+    }
+    ptx::fence_barrier_init();
+  }
+  __syncthreads();
+  constexpr int kStagesPerTile = kTileRows / kRowsPerStage;
+
+  if (warp == kBulkConsumerWarps) {
+    // ---------------- producer ----------------
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        const uint8_t* src = reinterpret_cast<const uint8_t*>(rows + (int64_t)tile * kTileRows * pitch);
+        for (int st = 0; st < kStagesPerTile; st++) {
+          ptx::mbar_wait(&bars->empty[stage], phase ^ 1);
+          ptx::mbar_arrive_expect_tx(&bars->full[stage], stage_bytes);
+          ptx::bulk_load_1d(bsm + (size_t)stage * stage_bytes, src + (size_t)st * stage_bytes, stage_bytes,
+                            &bars->full[stage], ptx::kEvictFirst);
+          if (++stage == n_stages) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+      }
+    }
+    return;
+  }
+
+  // ---------------- consumers ----------------
+  const uint32_t* bitmap = bitmaps + (int64_t)(query_group ? __ldg(query_group) : 0) * words_per_group;
+  // query fragment of this lane: elements (c*32 + lane)*8 .. +8 for each chunk c
+  float qf[CHUNKS][8];
+#pragma unroll
+  for (int c = 0; c < CHUNKS; c++) {
+    const int e0 = (c * 32 + lane) * 8;
+#pragma unroll
+    for (int j = 0; j < 8; j++) qf[c][j] = e0 + j < pitch ? __bfloat162float(qn[e0 + j]) : 0.0f;
+  }
+  int stage = 0;
+  uint32_t phase = 0;
+  int32_t m1 = kKeyNone, m2 = kKeyNone;
+  for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+    for (int st = 0; st < kStagesPerTile; st++) {
+      ptx::mbar_wait(&bars->full[stage], phase);
+      const uint8_t* sbase = bsm + (size_t)stage * stage_bytes;
+      // warp w scores rows w, w+8, ..., w+8(R-1) of the stage together
+      float acc[R];
+#pragma unroll
+      for (int r = 0; r < R; r++) acc[r] = 0.0f;
+#pragma unroll
+      for (int c = 0; c < CHUNKS; c++) {
+        const int i = c * 32 + lane;
+        if (i * 8 < pitch) {
+          uint4 x[R];
+#pragma unroll
+          for (int r = 0; r < R; r++)
+            x[r] = reinterpret_cast<const uint4*>(sbase + (size_t)(warp + kBulkConsumerWarps * r) * pitch * 2)[i];
+#pragma unroll
+          for (int r = 0; r < R; r++) {
+            acc[r] = fmaf(bf16_lo(x[r].x), qf[c][0], acc[r]);
+            acc[r] = fmaf(bf16_hi(x[r].x), qf[c][1], acc[r]);
+            acc[r] = fmaf(bf16_lo(x[r].y), qf[c][2], acc[r]);
+            acc[r] = fmaf(bf16_hi(x[r].y), qf[c][3], acc[r]);
+            acc[r] = fmaf(bf16_lo(x[r].z), qf[c][4], acc[r]);
+            acc[r] = fmaf(bf16_hi(x[r].z), qf[c][5], acc[r]);
+            acc[r] = fmaf(bf16_lo(x[r].w), qf[c][6], acc[r]);
+            acc[r] = fmaf(bf16_hi(x[r].w), qf[c][7], acc[r]);
+          }
+        }
+      }
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive(&bars->empty[stage]);   // the stage's bytes are in registers now
+      if (++stage == n_stages) {
+        stage = 0;
+        phase ^= 1;
+      }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+#pragma unroll
+        for (int r = 0; r < R; r++) acc[r] += __shfl_xor_sync(0xffffffffu, acc[r], o);
+      }
+      const int rt0 = st * kRowsPerStage;  // kRowsPerStage <= 32 rows: one bitmap word
+      const uint32_t word = __ldg(bitmap + (int64_t)tile * 8 + (rt0 >> 5)) >> (rt0 & 31);
+#pragma unroll
+      for (int r = 0; r < R; r++) {
+        const int rs = warp + kBulkConsumerWarps * r;
+        if ((word >> rs) & 1u) top2_insert(m1, m2, pack_key(acc[r], (rt0 + rs) & (S - 1)));
+      }
+      // sub-bucket boundary: merge the eight warps' partial top-2 and emit two keys
+      if (((st + 1) * kRowsPerStage) % S == 0) {
+        if (lane == 0) {
+          part[warp * 2] = m1;
+          part[warp * 2 + 1] = m2;
+        }
+        asm volatile("bar.sync 1, %0;" ::"n"(kBulkConsumerWarps * 32) : "memory");
+        if (warp == 0) {
+          int32_t a = lane < kBulkConsumerWarps * 2 ? part[lane] : kKeyNone, b = kKeyNone;
+#pragma unroll
+          for (int o = 1; o < 16; o <<= 1) {
+            const int32_t oa = __shfl_xor_sync(0xffffffffu, a, o), ob = __shfl_xor_sync(0xffffffffu, b, o);
+            top2_insert(a, b, oa);
+            top2_insert(a, b, ob);
+          }
+          if (lane == 0) {
+            const int64_t sb = (int64_t)tile * (kTileRows / S) + ((st + 1) * kRowsPerStage) / S - 1;
+            *reinterpret_cast<int2*>(cand_keys + sb * 2) = make_int2(a, b);
+          }
+        }
+        asm volatile("bar.sync 1, %0;" ::"n"(kBulkConsumerWarps * 32) : "memory");
+        m1 = kKeyNone;
+        m2 = kKeyNone;
+      }
+    }
+  }
+}
+
+template <int CHUNKS, int R>
+int launch_stream1_r(const ShardView& sh, const __nv_bfloat16* qn, int n_tiles, int S, const uint32_t* bitmaps,
+                     int words_per_group, const int32_t* query_group, int32_t* cand_keys, int num_sms,
+                     cudaStream_t st) {
+  const size_t stage_bytes = (size_t)kBulkConsumerWarps * R * sh.pitch * 2;
+  int n_stages = (int)((200 * 1024) / stage_bytes);
+  if (n_stages > kBulkMaxStages) n_stages = kBulkMaxStages;
+  const size_t smem = n_stages * stage_bytes + sizeof(BulkBarriers) + kBulkConsumerWarps * 2 * 4;
+  auto kern = score_stream1_kernel<CHUNKS, R>;
+  OMR_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int grid = num_sms;
+  if (grid > n_tiles) grid = n_tiles;
+  kern<<<grid, kBulkThreads, smem, st>>>(sh.rows_bf16, sh.pitch, n_tiles, n_stages, qn, S, bitmaps, words_per_group,
+                                         query_group, cand_keys);
+  OMR_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+// 32 rows per stage (4 per warp) when two such stages fit in shared memory, else 16.
+template <int CHUNKS>
+int launch_stream1(const ShardView& sh, const __nv_bfloat16* qn, int n_tiles, int S, const uint32_t* bitmaps,
+                   int words_per_group, const int32_t* query_group, int32_t* cand_keys, int num_sms,
+                   cudaStream_t st) {
+  if ((size_t)2 * 32 * sh.pitch * 2 <= 200 * 1024)
+    return launch_stream1_r<CHUNKS, 4>(sh, qn, n_tiles, S, bitmaps, words_per_group, query_group, cand_keys, num_sms, st);
+  return launch_stream1_r<CHUNKS, 2>(sh, qn, n_tiles, S, bitmaps, words_per_group, query_group, cand_keys, num_sms, st);
+}
+
 template <int NQ>
 int launch_nq(const ShardView& sh, const __nv_bfloat16* qn, int nq, int n_tiles, int S, const uint32_t* bitmaps,
               int words_per_group, const int32_t* query_group, int32_t* cand_keys, int num_sms, cudaStream_t st) {
@@ -153,10 +333,24 @@ int launch_nq(const ShardView& sh, const __nv_bfloat16* qn, int nq, int n_tiles,
 
 }  // namespace
 
+bool g_force_ldg_stream = false;  // OMR_STREAM_LDG=1 keeps the LDG-based kernel for a single query (A/B measurements)
+
 int launch_score_stream(const ShardView& sh, const __nv_bfloat16* qn, int nq, int n_tiles, int S,
                         const uint32_t* bitmaps, int words_per_group, const int32_t* query_group,
                         int32_t* cand_keys, int num_sms, cudaStream_t st) {
   if (n_tiles <= 0) return 0;
+  if (nq <= 1 && !g_force_ldg_stream) {
+    switch ((sh.pitch + 255) / 256) {
+      case 1: return launch_stream1<1>(sh, qn, n_tiles, S, bitmaps, words_per_group, query_group, cand_keys, num_sms, st);
+      case 2: return launch_stream1<2>(sh, qn, n_tiles, S, bitmaps, words_per_group, query_group, cand_keys, num_sms, st);
+      case 3: return launch_stream1<3>(sh, qn, n_tiles, S, bitmaps, words_per_group, query_group, cand_keys, num_sms, st);
+      case 4: return launch_stream1<4>(sh, qn, n_tiles, S, bitmaps, words_per_group, query_group, cand_keys, num_sms, st);
+      case 5: return launch_stream1<5>(sh, qn, n_tiles, S, bitmaps, words_per_group, query_group, cand_keys, num_sms, st);
+      case 6: return launch_stream1<6>(sh, qn, n_tiles, S, bitmaps, words_per_group, query_group, cand_keys, num_sms, st);
+      case 7: return launch_stream1<7>(sh, qn, n_tiles, S, bitmaps, words_per_group, query_group, cand_keys, num_sms, st);
+      default: return launch_stream1<8>(sh, qn, n_tiles, S, bitmaps, words_per_group, query_group, cand_keys, num_sms, st);
+    }
+  }
   if (nq <= 1) return launch_nq<1>(sh, qn, nq, n_tiles, S, bitmaps, words_per_group, query_group, cand_keys, num_sms, st);
   if (nq <= 2) return launch_nq<2>(sh, qn, nq, n_tiles, S, bitmaps, words_per_group, query_group, cand_keys, num_sms, st);
   if (nq <= 4) return launch_nq<4>(sh, qn, nq, n_tiles, S, bitmaps, words_per_group, query_group, cand_keys, num_sms, st);

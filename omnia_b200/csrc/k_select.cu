@@ -408,12 +408,25 @@ __global__ void __launch_bounds__(1024) select_exact_kernel(const double* __rest
     T = rs.prefix;
     need_eq = rs.need;
   }
-  for (int64_t i = threadIdx.x; i < n_pad; i += blockDim.x) {
-    const unsigned long long u = d[i];
-    if (u >= kInf) continue;
-    bool take = u < T;
-    if (u == T) take = atomicAdd(&s_eq, 1u) < need_eq;
-    if (finite <= (unsigned long long)k) take = true;
+  // Rows strictly nearer than T are all taken; of the rows AT distance T exactly `need_eq` are, and
+  // they are the ones with the smallest row ids (an ordered block scan), so the answer does not
+  // depend on thread timing even when exact duplicates straddle the k-th place.
+  __shared__ uint32_t s_warp_ties[32];
+  __shared__ uint32_t s_tie_base;
+  if (threadIdx.x == 0) s_tie_base = 0;
+  __syncthreads();
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+  for (int64_t i0 = 0; i0 < n_pad; i0 += blockDim.x) {
+    const int64_t i = i0 + threadIdx.x;
+    const unsigned long long u = i < n_pad ? d[i] : kInf;
+    const bool finite_row = u < kInf;
+    const bool tie = finite_row && u == T && finite > (unsigned long long)k;
+    const uint32_t ballot = __ballot_sync(0xffffffffu, tie);
+    if (lane == 0) s_warp_ties[wid] = __popc(ballot);
+    __syncthreads();
+    uint32_t before = s_tie_base + __popc(ballot & ((1u << lane) - 1u));
+    for (int w = 0; w < wid; w++) before += s_warp_ties[w];
+    bool take = finite_row && (finite <= (unsigned long long)k || u < T || (tie && before < need_eq));
     if (take) {
       const uint32_t o = atomicAdd(&s_out, 1u);
       if (o < (uint32_t)K2) {
@@ -421,6 +434,13 @@ __global__ void __launch_bounds__(1024) select_exact_kernel(const double* __rest
         odist[o] = __longlong_as_double((long long)u);
       }
     }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      uint32_t t = 0;
+      for (int w = 0; w < nwarps; w++) t += s_warp_ties[w];
+      s_tie_base += t;
+    }
+    __syncthreads();
   }
 }
 

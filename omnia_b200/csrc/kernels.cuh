@@ -78,6 +78,7 @@ struct PostArgs {
   const int32_t* cand_keys = nullptr;
   int64_t keys_per_query = 0;
   int nq = 0, S = 256, K2 = 32, k = 10;
+  int sort_cap = 2048;                 // in-block merge capacity (candidates + rescued rows); >= 384, even
   const double* max_dist = nullptr;
   float margin = 0.0f;
   const uint32_t* bitmaps = nullptr;

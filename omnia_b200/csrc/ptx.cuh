@@ -94,6 +94,18 @@ __device__ __forceinline__ void tma_load_2d(void* smem_dst, const void* desc, ui
       : "memory");
 }
 
+// 1-D bulk copy global -> shared (no tensor map): `bytes` contiguous bytes, 16-byte aligned on
+// both sides, completing on the mbarrier.  SASS: UBLKCP.
+__device__ __forceinline__ void bulk_load_1d(void* smem_dst, const void* gmem_src, uint32_t bytes, uint64_t* bar,
+                                             uint64_t cache_hint) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;"
+      :
+      : "r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(gmem_src)), "r"(bytes), "r"(smem_u32(bar)),
+        "l"(cache_hint)
+      : "memory");
+}
+
 // ---- tcgen05 / TMEM --------------------------------------------------------
 
 // Whole-warp call.  Writes the TMEM base address of `ncols` columns to smem.

@@ -38,6 +38,7 @@ int fail_cuda(cudaError_t e, const char* what, const char* file, int line) {
   return fail_msg(OMR_E_CUDA, "memory: gpu: %s failed: %s (%s:%d)", what, cudaGetErrorString(e), file, line);
 }
 
+extern bool g_force_ldg_stream;
 int launch_iota(int32_t* p, int n, cudaStream_t st);
 int launch_fill_empty(int64_t* rows, double* dist, int32_t* count, int nq, int k, cudaStream_t st);
 int launch_pair_remap(PairCand* pairs, unsigned long long n, const int32_t* remap, cudaStream_t st);
@@ -181,10 +182,31 @@ struct omr_store {
   std::unordered_map<Key128, uint32_t, Key128Hash> entity_idx;
   Interner ws_names{1}, user_names{1}, agent_names{1}, kind_names{0}, purpose_names{0};
 
-  // per-search scratch (grown on demand, reused)
-  DevBuf<__nv_bfloat16> w_qn;
-  DevBuf<double> w_qnorm2, w_sel_dist, w_exact, w_maxdist, w_out_dist, w_pair_sim;
-  DevBuf<int32_t> w_cand, w_sel_rows, w_extra_cnt, w_extra_items, w_fail_list, w_counters, w_qgroup, w_out_count, w_idx;
+  // Per-search scratch (grown on demand, reused).  A Lane is everything one batch in flight needs to
+  // itself: lane 0 serves the synchronous entry points, lanes 1 and 2 the begin/finish pipeline.
+  struct Lane {
+    DevBuf<__nv_bfloat16> qn;
+    DevBuf<double> qnorm2;
+    DevBuf<int32_t> cand, fail_list, counters, extra_cnt;
+    DevBuf<long long> timing;
+    PinBuf<int32_t> pin;
+    CUtensorMap tmap_q{};
+    size_t tmap_q_rows = 0;
+    const void* tmap_q_ptr = nullptr;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev_in = nullptr, ev_done = nullptr, ev0 = nullptr, ev1 = nullptr;
+    bool busy = false, immediate = false, timed = false;
+    // the batch in flight
+    const float* d_q = nullptr;
+    const uint32_t* d_bitmaps = nullptr;
+    const int32_t* d_qgroup = nullptr;
+    int nq = 0, k = 0, K2 = 0, K2x = 0, qpad = 0, nfail_known = -1;
+    cudaStream_t caller = nullptr;
+    FinalizeArgs fa;
+  };
+  Lane lanes[3];
+  DevBuf<double> w_sel_dist, w_exact, w_maxdist, w_out_dist, w_pair_sim;
+  DevBuf<int32_t> w_sel_rows, w_extra_items, w_qgroup, w_out_count, w_idx;
   DevBuf<float> w_sel_bound, w_queries, w_stage;
   DevBuf<uint32_t> w_bitmaps, w_live, w_member;
   DevBuf<int64_t> w_out_rows;
@@ -193,19 +215,13 @@ struct omr_store {
   DevBuf<unsigned long long> w_pair_count;
   DevBuf<__nv_bfloat16> w_gather;
   PinBuf<uint8_t> pin_in, pin_out;
-  PinBuf<int32_t> pin_counters;
-  CUtensorMap tmap_q{};
-  size_t tmap_q_rows = 0;
-  const void* tmap_q_ptr = nullptr;
   bool live_dirty = true;
   bool post_timing = false;  // OMR_POST_TIMING=1: per-phase clock stamps of the fused post kernel
-  DevBuf<long long> w_timing;
   bool legacy_post = false;  // OMR_LEGACY_POST=1: use the unfused select/rescore/finalize chain
 
   std::atomic<int64_t> st_launches{0}, st_searches{0}, st_queries{0}, st_rescued{0}, st_fallback{0};
   // optional device timing of the dominant kernel (the approximate scorer), for bench.py's roofline
   bool profiling = false;
-  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   double scorer_ms_sum = 0.0;
   int64_t scorer_timed = 0;
   int last_path = 0, last_S = 0, last_K2 = 0;
@@ -235,6 +251,11 @@ struct omr_store {
   int ensure_live(cudaStream_t st);
   int device_search(const float* d_q, int nq, const uint32_t* d_bitmaps, const int32_t* d_qgroup,
                     const double* d_maxdist, int k, int64_t* d_rows, double* d_dist, int32_t* d_count, cudaStream_t st);
+  int enqueue(Lane& L, const float* d_q, int nq, const uint32_t* d_bitmaps, const int32_t* d_qgroup,
+              const double* d_maxdist, int k, int64_t* d_rows, double* d_dist, int32_t* d_count, cudaStream_t st,
+              bool* fused_out);
+  int complete(Lane& L, cudaStream_t st);
+  int drain();
   int host_search(const float* queries, int nq, const omr_filter* filters, int n_filters, const int32_t* query_filter,
                   int k, omr_hit* hits, int32_t* counts, int64_t* soa_rows = nullptr, double* soa_dist = nullptr);
   void fill_hit(omr_hit* h, int64_t grow, double dist) const;
@@ -276,12 +297,16 @@ int omr_store::open() {
   if (rc) return rc;
   rc = make_tmap(&tmap_rows_a, d_bf16, (uint64_t)cap, kQueryTile);
   if (rc) return rc;
-  OMR_CUDA_OK(cudaEventCreate(&ev0));
-  OMR_CUDA_OK(cudaEventCreate(&ev1));
-  rc = pin_counters.reserve(4);
-  if (rc) return rc;
-  rc = w_counters.reserve(4);
-  return rc;
+  for (Lane& L : lanes) {
+    OMR_CUDA_OK(cudaStreamCreateWithFlags(&L.stream, cudaStreamNonBlocking));
+    OMR_CUDA_OK(cudaEventCreateWithFlags(&L.ev_in, cudaEventDisableTiming));
+    OMR_CUDA_OK(cudaEventCreateWithFlags(&L.ev_done, cudaEventDisableTiming));
+    OMR_CUDA_OK(cudaEventCreate(&L.ev0));
+    OMR_CUDA_OK(cudaEventCreate(&L.ev1));
+    if ((rc = L.pin.reserve(4))) return rc;
+    if ((rc = L.counters.reserve(4))) return rc;
+  }
+  return 0;
 }
 
 void omr_store::destroy() {
@@ -290,15 +315,21 @@ void omr_store::destroy() {
   void* ptrs[] = {d_bf16, d_f32, d_norm2, d_ws, d_user, d_agent, d_kind, d_purpose, d_conf, d_flags, d_valid};
   for (void* p : ptrs)
     if (p) cudaFree(p);
-  w_qn.release(); w_qnorm2.release(); w_sel_dist.release(); w_exact.release(); w_maxdist.release();
-  w_out_dist.release(); w_pair_sim.release(); w_cand.release(); w_sel_rows.release(); w_extra_cnt.release();
-  w_extra_items.release(); w_fail_list.release(); w_counters.release(); w_qgroup.release(); w_out_count.release();
+  for (Lane& L : lanes) {
+    if (L.stream) cudaStreamSynchronize(L.stream);
+    L.qn.release(); L.qnorm2.release(); L.cand.release(); L.fail_list.release(); L.counters.release();
+    L.extra_cnt.release(); L.timing.release(); L.pin.release();
+    for (cudaEvent_t e : {L.ev_in, L.ev_done, L.ev0, L.ev1})
+      if (e) cudaEventDestroy(e);
+    if (L.stream) cudaStreamDestroy(L.stream);
+  }
+  w_sel_dist.release(); w_exact.release(); w_maxdist.release();
+  w_out_dist.release(); w_pair_sim.release(); w_sel_rows.release();
+  w_extra_items.release(); w_qgroup.release(); w_out_count.release();
   w_idx.release(); w_sel_bound.release(); w_queries.release(); w_stage.release(); w_bitmaps.release();
   w_live.release(); w_member.release(); w_out_rows.release(); w_filters.release(); w_pairs.release();
   w_pair_count.release(); w_gather.release();
-  pin_in.release(); pin_out.release(); pin_counters.release();
-  if (ev0) cudaEventDestroy(ev0);
-  if (ev1) cudaEventDestroy(ev1);
+  pin_in.release(); pin_out.release();
   if (stream) cudaStreamDestroy(stream);
 }
 
@@ -405,6 +436,27 @@ int omr_store::ensure_live(cudaStream_t st) {
 int omr_store::device_search(const float* d_q, int nq, const uint32_t* d_bitmaps, const int32_t* d_qgroup,
                              const double* d_maxdist, int k, int64_t* d_rows, double* d_dist, int32_t* d_count,
                              cudaStream_t st) {
+  Lane& L = lanes[0];
+  int rc = enqueue(L, d_q, nq, d_bitmaps, d_qgroup, d_maxdist, k, d_rows, d_dist, d_count, st, nullptr);
+  if (rc) return rc;
+  return complete(L, st);
+}
+
+// Waits for every batch of the begin/finish pipeline that is still in flight (before the store mutates).
+int omr_store::drain() {
+  for (int i = 1; i < 3; i++)
+    if (lanes[i].busy && !lanes[i].immediate) OMR_CUDA_OK(cudaStreamSynchronize(lanes[i].stream));
+  return 0;
+}
+
+// Enqueues one batch on `st` up to (and including) the read-back of its counters; no host wait.
+int omr_store::enqueue(Lane& L, const float* d_q, int nq, const uint32_t* d_bitmaps, const int32_t* d_qgroup,
+                       const double* d_maxdist, int k, int64_t* d_rows, double* d_dist, int32_t* d_count,
+                       cudaStream_t st, bool* fused_out) {
+  L.nq = 0;
+  L.nfail_known = 0;
+  L.timed = false;
+  if (fused_out) *fused_out = true;
   if (nq <= 0) return 0;
   if (k <= 0 || k > 4096) return fail_msg(OMR_E_INVALID, "memory: k must be in 1..4096, got %d", k);
   st_searches++;
@@ -443,110 +495,136 @@ int omr_store::device_search(const float* d_q, int nq, const uint32_t* d_bitmaps
   last_path = path; last_S = S; last_K2 = K2;
 
   const bool fused = path != 3 && !legacy_post && post_fused_supported(K2, k);
-  if ((rc = w_qn.reserve((size_t)qpad * pitch))) return rc;
-  if ((rc = w_qnorm2.reserve((size_t)qpad))) return rc;
-  if ((rc = w_fail_list.reserve((size_t)qpad))) return rc;
-  if ((rc = w_extra_cnt.reserve((size_t)qpad))) return rc;
+  if (fused_out) *fused_out = fused;
+  if ((rc = L.qn.reserve((size_t)qpad * pitch))) return rc;
+  if ((rc = L.qnorm2.reserve((size_t)qpad))) return rc;
+  if ((rc = L.fail_list.reserve((size_t)qpad))) return rc;
+  if ((rc = L.extra_cnt.reserve((size_t)qpad))) return rc;
   if (!fused) {
     if ((rc = w_sel_rows.reserve((size_t)qpad * K2x))) return rc;
     if ((rc = w_sel_dist.reserve((size_t)qpad * K2x))) return rc;
     if ((rc = w_sel_bound.reserve((size_t)qpad))) return rc;
     if ((rc = w_extra_items.reserve((size_t)qpad * kExtraSlots))) return rc;
   }
-  if (path != 3 && (rc = w_cand.reserve((size_t)qpad * kpq))) return rc;
+  if (path != 3 && (rc = L.cand.reserve((size_t)qpad * kpq))) return rc;
 
-  OMR_CUDA_OK(cudaMemsetAsync(w_counters.p, 0, 4 * sizeof(int32_t), st));
-  OMR_CUDA_OK(cudaMemsetAsync(w_extra_cnt.p, 0, (size_t)qpad * sizeof(int32_t), st));
-  int32_t* extra_total = w_counters.p;
-  int32_t* fail_count = w_counters.p + 1;
+  OMR_CUDA_OK(cudaMemsetAsync(L.counters.p, 0, 4 * sizeof(int32_t), st));
+  OMR_CUDA_OK(cudaMemsetAsync(L.extra_cnt.p, 0, (size_t)qpad * sizeof(int32_t), st));
+  int32_t* extra_total = L.counters.p;
+  int32_t* fail_count = L.counters.p + 1;
   const ShardView sh = view();
 
-  rc = launch_prep_queries(d_q, nq, qpad, dim, pitch, w_qn.p, w_qnorm2.p, st);
+  rc = launch_prep_queries(d_q, nq, qpad, dim, pitch, L.qn.p, L.qnorm2.p, st);
   if (rc) return rc;
   st_launches++;
 
   FinalizeArgs fa;
   fa.nq = nq; fa.K2 = K2; fa.K2x = K2x; fa.k = k; fa.S = S;
   fa.sel_rows = w_sel_rows.p; fa.sel_dist = w_sel_dist.p; fa.max_dist = d_maxdist; fa.sel_bound = w_sel_bound.p;
-  fa.cand_keys = w_cand.p; fa.keys_per_query = kpq; fa.margin = margin;
+  fa.cand_keys = L.cand.p; fa.keys_per_query = kpq; fa.margin = margin;
   fa.bitmaps = d_bitmaps; fa.words_per_group = wpg; fa.query_group = d_qgroup;
   fa.row_base = cfg.row_base; fa.row_stride = cfg.row_stride;
   fa.out_rows = d_rows; fa.out_dist = d_dist; fa.out_count = d_count;
-  fa.extra_cnt = w_extra_cnt.p; fa.extra_items = w_extra_items.p; fa.extra_total = extra_total;
-  fa.fail_list = w_fail_list.p; fa.fail_count = fail_count;
+  fa.extra_cnt = L.extra_cnt.p; fa.extra_items = w_extra_items.p; fa.extra_total = extra_total;
+  fa.fail_list = L.fail_list.p; fa.fail_count = fail_count;
 
-  int nfail = 0;
+  L.d_q = d_q; L.d_bitmaps = d_bitmaps; L.d_qgroup = d_qgroup; L.nq = nq; L.k = k; L.K2 = K2; L.K2x = K2x; L.qpad = qpad;
+  L.fa = fa;
   if (path == 3) {
-    rc = launch_iota(w_fail_list.p, nq, st);
+    rc = launch_iota(L.fail_list.p, nq, st);
     if (rc) return rc;
     st_launches++;
-    nfail = nq;
-  } else {
-    if (profiling) OMR_CUDA_OK(cudaEventRecord(ev0, st));
+    L.nfail_known = nq;
+    return 0;
+  }
+  L.nfail_known = -1;
+  {
+    if (profiling) OMR_CUDA_OK(cudaEventRecord(L.ev0, st));
     if (path == 1) {
       // the streaming scorer takes 8 queries per pass over the matrix
       for (int q0 = 0; q0 < nq; q0 += 8) {
         const int c = std::min(8, nq - q0);
-        rc = launch_score_stream(sh, w_qn.p + (size_t)q0 * pitch, c, n_tiles, S, d_bitmaps, wpg,
-                                 d_qgroup ? d_qgroup + q0 : nullptr, w_cand.p + (size_t)q0 * kpq, num_sms, st);
+        rc = launch_score_stream(sh, L.qn.p + (size_t)q0 * pitch, c, n_tiles, S, d_bitmaps, wpg,
+                                 d_qgroup ? d_qgroup + q0 : nullptr, L.cand.p + (size_t)q0 * kpq, num_sms, st);
         if (rc) return rc;
         st_launches++;
       }
     } else {
-      if (tmap_q_ptr != w_qn.p || tmap_q_rows != w_qn.n / pitch) {
-        rc = make_tmap(&tmap_q, w_qn.p, w_qn.n / pitch, kQueryTile);
+      if (L.tmap_q_ptr != L.qn.p || L.tmap_q_rows != L.qn.n / pitch) {
+        rc = make_tmap(&L.tmap_q, L.qn.p, L.qn.n / pitch, kQueryTile);
         if (rc) return rc;
-        tmap_q_ptr = w_qn.p;
-        tmap_q_rows = w_qn.n / pitch;
+        L.tmap_q_ptr = L.qn.p;
+        L.tmap_q_rows = L.qn.n / pitch;
       }
       if (path == 4)
-        rc = launch_score_umma2(tmap_q, tmap_rows_a, nq, qpad / (2 * kQueryTile), n_tiles, pitch / kBlockK, S, d_bitmaps, wpg,
-                                d_qgroup, w_cand.p, num_sms, st);
+        rc = launch_score_umma2(L.tmap_q, tmap_rows_a, nq, qpad / (2 * kQueryTile), n_tiles, pitch / kBlockK, S, d_bitmaps, wpg,
+                                d_qgroup, L.cand.p, num_sms, st);
       else
-        rc = launch_score_umma(tmap_q, tmap_rows_b, nq, qpad / kQueryTile, n_tiles, pitch / kBlockK, S, d_bitmaps, wpg,
-                               d_qgroup, w_cand.p, num_sms, st);
+        rc = launch_score_umma(L.tmap_q, tmap_rows_b, nq, qpad / kQueryTile, n_tiles, pitch / kBlockK, S, d_bitmaps, wpg,
+                               d_qgroup, L.cand.p, num_sms, st);
       if (rc) return rc;
       st_launches++;
     }
-    if (profiling) OMR_CUDA_OK(cudaEventRecord(ev1, st));
+    if (profiling) OMR_CUDA_OK(cudaEventRecord(L.ev1, st));
     if (fused) {
       PostArgs pa;
-      pa.sh = sh; pa.q = d_q; pa.qnorm2 = w_qnorm2.p; pa.cand_keys = w_cand.p; pa.keys_per_query = kpq;
+      pa.sh = sh; pa.q = d_q; pa.qnorm2 = L.qnorm2.p; pa.cand_keys = L.cand.p; pa.keys_per_query = kpq;
       // the fused kernel tops its candidate list up adaptively, so its first pass can be narrow
       pa.nq = nq; pa.S = S; pa.K2 = cfg.rescore_width > 0 ? K2 : std::min(K2, std::max(16, k + 6)); pa.k = k; pa.max_dist = d_maxdist; pa.margin = margin;
       pa.bitmaps = d_bitmaps; pa.words_per_group = wpg; pa.query_group = d_qgroup;
       pa.row_base = cfg.row_base; pa.row_stride = cfg.row_stride;
       pa.out_rows = d_rows; pa.out_dist = d_dist; pa.out_count = d_count;
-      pa.fail_list = w_fail_list.p; pa.fail_count = fail_count; pa.rescued_total = extra_total;
+      pa.fail_list = L.fail_list.p; pa.fail_count = fail_count; pa.rescued_total = extra_total;
+      pa.sort_cap = k <= 16 ? 512 : 2048;   // 512 keeps the block under 30 KB so it fits beside a scorer CTA
       if (post_timing) {
-        if ((rc = w_timing.reserve((size_t)qpad * 8))) return rc;
-        pa.timing = w_timing.p;
+        if ((rc = L.timing.reserve((size_t)qpad * 8))) return rc;
+        pa.timing = L.timing.p;
       }
       if ((rc = launch_post(pa, st))) return rc;
       st_launches += 1;
     } else {
-      if ((rc = launch_select_keys(w_cand.p, nq, kpq, S, K2, K2x, w_sel_rows.p, w_sel_bound.p, st))) return rc;
-      if ((rc = launch_rescore(sh, d_q, w_qnorm2.p, nq, K2, K2x, w_sel_rows.p, w_sel_dist.p, st))) return rc;
+      if ((rc = launch_select_keys(L.cand.p, nq, kpq, S, K2, K2x, w_sel_rows.p, w_sel_bound.p, st))) return rc;
+      if ((rc = launch_rescore(sh, d_q, L.qnorm2.p, nq, K2, K2x, w_sel_rows.p, w_sel_dist.p, st))) return rc;
       if ((rc = launch_finalize(fa, st))) return rc;
-      if ((rc = launch_rescore_items(sh, d_q, w_qnorm2.p, K2x, w_extra_items.p, extra_total, w_sel_rows.p, w_sel_dist.p,
+      if ((rc = launch_rescore_items(sh, d_q, L.qnorm2.p, K2x, w_extra_items.p, extra_total, w_sel_rows.p, w_sel_dist.p,
                                      num_sms, st)))
         return rc;
       if ((rc = launch_finalize_extra(fa, st))) return rc;
       st_launches += 5;
     }
-    OMR_CUDA_OK(cudaMemcpyAsync(pin_counters.p, w_counters.p, 2 * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+    OMR_CUDA_OK(cudaMemcpyAsync(L.pin.p, L.counters.p, 2 * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+    L.timed = profiling;
+  }
+  return 0;
+}
+
+// Host side of a batch: waits for `st`, reads the counters and runs the exact fallback for the
+// (rare) queries whose certificate failed.
+int omr_store::complete(Lane& L, cudaStream_t st) {
+  if (L.nq <= 0) return 0;
+  int rc;
+  int nfail = L.nfail_known;
+  if (nfail < 0) {
     OMR_CUDA_OK(cudaStreamSynchronize(st));
-    st_rescued += pin_counters.p[0];
-    nfail = pin_counters.p[1];
-    if (profiling) {
+    st_rescued += L.pin.p[0];
+    nfail = L.pin.p[1];
+    if (L.timed) {
       float ms = 0.0f;
-      OMR_CUDA_OK(cudaEventElapsedTime(&ms, ev0, ev1));
+      OMR_CUDA_OK(cudaEventElapsedTime(&ms, L.ev0, L.ev1));
       scorer_ms_sum += ms;
       scorer_timed++;
     }
   }
   if (nfail > 0) {
     // Exact fallback: score every eligible row of the failing queries in fp64.
+    const int nq = L.nq, k = L.k, K2 = L.K2, K2x = L.K2x, qpad = L.qpad;
+    const float* d_q = L.d_q;
+    const uint32_t* d_bitmaps = L.d_bitmaps;
+    const int32_t* d_qgroup = L.d_qgroup;
+    const int wpg = (int)words();
+    const ShardView sh = view();
+    FinalizeArgs fa = L.fa;
+    (void)nq;
     st_fallback += nfail;
     if ((rc = w_sel_rows.reserve((size_t)qpad * K2x))) return rc;   // the fallback's tail uses the candidate-slot layout
     if ((rc = w_sel_dist.reserve((size_t)qpad * K2x))) return rc;
@@ -559,8 +637,8 @@ int omr_store::device_search(const float* d_q, int nq, const uint32_t* d_bitmaps
     fx.cand_keys = nullptr;
     for (int s0 = 0; s0 < nfail; s0 += slots) {
       const int c = std::min(slots, nfail - s0);
-      const int32_t* list = w_fail_list.p + s0;
-      if ((rc = launch_exact_scan(sh, d_q, w_qnorm2.p, list, c, d_bitmaps, wpg, d_qgroup, w_exact.p, st))) return rc;
+      const int32_t* list = L.fail_list.p + s0;
+      if ((rc = launch_exact_scan(sh, d_q, L.qnorm2.p, list, c, d_bitmaps, wpg, d_qgroup, w_exact.p, st))) return rc;
       if ((rc = launch_select_exact(w_exact.p, n_pad, list, c, K2, K2x, k, w_sel_rows.p, w_sel_dist.p, st))) return rc;
       fx.qlist = list;
       fx.nlist = c;
@@ -679,6 +757,7 @@ int omr_open(const omr_config* cfg, omr_store** out) {
   s->margin = cfg->candidate_margin > 0 ? cfg->candidate_margin : 1e-3f;
   if (const char* e = getenv("OMR_LEGACY_POST")) s->legacy_post = e[0] == '1';
   if (const char* e = getenv("OMR_POST_TIMING")) s->post_timing = e[0] == '1';
+  if (const char* e = getenv("OMR_STREAM_LDG")) g_force_ldg_stream = e[0] == '1';
   int rc = s->open();
   if (rc) {
     s->destroy();
@@ -732,6 +811,7 @@ int omr_bulk_load(omr_store* s, const omr_bulk* b) {
   if (!b->vectors) return fail_msg(OMR_E_INVALID, "memory: omr_bulk_load: vectors is null");
   std::lock_guard<std::mutex> lk(s->mu);
   cudaSetDevice(s->cfg.device);
+  if (int drc = s->drain()) return drc;
   if (s->n + b->n > s->cfg.capacity) return fail_msg(OMR_E_CAPACITY, "memory: gpu store is full (%lld + %lld > %lld rows)",
                                                      (long long)s->n, (long long)b->n, (long long)s->cfg.capacity);
   auto table = [](Interner& in, const char* const* names, int cnt, const char* what, std::vector<uint32_t>* map) {
@@ -799,6 +879,7 @@ int omr_upsert(omr_store* s, const omr_row* row, const float* vec, int32_t dim) 
   if (!row->workspace_id || !row->workspace_id[0]) return fail_msg(OMR_E_WORKSPACE, "memory: workspace_id is required");
   std::lock_guard<std::mutex> lk(s->mu);
   cudaSetDevice(s->cfg.device);
+  if (int drc = s->drain()) return drc;
   const Key128 ok = key_of(row->observation_id);
   int64_t r;
   auto it = s->obs_row.find(ok);
@@ -839,6 +920,7 @@ int omr_update_embedding(omr_store* s, const uint8_t entity_id[16], const float*
   if (dim != s->dim) return fail_msg(OMR_E_DIM, "memory: embedding dimension mismatch: got %d, store has %d", dim, s->dim);
   std::lock_guard<std::mutex> lk(s->mu);
   cudaSetDevice(s->cfg.device);
+  if (int drc = s->drain()) return drc;
   auto it = s->entity_idx.find(key_of(entity_id));
   if (it == s->entity_idx.end() || s->entity_latest[it->second] < 0) return fail_msg(OMR_E_NOT_FOUND, "memory: not found");
   const int64_t r = s->entity_latest[it->second];
@@ -861,6 +943,7 @@ int omr_set_row_flags(omr_store* s, const uint8_t observation_id[16], uint32_t s
   if (!s || !observation_id) return fail_msg(OMR_E_INVALID, "memory: null argument");
   std::lock_guard<std::mutex> lk(s->mu);
   cudaSetDevice(s->cfg.device);
+  if (int drc = s->drain()) return drc;
   auto it = s->obs_row.find(key_of(observation_id));
   if (it == s->obs_row.end()) return fail_msg(OMR_E_NOT_FOUND, "memory: not found");
   return edit_rows(s, {it->second}, set_mask, clear_mask);
@@ -870,6 +953,7 @@ int omr_set_entity_flags(omr_store* s, const uint8_t entity_id[16], uint32_t set
   if (!s || !entity_id) return fail_msg(OMR_E_INVALID, "memory: null argument");
   std::lock_guard<std::mutex> lk(s->mu);
   cudaSetDevice(s->cfg.device);
+  if (int drc = s->drain()) return drc;
   auto it = s->entity_idx.find(key_of(entity_id));
   if (it == s->entity_idx.end()) return fail_msg(OMR_E_NOT_FOUND, "memory: not found");
   return edit_rows(s, s->entity_rows[it->second], set_mask, clear_mask);
@@ -883,6 +967,7 @@ int omr_set_valid_until(omr_store* s, const uint8_t observation_id[16], int64_t 
   if (!s || !observation_id) return fail_msg(OMR_E_INVALID, "memory: null argument");
   std::lock_guard<std::mutex> lk(s->mu);
   cudaSetDevice(s->cfg.device);
+  if (int drc = s->drain()) return drc;
   auto it = s->obs_row.find(key_of(observation_id));
   if (it == s->obs_row.end()) return fail_msg(OMR_E_NOT_FOUND, "memory: not found");
   s->h_valid[it->second] = valid_until_us;
@@ -894,6 +979,7 @@ int omr_set_confidence(omr_store* s, const uint8_t observation_id[16], float con
   if (!s || !observation_id) return fail_msg(OMR_E_INVALID, "memory: null argument");
   std::lock_guard<std::mutex> lk(s->mu);
   cudaSetDevice(s->cfg.device);
+  if (int drc = s->drain()) return drc;
   auto it = s->obs_row.find(key_of(observation_id));
   if (it == s->obs_row.end()) return fail_msg(OMR_E_NOT_FOUND, "memory: not found");
   s->h_conf[it->second] = confidence;
@@ -981,6 +1067,62 @@ int omr_device_search(omr_store* s, const float* d_queries, int32_t nq, const ui
                           (cudaStream_t)stream);
 }
 
+int omr_device_search_begin(omr_store* s, const float* d_queries, int32_t nq, const uint32_t* d_bitmaps,
+                            int32_t n_groups, const int32_t* d_query_group, const double* d_max_distance, int32_t k,
+                            int64_t* d_rows, double* d_dist, int32_t* d_count, void* stream, int32_t* ticket) {
+  if (!s || !d_queries || !d_rows || !d_dist || !d_count || !ticket)
+    return fail_msg(OMR_E_INVALID, "memory: omr_device_search_begin: null argument");
+  (void)n_groups;
+  std::lock_guard<std::mutex> lk(s->mu);
+  cudaSetDevice(s->cfg.device);
+  int idx = -1;
+  for (int i = 1; i < 3; i++)
+    if (!s->lanes[i].busy) { idx = i; break; }
+  if (idx < 0) return fail_msg(OMR_E_CAPACITY, "memory: two batches are already in flight; finish one first");
+  omr_store::Lane& L = s->lanes[idx];
+  cudaStream_t caller = (cudaStream_t)stream;
+  // the lane's stream picks up after whatever the caller already enqueued (its inputs)
+  OMR_CUDA_OK(cudaEventRecord(L.ev_in, caller));
+  OMR_CUDA_OK(cudaStreamWaitEvent(L.stream, L.ev_in, 0));
+  bool fused = true;
+  int rc = s->enqueue(L, d_queries, nq, d_bitmaps, d_query_group, d_max_distance, k, d_rows, d_dist, d_count, L.stream,
+                      &fused);
+  if (rc) return rc;
+  L.caller = caller;
+  L.immediate = false;
+  if (!fused) {
+    // the unfused chain and the exact-only path share scratch between lanes: run them to completion now
+    if ((rc = s->complete(L, L.stream))) return rc;
+    OMR_CUDA_OK(cudaStreamSynchronize(L.stream));
+    L.immediate = true;
+  } else {
+    OMR_CUDA_OK(cudaEventRecord(L.ev_done, L.stream));
+  }
+  L.busy = true;
+  *ticket = idx;
+  return OMR_OK;
+}
+
+int omr_device_search_finish(omr_store* s, int32_t ticket) {
+  if (!s || ticket < 1 || ticket > 2) return fail_msg(OMR_E_INVALID, "memory: omr_device_search_finish: bad ticket %d", ticket);
+  std::lock_guard<std::mutex> lk(s->mu);
+  cudaSetDevice(s->cfg.device);
+  omr_store::Lane& L = s->lanes[ticket];
+  if (!L.busy) return fail_msg(OMR_E_INVALID, "memory: ticket %d is not in flight", ticket);
+  int rc = OMR_OK;
+  if (!L.immediate) {
+    rc = s->complete(L, L.stream);   // waits for the lane, runs the exact fallback if a certificate failed
+    if (rc == OMR_OK) {
+      // later work on the caller's stream is ordered after the lane's results
+      cudaError_t e = cudaEventRecord(L.ev_done, L.stream);
+      if (e == cudaSuccess) e = cudaStreamWaitEvent(L.caller, L.ev_done, 0);
+      if (e != cudaSuccess) rc = fail_cuda(e, "event hand-off", __FILE__, __LINE__);
+    }
+  }
+  L.busy = false;
+  return rc;
+}
+
 int omr_device_merge_topk(omr_store* s, const int64_t* d_in_rows, const double* d_in_dist, int32_t n_shards,
                           int32_t nq, int32_t k, int64_t shard_stride, int64_t* d_rows, double* d_dist, int32_t* d_count, void* stream) {
   if (!s || !d_in_rows || !d_in_dist || !d_rows || !d_dist || !d_count) return fail_msg(OMR_E_INVALID, "memory: omr_device_merge_topk: null argument");
@@ -996,6 +1138,7 @@ int omr_selfjoin(omr_store* s, const omr_selfjoin_opts* o, omr_pair* out, int64_
   if (!o->workspace_id || !o->workspace_id[0]) return fail_msg(OMR_E_WORKSPACE, "memory: workspace_id is required");
   std::lock_guard<std::mutex> lk(s->mu);
   cudaSetDevice(s->cfg.device);
+  if (int drc = s->drain()) return drc;
   *found = 0;
   uint32_t ws;
   if (!s->ws_names.lookup(o->workspace_id, &ws) || s->n == 0) return OMR_OK;
@@ -1116,34 +1259,34 @@ int omr_debug_candidate_keys(omr_store* s, const float* queries, int32_t nq, int
   const int qtile = path == 4 ? 2 * kQueryTile : kQueryTile;
   const int qpad = path != 1 ? ((nq + qtile - 1) / qtile) * qtile : std::max(nq, 8);
   if ((rc = s->w_queries.reserve((size_t)nq * s->dim))) return rc;
-  if ((rc = s->w_qn.reserve((size_t)qpad * s->pitch))) return rc;
-  if ((rc = s->w_qnorm2.reserve((size_t)qpad))) return rc;
-  if ((rc = s->w_cand.reserve((size_t)qpad * kpq))) return rc;
+  if ((rc = s->lanes[0].qn.reserve((size_t)qpad * s->pitch))) return rc;
+  if ((rc = s->lanes[0].qnorm2.reserve((size_t)qpad))) return rc;
+  if ((rc = s->lanes[0].cand.reserve((size_t)qpad * kpq))) return rc;
   if ((rc = s->ensure_live(st))) return rc;
   OMR_CUDA_OK(cudaMemcpyAsync(s->w_queries.p, queries, (size_t)nq * s->dim * 4, cudaMemcpyHostToDevice, st));
-  if ((rc = launch_prep_queries(s->w_queries.p, nq, qpad, s->dim, s->pitch, s->w_qn.p, s->w_qnorm2.p, st))) return rc;
+  if ((rc = launch_prep_queries(s->w_queries.p, nq, qpad, s->dim, s->pitch, s->lanes[0].qn.p, s->lanes[0].qnorm2.p, st))) return rc;
   if (path == 1) {
     for (int q0 = 0; q0 < nq; q0 += 8) {
       const int c = std::min(8, nq - q0);
-      if ((rc = launch_score_stream(s->view(), s->w_qn.p + (size_t)q0 * s->pitch, c, n_tiles, S, s->w_live.p,
-                                    (int)s->words(), nullptr, s->w_cand.p + (size_t)q0 * kpq, s->num_sms, st)))
+      if ((rc = launch_score_stream(s->view(), s->lanes[0].qn.p + (size_t)q0 * s->pitch, c, n_tiles, S, s->w_live.p,
+                                    (int)s->words(), nullptr, s->lanes[0].cand.p + (size_t)q0 * kpq, s->num_sms, st)))
         return rc;
     }
   } else {
-    if (s->tmap_q_ptr != s->w_qn.p || s->tmap_q_rows != s->w_qn.n / s->pitch) {
-      if ((rc = s->make_tmap(&s->tmap_q, s->w_qn.p, s->w_qn.n / s->pitch, kQueryTile))) return rc;
-      s->tmap_q_ptr = s->w_qn.p;
-      s->tmap_q_rows = s->w_qn.n / s->pitch;
+    if (s->lanes[0].tmap_q_ptr != s->lanes[0].qn.p || s->lanes[0].tmap_q_rows != s->lanes[0].qn.n / s->pitch) {
+      if ((rc = s->make_tmap(&s->lanes[0].tmap_q, s->lanes[0].qn.p, s->lanes[0].qn.n / s->pitch, kQueryTile))) return rc;
+      s->lanes[0].tmap_q_ptr = s->lanes[0].qn.p;
+      s->lanes[0].tmap_q_rows = s->lanes[0].qn.n / s->pitch;
     }
     if (path == 4)
-      rc = launch_score_umma2(s->tmap_q, s->tmap_rows_a, nq, qpad / (2 * kQueryTile), n_tiles, s->pitch / kBlockK, S,
-                              s->w_live.p, (int)s->words(), nullptr, s->w_cand.p, s->num_sms, st);
+      rc = launch_score_umma2(s->lanes[0].tmap_q, s->tmap_rows_a, nq, qpad / (2 * kQueryTile), n_tiles, s->pitch / kBlockK, S,
+                              s->w_live.p, (int)s->words(), nullptr, s->lanes[0].cand.p, s->num_sms, st);
     else
-      rc = launch_score_umma(s->tmap_q, s->tmap_rows_b, nq, qpad / kQueryTile, n_tiles, s->pitch / kBlockK, S,
-                             s->w_live.p, (int)s->words(), nullptr, s->w_cand.p, s->num_sms, st);
+      rc = launch_score_umma(s->lanes[0].tmap_q, s->tmap_rows_b, nq, qpad / kQueryTile, n_tiles, s->pitch / kBlockK, S,
+                             s->w_live.p, (int)s->words(), nullptr, s->lanes[0].cand.p, s->num_sms, st);
     if (rc) return rc;
   }
-  OMR_CUDA_OK(cudaMemcpyAsync(out_keys, s->w_cand.p, (size_t)nq * kpq * 4, cudaMemcpyDeviceToHost, st));
+  OMR_CUDA_OK(cudaMemcpyAsync(out_keys, s->lanes[0].cand.p, (size_t)nq * kpq * 4, cudaMemcpyDeviceToHost, st));
   OMR_CUDA_OK(cudaStreamSynchronize(st));
   return OMR_OK;
 }
@@ -1168,8 +1311,8 @@ int omr_debug_post_timing(omr_store* s, int64_t* out, int32_t nq) {
   if (!s || !out) return fail_msg(OMR_E_INVALID, "memory: null argument");
   std::lock_guard<std::mutex> lk(s->mu);
   cudaSetDevice(s->cfg.device);
-  if (!s->w_timing.p || s->w_timing.n < (size_t)nq * 8) return fail_msg(OMR_E_INVALID, "memory: post timing was not recorded (set OMR_POST_TIMING=1)");
-  OMR_CUDA_OK(cudaMemcpy(out, s->w_timing.p, (size_t)nq * 8 * sizeof(long long), cudaMemcpyDeviceToHost));
+  if (!s->lanes[0].timing.p || s->lanes[0].timing.n < (size_t)nq * 8) return fail_msg(OMR_E_INVALID, "memory: post timing was not recorded (set OMR_POST_TIMING=1)");
+  OMR_CUDA_OK(cudaMemcpy(out, s->lanes[0].timing.p, (size_t)nq * 8 * sizeof(long long), cudaMemcpyDeviceToHost));
   return OMR_OK;
 }
 

@@ -49,8 +49,8 @@ class ShardedRecall:
         self.device = torch.device("cuda", device)
         self._buf = {}
 
-    def _buffers(self, nq: int, k: int):
-        key = (nq, k)
+    def _buffers(self, nq: int, k: int, slot: int = 0):
+        key = (nq, k, slot)
         if key not in self._buf:
             d = self.device
             # rows and distances of one rank live in ONE buffer [2][nq][k] (int64 / float64 views), so the
@@ -73,6 +73,31 @@ class ShardedRecall:
                                  d_max_distance, stream)
         if self.world == 1:
             return b["lr"], b["ld"], b["lc"]
+        dist.all_gather_into_tensor(b["gathered"], b["local"], group=self.group)
+        g = b["gathered"]
+        self.store.device_merge_topk(g[:, 0], g[:, 1].view(torch.float64), self.world, nq, k, b["r"], b["d"], b["c"],
+                                     stream, shard_stride=2 * nq * k)
+        return b["r"], b["d"], b["c"]
+
+    # Pipelined form: begin() enqueues the local search of a batch and returns; finish() waits for it,
+    # then exchanges and merges.  With two batches in flight (slots 0 and 1) the select / rescore tail,
+    # the allgather and the merge of batch i all run underneath the scorer of batch i+1.
+    def begin(self, d_queries: torch.Tensor, k: int, slot: int, d_bitmaps=None, d_query_group=None,
+              d_max_distance=None):
+        nq = d_queries.shape[0]
+        b = self._buffers(nq, k, slot)
+        stream = torch.cuda.current_stream(self.device).cuda_stream
+        ticket = self.store.device_search_begin(d_queries, k, b["lr"], b["ld"], b["lc"], d_bitmaps, 0, d_query_group,
+                                                d_max_distance, stream)
+        return (ticket, nq, k, slot)
+
+    def finish(self, handle):
+        ticket, nq, k, slot = handle
+        b = self._buffers(nq, k, slot)
+        self.store.device_search_finish(ticket)
+        if self.world == 1:
+            return b["lr"], b["ld"], b["lc"]
+        stream = torch.cuda.current_stream(self.device).cuda_stream
         dist.all_gather_into_tensor(b["gathered"], b["local"], group=self.group)
         g = b["gathered"]
         self.store.device_merge_topk(g[:, 0], g[:, 1].view(torch.float64), self.world, nq, k, b["r"], b["d"], b["c"],

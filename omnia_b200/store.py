@@ -337,6 +337,20 @@ class GPUMemoryStore:
                                             p(d_max_distance), k, d_rows.data_ptr(), d_dist.data_ptr(),
                                             d_count.data_ptr(), stream))
 
+    def device_search_begin(self, d_queries, k: int, d_rows, d_dist, d_count, d_bitmaps=None, n_groups: int = 0,
+                            d_query_group=None, d_max_distance=None, stream: int = 0) -> int:
+        """omr_device_search_begin: enqueue a batch, return its ticket at once (at most two in flight)."""
+        nq = d_queries.shape[0]
+        p = lambda t: None if t is None else t.data_ptr()
+        ticket = C.c_int32(0)
+        L.check(self._lib.omr_device_search_begin(self._h, d_queries.data_ptr(), nq, p(d_bitmaps), n_groups,
+                                                  p(d_query_group), p(d_max_distance), k, d_rows.data_ptr(),
+                                                  d_dist.data_ptr(), d_count.data_ptr(), stream, C.byref(ticket)))
+        return ticket.value
+
+    def device_search_finish(self, ticket: int) -> None:
+        L.check(self._lib.omr_device_search_finish(self._h, ticket))
+
     def device_merge_topk(self, d_in_rows, d_in_dist, n_shards: int, nq: int, k: int, d_rows, d_dist, d_count,
                           stream: int = 0, shard_stride: int = 0) -> None:
         L.check(self._lib.omr_device_merge_topk(self._h, d_in_rows.data_ptr(), d_in_dist.data_ptr(), n_shards, nq, k,

@@ -62,7 +62,7 @@ def small():
     corpus = synth.gauss_unit(n, dim)
     with GPUMemoryStore(dim, n) as s:
         s.bulk_load(corpus)
-        for nq in (1, 2, 4, 8, 16, 64, 128, 256, 512, 1024):
+        for nq in [int(x) for x in os.environ.get("BATCHES", "1,2,4,8,16,64,128,256,512,1024").split(",")]:
             q = torch.from_numpy(synth.queries_from(corpus, nq)).cuda()
             ms, sc, st = timed_search(s, q, 10)
             bytes_alg = n * dim * 2

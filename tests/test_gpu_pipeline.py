@@ -1,0 +1,52 @@
+"""omr_device_search_begin / _finish: two batches in flight must give exactly the answers of the
+synchronous entry point, including batches that need the exact fallback or the unfused chain."""
+import numpy as np
+import pytest
+import torch
+
+from omnia_b200 import GPUMemoryStore, RecallError, synth
+
+pytestmark = pytest.mark.gpu
+
+
+def outs(nq, k):
+    return (torch.empty((nq, k), dtype=torch.int64, device="cuda"), torch.empty((nq, k), dtype=torch.float64, device="cuda"),
+            torch.empty(nq, dtype=torch.int32, device="cuda"))
+
+
+@pytest.mark.parametrize("n,dim,nq,k,path", [(30_000, 256, 200, 10, 0), (30_000, 256, 5, 10, 0), (8_000, 128, 40, 200, 0),
+                                             (5_000, 64, 16, 10, 3), (20_000, 384, 130, 100, 2)])
+def test_pipelined_equals_synchronous(n, dim, nq, k, path):
+    corpus = synth.clustered(n, dim) if k == 10 and path == 0 else synth.gauss_unit(n, dim)
+    batches = [torch.from_numpy(synth.queries_from(corpus, nq, seed=s)).cuda() for s in range(5)]
+    with GPUMemoryStore(dim, n, force_path=path) as s:
+        s.bulk_load(corpus)
+        want = []
+        for b in batches:
+            o = outs(nq, k)
+            s.device_search(b, k, *o)
+            torch.cuda.synchronize()
+            want.append([t.cpu().numpy().copy() for t in o])
+        got, o2 = [], [outs(nq, k), outs(nq, k)]
+        stream = torch.cuda.current_stream().cuda_stream
+        pending = None
+        for i, b in enumerate(batches):
+            t = s.device_search_begin(b, k, *o2[i & 1], stream=stream)
+            if pending is not None:
+                s.device_search_finish(pending[0])
+                torch.cuda.synchronize()
+                got.append([x.cpu().numpy().copy() for x in o2[pending[1]]])
+            pending = (t, i & 1)
+        s.device_search_finish(pending[0])
+        torch.cuda.synchronize()
+        got.append([x.cpu().numpy().copy() for x in o2[pending[1]]])
+        for w, g in zip(want, got):
+            assert np.array_equal(w[2], g[2]) and np.array_equal(w[0], g[0]) and np.array_equal(w[1], g[1])
+        # a third begin without a finish is refused, and a stale ticket too
+        t1 = s.device_search_begin(batches[0], k, *o2[0], stream=stream)
+        t2 = s.device_search_begin(batches[1], k, *o2[1], stream=stream)
+        with pytest.raises(RecallError, match="already in flight"):
+            s.device_search_begin(batches[2], k, *outs(nq, k), stream=stream)
+        s.device_search_finish(t1); s.device_search_finish(t2)
+        with pytest.raises(RecallError, match="not in flight"):
+            s.device_search_finish(t1)
