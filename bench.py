@@ -49,50 +49,62 @@ def measured_peaks():
 
 
 class ClockSampler:
-    """nvidia-smi clocks and throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
-    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
-         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
-         "clocks_event_reasons.sw_power_cap")
+    """SM clocks and throttle reasons DURING the timed region (B200_PROFILING.md), sampled through NVML
+    every few milliseconds (the timed region of a default run is only tens of milliseconds long)."""
 
-    def __init__(self, gpu_index: int):
-        self.idx = gpu_index
-        self.proc = None
-        self.lines = []
+    def __init__(self, gpu_index: int, period_s: float = 0.004):
+        self.idx, self.period = gpu_index, period_s
+        self.sm, self.reasons, self.stop_flag, self.thread, self.h = [], set(), False, None, None
+        try:
+            import pynvml
+            self.nv = pynvml
+            pynvml.nvmlInit()
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(self._physical_index(gpu_index))
+            self.smax = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception as e:  # noqa: BLE001
+            self.err = repr(e)
+            self.h = None
+
+    @staticmethod
+    def _physical_index(i: int) -> int:
+        vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+        if vis:
+            ids = [x for x in vis.split(",") if x.strip() != ""]
+            if i < len(ids) and ids[i].strip().isdigit():
+                return int(ids[i])
+        return i
+
+    def _loop(self):
+        nv = self.nv
+        names = {"hw_slowdown": getattr(nv, "nvmlClocksEventReasonHwSlowdown", 0x8),
+                 "hw_thermal_slowdown": getattr(nv, "nvmlClocksEventReasonHwThermalSlowdown", 0x40),
+                 "sw_thermal_slowdown": getattr(nv, "nvmlClocksEventReasonSwThermalSlowdown", 0x20),
+                 "sw_power_cap": getattr(nv, "nvmlClocksEventReasonSwPowerCap", 0x4)}
+        get_reasons = getattr(nv, "nvmlDeviceGetCurrentClocksEventReasons", None) or nv.nvmlDeviceGetCurrentClocksThrottleReasons
+        while not self.stop_flag:
+            try:
+                self.sm.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                r = get_reasons(self.h)
+                for nm, bit in names.items():
+                    if r & bit:
+                        self.reasons.add(nm)
+            except Exception:  # noqa: BLE001
+                pass
+            time.sleep(self.period)
 
     def start(self):
-        try:
-            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                          "-i", str(self.idx), "-lms", "100"], stdout=subprocess.PIPE, text=True)
-            self.t = threading.Thread(target=self._read, daemon=True)
-            self.t.start()
-        except OSError:
-            self.proc = None
-
-    def _read(self):
-        for ln in self.proc.stdout:
-            self.lines.append(ln.strip())
+        if self.h is None:
+            return
+        self.thread = threading.Thread(target=self._loop, daemon=True)
+        self.thread.start()
 
     def stop(self):
-        if not self.proc:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        time.sleep(0.15)
-        self.proc.terminate()
-        self.t.join(timeout=2)
-        sm, smax, reasons = [], [], set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for ln in self.lines:
-            f = [x.strip() for x in ln.split(",")]
-            if len(f) < 9:
-                continue
-            try:
-                sm.append(float(f[1])); smax.append(float(f[2]))
-            except ValueError:
-                continue
-            for nm, v in zip(names, f[5:9]):
-                if v.lower().startswith("active"):
-                    reasons.add(nm)
-        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(smax) if smax else None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+        if self.h is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvml unavailable: " + getattr(self, "err", "")]}
+        self.stop_flag = True
+        self.thread.join(timeout=2)
+        return {"sm_mhz": float(np.median(self.sm)) if self.sm else None, "sm_max_mhz": float(self.smax),
+                "reasons": sorted(self.reasons), "samples": len(self.sm)}
 
 
 # ------------------------------------------------------------------ CPU baseline / reference arm
@@ -220,7 +232,7 @@ def main():
             return
         pending = None
         for i in range(first, first + count):
-            h = sr.begin(dq[i % N_BATCHES], TOPK, i & 1)
+            h = sr.begin(dq[i % N_BATCHES], TOPK, i & 3)
             if pending is not None:
                 sr.finish(pending)
             pending = h
@@ -229,20 +241,26 @@ def main():
     run_steps(0, args.warmup)
     torch.cuda.synchronize()
     barrier()
-    # unpipelined latency of one step (one batch start to finish), for the record
+    # Unpipelined pass: latency of one step, and the scorer kernel's own duration (CUDA events on its
+    # stream, recorded by the library around that one kernel; under the pipeline kernels of two batches
+    # overlap, so the kernel is timed here, back to back, right before the pipelined measurement).
+    sr.store.set_profiling(True)
     lat0, lat1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     lat0.record(stream)
-    for i in range(5):
+    n_lat = max(5, min(args.steps, 20))
+    for i in range(n_lat):
         sr.search_device(dq[i % N_BATCHES], TOPK)
     lat1.record(stream)
     torch.cuda.synchronize()
-    latency_ms = lat0.elapsed_time(lat1) / 5
+    latency_ms = lat0.elapsed_time(lat1) / n_lat
+    stp = sr.store.stats()
+    scorer_ms = stp.scorer_ms_sum / max(1, stp.scorer_timed)
+    sr.store.set_profiling(False)
     barrier()
 
     # ---- value: inputs resident in HBM, device timing, max over ranks
     sampler = ClockSampler(local_rank)
     st0 = sr.store.stats()
-    sr.store.set_profiling(True)
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     if rank == 0:
         sampler.start()
@@ -256,14 +274,12 @@ def main():
     ms_total = ev0.elapsed_time(ev1)
     clocks = sampler.stop() if rank == 0 else None
     st1 = sr.store.stats()
-    sr.store.set_profiling(False)
     t = torch.tensor([ms_total], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms_step = float(t.item()) / args.steps
     value = NQ / (ms_step / 1e3)
     launches = int(st1.kernel_launches - st0.kernel_launches)   # every kernel the library enqueued, merge included
-    scorer_ms = st1.scorer_ms_sum / max(1, st1.scorer_timed)
 
     # ---- e2e: host buffers through the C ABI (N=1) / pinned H2D + D2H around the sharded search (N>1)
     out = (np.empty((NQ, TOPK), np.int64), np.empty((NQ, TOPK), np.float64), np.empty(NQ, np.int32))

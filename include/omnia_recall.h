@@ -270,6 +270,9 @@ OMR_API const char* omr_kind_name(const omr_store* s, uint32_t kind);
  * candidate keys, [nq][ceil(n/256) * (256/S) * 2] int32 on the host.  A key is the
  * order-preserving int32 image of the bf16-accurate cosine with its low 8 bits replaced by
  * the row's offset inside its S-row sub-bucket; INT32_MIN = no eligible row. */
+/* Test hook: mean device time (ms) of `iters` back-to-back launches of ONE scorer (path 1, 2 or 4)
+ * over every live row, the queries being the store's own first nq rows; nothing downstream runs. */
+OMR_API int omr_debug_time_scorer(omr_store* s, int32_t nq, int32_t path, int32_t S, int32_t iters, float* ms_out);
 /* Test hook: per-query clock64 stamps [nq][8] of the fused post-processing kernel's phases from the
  * last search (only recorded when the store was opened with OMR_POST_TIMING=1 in the environment). */
 OMR_API int omr_debug_post_timing(omr_store* s, int64_t* out, int32_t nq);

@@ -108,6 +108,7 @@ SIGNATURES = {
     "omr_get_stats": (C.c_int, [C.c_void_p, C.POINTER(Stats)]),
     "omr_set_profiling": (C.c_int, [C.c_void_p, C.c_int32]),
     "omr_kind_name": (C.c_char_p, [C.c_void_p, C.c_uint32]),
+    "omr_debug_time_scorer": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.POINTER(C.c_float)]),
     "omr_debug_post_timing": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32]),
     "omr_debug_candidate_keys": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_void_p,
                                            C.c_int64]),

@@ -25,6 +25,9 @@
 // Roofline: tensor for >= ~256 queries (2*Q*N*D flops per launch), HBM below that
 // (the bf16 matrix is read once per launch: consecutive CTAs take the query tiles
 // of the same row tile, so its K blocks are served from L2 after the first read).
+#include <algorithm>
+#include <cstdlib>
+
 #include "kernels.cuh"
 #include "ptx.cuh"
 
@@ -122,6 +125,8 @@ struct KernelArgs {
   int64_t n_work;  // total (a tile, b tile) work items
   int k_blocks;
   int nq;          // real queries; tiles are padded with zero queries beyond it
+  int n_stages;    // TMA ring depth in use (<= kStages); experiments only, normally kStages
+  int exp;         // experiment bits (OMR_UMMA_EXP): 1 = epilogue only waits/arrives, 2 = MMA issue without TMA
   // recall
   const uint32_t* bitmaps;
   int words_per_group;
@@ -185,7 +190,7 @@ __global__ void __launch_bounds__(kNumThreads, 1)
 
   if (warp == 0) {
     // ---------------- TMA producer ----------------
-    if (lane == 0) {
+    if (lane == 0 && !(args.exp & 2)) {
       int stage = 0;
       uint32_t phase = 0;
       for (int64_t w = blockIdx.x; w < args.n_work; w += gridDim.x) {
@@ -198,7 +203,7 @@ __global__ void __launch_bounds__(kNumThreads, 1)
                            a_tile * kQueryTile, ptx::kEvictLast);
           ptx::tma_load_2d(smem_b + stage * kBBytes, &tmap_b, &bars->full[stage], kb * kBlockK,
                            b_tile * kTileRows, kSelfJoin ? ptx::kEvictLast : ptx::kEvictNormal);
-          if (++stage == kStages) {
+          if (++stage == args.n_stages) {
             stage = 0;
             phase ^= 1;
           }
@@ -216,7 +221,7 @@ __global__ void __launch_bounds__(kNumThreads, 1)
       ptx::mbar_wait(&bars->tmem_empty[as], aphase ^ 1);
       ptx::tc_fence_after_sync();
       for (int kb = 0; kb < args.k_blocks; kb++) {
-        ptx::mbar_wait(&bars->full[stage], phase);
+        if (!(args.exp & 2)) ptx::mbar_wait(&bars->full[stage], phase);
         ptx::tc_fence_after_sync();
         if (lane == 0) {
           const uint64_t da = ptx::make_smem_desc_sw128(ptx::smem_u32(smem_a + stage * kABytes));
@@ -224,11 +229,11 @@ __global__ void __launch_bounds__(kNumThreads, 1)
 #pragma unroll
           for (int k = 0; k < kBlockK / 16; k++)
             ptx::umma_bf16(tmem_base + as * kTileRows, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
-          ptx::umma_commit(&bars->empty[stage]);  // frees the smem stage when these MMAs retire
+          if (!(args.exp & 2)) ptx::umma_commit(&bars->empty[stage]);  // frees the smem stage when these MMAs retire
           if (kb == args.k_blocks - 1) ptx::umma_commit(&bars->tmem_full[as]);
         }
         __syncwarp();
-        if (++stage == kStages) {
+        if (++stage == args.n_stages) {
           stage = 0;
           phase ^= 1;
         }
@@ -259,7 +264,7 @@ __global__ void __launch_bounds__(kNumThreads, 1)
       ptx::mbar_wait(&bars->tmem_full[as], aphase);
       ptx::tc_fence_after_sync();
 #pragma unroll 1
-      for (int c = 0; c < kTileRows / 32; c += 2) {
+      for (int c = 0; c < ((args.exp & 1) ? 0 : kTileRows / 32); c += 2) {
         uint32_t v0[32], v1[32];
         __syncwarp();  // the epilogue's data-dependent branches must reconverge before a .sync.aligned load
         ptx::tmem_ld_32x32(lane_addr + as * kTileRows + c * 32, v0);
@@ -464,6 +469,10 @@ int launch_recall_s(const CUtensorMap& tmap_q, const CUtensorMap& tmap_rows, int
   a.query_group = query_group;
   a.cand_keys = cand_keys;
   a.keys_per_query = (int64_t)n_tiles * (kTileRows / S) * 2;
+  a.n_stages = kStages;
+  a.exp = 0;
+  if (const char* e = getenv("OMR_UMMA_EXP")) a.exp = atoi(e);
+  if (const char* e = getenv("OMR_UMMA_STAGES")) a.n_stages = std::max(2, std::min(kStages, atoi(e)));
   auto kern = score_umma_kernel<false, S>;
   OMR_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
   int grid = num_sms;
@@ -519,6 +528,8 @@ int launch_selfjoin_umma(const CUtensorMap& tmap_a, const CUtensorMap& tmap_b, i
   a.pe.cap = cap;
   a.pe.count = pair_count;
   a.pe.threshold = threshold;
+  a.n_stages = kStages;
+  a.exp = 0;
   auto kern = score_umma_kernel<true, 256>;
   OMR_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
   int grid = num_sms;

@@ -676,7 +676,14 @@ int omr_store::host_search(const float* queries, int nq, const omr_filter* filte
   float* pq = reinterpret_cast<float*>(pin_in.p);
   double* pm = reinterpret_cast<double*>(pin_in.p + ((qbytes + 7) & ~size_t(7)));
   int32_t* pg = reinterpret_cast<int32_t*>(reinterpret_cast<uint8_t*>(pm) + (size_t)nq * 8);
-  memcpy(pq, queries, qbytes);
+  // A caller whose query buffer is already page-locked (cudaHostAlloc / cudaHostRegister) is copied from
+  // directly; pageable memory goes through the store's pinned staging buffer.
+  const float* qsrc = pq;
+  {
+    cudaPointerAttributes attr{};
+    if (cudaPointerGetAttributes(&attr, queries) == cudaSuccess && attr.type == cudaMemoryTypeHost) qsrc = queries;
+    else { cudaGetLastError(); memcpy(pq, queries, qbytes); }
+  }
   for (int i = 0; i < nq; i++) {
     const int g = query_filter ? query_filter[i] : 0;
     if (g < 0 || g >= n_filters) return fail_msg(OMR_E_INVALID, "memory: query %d names filter %d of %d", i, g, n_filters);
@@ -691,7 +698,7 @@ int omr_store::host_search(const float* queries, int nq, const omr_filter* filte
   if ((rc = w_out_rows.reserve((size_t)nq * k))) return rc;
   if ((rc = w_out_dist.reserve((size_t)nq * k))) return rc;
   if ((rc = w_out_count.reserve((size_t)nq))) return rc;
-  OMR_CUDA_OK(cudaMemcpyAsync(w_queries.p, pq, qbytes, cudaMemcpyHostToDevice, stream));
+  OMR_CUDA_OK(cudaMemcpyAsync(w_queries.p, qsrc, qbytes, cudaMemcpyHostToDevice, stream));
   OMR_CUDA_OK(cudaMemcpyAsync(w_qgroup.p, pg, (size_t)nq * 4, cudaMemcpyHostToDevice, stream));
   OMR_CUDA_OK(cudaMemcpyAsync(w_maxdist.p, pm, (size_t)nq * 8, cudaMemcpyHostToDevice, stream));
   OMR_CUDA_OK(cudaMemcpyAsync(w_filters.p, df.data(), (size_t)n_filters * sizeof(DeviceFilter), cudaMemcpyHostToDevice, stream));
@@ -1304,6 +1311,55 @@ int omr_get_stats(const omr_store* s, omr_stats* out) {
   out->num_sms = s->num_sms;
   out->scorer_ms_sum = s->scorer_ms_sum;
   out->scorer_timed = s->scorer_timed;
+  return OMR_OK;
+}
+
+// Diagnostics: device time (ms, CUDA events) of `iters` back-to-back launches of one scorer over the
+// whole store with nq random-free (zero) queries already prepared; nothing downstream runs.
+int omr_debug_time_scorer(omr_store* s, int32_t nq, int32_t path, int32_t S, int32_t iters, float* ms_out) {
+  if (!s || !ms_out || iters < 1) return fail_msg(OMR_E_INVALID, "memory: omr_debug_time_scorer: bad argument");
+  std::lock_guard<std::mutex> lk(s->mu);
+  cudaSetDevice(s->cfg.device);
+  cudaStream_t st = s->stream;
+  omr_store::Lane& L = s->lanes[0];
+  int rc;
+  const int n_tiles = (int)((s->n + kTileRows - 1) / kTileRows);
+  const int64_t kpq = (int64_t)n_tiles * (kTileRows / S) * 2;
+  const int qtile = path == 4 ? 2 * kQueryTile : kQueryTile;
+  const int qpad = path != 1 ? ((nq + qtile - 1) / qtile) * qtile : std::max(nq, 8);
+  if ((rc = s->w_queries.reserve((size_t)nq * s->dim))) return rc;
+  if ((rc = L.qn.reserve((size_t)qpad * s->pitch))) return rc;
+  if ((rc = L.qnorm2.reserve((size_t)qpad))) return rc;
+  if ((rc = L.cand.reserve((size_t)qpad * kpq))) return rc;
+  if ((rc = s->ensure_live(st))) return rc;
+  // queries = the store's own first rows (real data: all-zero operands would flatter the power-limited clocks)
+  if (nq > s->n) return fail_msg(OMR_E_INVALID, "memory: omr_debug_time_scorer needs nq <= rows");
+  OMR_CUDA_OK(cudaMemcpy2DAsync(s->w_queries.p, (size_t)s->dim * 4, s->d_f32, (size_t)s->pitch * 4, (size_t)s->dim * 4, nq,
+                                cudaMemcpyDeviceToDevice, st));
+  if ((rc = launch_prep_queries(s->w_queries.p, nq, qpad, s->dim, s->pitch, L.qn.p, L.qnorm2.p, st))) return rc;
+  if (L.tmap_q_ptr != L.qn.p || L.tmap_q_rows != L.qn.n / s->pitch) {
+    if ((rc = s->make_tmap(&L.tmap_q, L.qn.p, L.qn.n / s->pitch, kQueryTile))) return rc;
+    L.tmap_q_ptr = L.qn.p;
+    L.tmap_q_rows = L.qn.n / s->pitch;
+  }
+  for (int it = -1; it < iters; it++) {
+    if (it == 0) OMR_CUDA_OK(cudaEventRecord(L.ev0, st));
+    if (path == 4)
+      rc = launch_score_umma2(L.tmap_q, s->tmap_rows_a, nq, qpad / (2 * kQueryTile), n_tiles, s->pitch / kBlockK, S,
+                              s->w_live.p, (int)s->words(), nullptr, L.cand.p, s->num_sms, st);
+    else if (path == 2)
+      rc = launch_score_umma(L.tmap_q, s->tmap_rows_b, nq, qpad / kQueryTile, n_tiles, s->pitch / kBlockK, S,
+                             s->w_live.p, (int)s->words(), nullptr, L.cand.p, s->num_sms, st);
+    else
+      rc = launch_score_stream(s->view(), L.qn.p, std::min(nq, 8), n_tiles, S, s->w_live.p, (int)s->words(), nullptr,
+                               L.cand.p, s->num_sms, st);
+    if (rc) return rc;
+  }
+  OMR_CUDA_OK(cudaEventRecord(L.ev1, st));
+  OMR_CUDA_OK(cudaStreamSynchronize(st));
+  float ms = 0;
+  OMR_CUDA_OK(cudaEventElapsedTime(&ms, L.ev0, L.ev1));
+  *ms_out = ms / iters;
   return OMR_OK;
 }
 

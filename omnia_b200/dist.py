@@ -48,6 +48,10 @@ class ShardedRecall:
         self.store = GPUMemoryStore(dim, max(1, n_local), device=device, row_base=base, row_stride=stride, **store_kw)
         self.device = torch.device("cuda", device)
         self._buf = {}
+        # exchange + merge of a finished batch run on their own stream, so that the next batch's scorer
+        # (ordered after the caller's stream at begin()) never waits behind a collective
+        self._comm = torch.cuda.Stream(device=self.device) if torch.cuda.is_available() else None
+        self._slot_ev = {}   # slot -> event of the last exchange that read / wrote the slot's buffers
 
     def _buffers(self, nq: int, k: int, slot: int = 0):
         key = (nq, k, slot)
@@ -80,29 +84,44 @@ class ShardedRecall:
         return b["r"], b["d"], b["c"]
 
     # Pipelined form: begin() enqueues the local search of a batch and returns; finish() waits for it,
-    # then exchanges and merges.  With two batches in flight (slots 0 and 1) the select / rescore tail,
-    # the allgather and the merge of batch i all run underneath the scorer of batch i+1.
+    # then exchanges and merges on the communication stream.  With two batches in flight the select /
+    # rescore tail, the allgather and the merge of batch i all run underneath the scorer of batch i+1.
+    # `slot` names a set of result buffers; rotate through >= 4 slots so a new batch never has to wait
+    # for the exchange that last used its buffers.
     def begin(self, d_queries: torch.Tensor, k: int, slot: int, d_bitmaps=None, d_query_group=None,
               d_max_distance=None):
         nq = d_queries.shape[0]
         b = self._buffers(nq, k, slot)
-        stream = torch.cuda.current_stream(self.device).cuda_stream
+        cur = torch.cuda.current_stream(self.device)
+        if slot in self._slot_ev:               # the slot's previous exchange must be done with its buffers
+            cur.wait_event(self._slot_ev[slot])
+        stream = cur.cuda_stream
         ticket = self.store.device_search_begin(d_queries, k, b["lr"], b["ld"], b["lc"], d_bitmaps, 0, d_query_group,
                                                 d_max_distance, stream)
         return (ticket, nq, k, slot)
 
     def finish(self, handle):
+        """Completes a batch started with begin().  Returns (rows, dist, count, event): with more than
+        one shard the exchange and merge are enqueued on the store's communication stream and `event`
+        marks their completion (wait on it, or synchronise the device, before reading the tensors)."""
         ticket, nq, k, slot = handle
         b = self._buffers(nq, k, slot)
         self.store.device_search_finish(ticket)
+        cur = torch.cuda.current_stream(self.device)
         if self.world == 1:
-            return b["lr"], b["ld"], b["lc"]
-        stream = torch.cuda.current_stream(self.device).cuda_stream
-        dist.all_gather_into_tensor(b["gathered"], b["local"], group=self.group)
-        g = b["gathered"]
-        self.store.device_merge_topk(g[:, 0], g[:, 1].view(torch.float64), self.world, nq, k, b["r"], b["d"], b["c"],
-                                     stream, shard_stride=2 * nq * k)
-        return b["r"], b["d"], b["c"]
+            ev = torch.cuda.Event()
+            ev.record(cur)
+            return b["lr"], b["ld"], b["lc"], ev
+        self._comm.wait_stream(cur)            # the local answer is ordered on `cur` by device_search_finish
+        with torch.cuda.stream(self._comm):
+            dist.all_gather_into_tensor(b["gathered"], b["local"], group=self.group)
+            g = b["gathered"]
+            self.store.device_merge_topk(g[:, 0], g[:, 1].view(torch.float64), self.world, nq, k, b["r"], b["d"],
+                                         b["c"], self._comm.cuda_stream, shard_stride=2 * nq * k)
+            ev = torch.cuda.Event()
+            ev.record(self._comm)
+        self._slot_ev[slot] = ev
+        return b["r"], b["d"], b["c"], ev
 
     def close(self):
         self.store.close()
