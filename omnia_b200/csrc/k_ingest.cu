@@ -110,6 +110,12 @@ int launch_ingest_rows(const float* src, int64_t n, int dim, int pitch, int64_t 
 int launch_prep_queries(const float* q, int nq, int qpad, int dim, int pitch, __nv_bfloat16* qn, double* qnorm2,
                         cudaStream_t st) {
   const int warps = 8;
+  static bool carveout_set = false;  // see k_post.cu: query preparation of batch i+1 runs beside scorer CTAs of batch i
+  if (!carveout_set) {
+    OMR_CUDA_OK(cudaFuncSetAttribute(normalize_rows_kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                     cudaSharedmemCarveoutMaxShared));
+    carveout_set = true;
+  }
   normalize_rows_kernel<<<(unsigned)((qpad + warps - 1) / warps), warps * 32, 0, st>>>(
       q, nq, dim, pitch, 0, qn, nullptr, qnorm2, qpad);
   OMR_CUDA_OK(cudaGetLastError());

@@ -511,6 +511,14 @@ int launch_post(const PostArgs& a, cudaStream_t st) {
   const size_t smem = (size_t)a.sh.pitch * sizeof(double) + (size_t)a.sort_cap * 12 + sizeof(PostSmem);
   if (smem > 48 * 1024)
     OMR_CUDA_OK(cudaFuncSetAttribute(post_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  // Same shared-memory carve-out as the scorer (maximum), so that blocks of this kernel can be resident on
+  // an SM next to a scorer CTA of the following batch; an SM cannot hold two carve-out configurations.
+  static bool carveout_set = false;
+  if (!carveout_set) {
+    OMR_CUDA_OK(cudaFuncSetAttribute(post_kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                     cudaSharedmemCarveoutMaxShared));
+    carveout_set = true;
+  }
   post_kernel<<<a.nq, kPostThreads, smem, st>>>(a);
   OMR_CUDA_OK(cudaGetLastError());
   return 0;

@@ -51,7 +51,9 @@ struct __align__(8) PipeBarriers {
   uint32_t tmem_base;
 };
 
-constexpr int kSmemBytes = kStages * kStageBytes + (int)sizeof(PipeBarriers) + 1024;  // +1024: manual alignment
+struct PairStage;
+constexpr int kPairStageBytes = 1024 * 8 + 32;
+constexpr int kSmemBytes = kStages * kStageBytes + (int)sizeof(PipeBarriers) + kPairStageBytes + 1024;  // +1024: manual alignment
 
 // Epilogue of the recall scorer: two best keys per sub-bucket for this thread's query.
 template <int S>
@@ -85,7 +87,16 @@ struct Top2Epilogue {
 };
 
 // Epilogue of the self-join: emit (a, b) for a < b when the approximate cosine clears the
-// (margin-lowered) floor and both rows are members of the join.
+// (margin-lowered) floor and both rows are members of the join.  Pairs are staged in shared
+// memory and flushed once per tile with ONE global atomic per CTA (the pair list is compacted in
+// shared memory first); a pair that finds the stage full goes straight to global memory.
+constexpr int kPairStage = 1024;
+struct PairStage {
+  PairCand buf[kPairStage];
+  unsigned int count;
+  unsigned long long base;
+};
+static_assert(sizeof(PairStage) <= 1024 * 8 + 32, "PairStage outgrew its shared-memory slot");
 struct PairEpilogue {
   const uint32_t* member;  // bitmap over rows
   PairCand* pairs;
@@ -94,6 +105,7 @@ struct PairEpilogue {
   float threshold;
   int32_t row_a;
   bool a_member;
+  PairStage* stage;  // shared memory of this CTA
 
   __device__ __forceinline__ void chunk(int b_tile, int c, const uint32_t (&v)[32]) {
     const int32_t b0 = b_tile * kTileRows + c * 32;
@@ -106,15 +118,32 @@ struct PairEpilogue {
 #pragma unroll
     for (int j = 0; j < 32; j++) pass |= (__uint_as_float(v[j]) >= threshold) ? (1u << j) : 0u;
     pass &= mask;
-    if (pass) {
-#pragma unroll
-      for (int j = 0; j < 32; j++) {
-        if ((pass >> j) & 1u) {
-          const unsigned long long slot = atomicAdd(count, 1ull);
-          if (slot < cap) pairs[slot] = PairCand{row_a, b0 + j};
-        }
+    while (pass) {
+      const int j = __ffs(pass) - 1;
+      pass &= pass - 1;
+      const unsigned int slot = atomicAdd(&stage->count, 1u);
+      if (slot < (unsigned)kPairStage) {
+        stage->buf[slot] = PairCand{row_a, b0 + j};
+      } else {
+        const unsigned long long g = atomicAdd(count, 1ull);
+        if (g < cap) pairs[g] = PairCand{row_a, b0 + j};
       }
     }
+  }
+
+  // All 128 epilogue threads, once per tile (t = thread index inside the epilogue group).
+  __device__ __forceinline__ void flush(int t) {
+    asm volatile("bar.sync 2, 128;" ::: "memory");
+    const unsigned int n = min(stage->count, (unsigned)kPairStage);
+    if (n == 0) return;                       // uniform: every thread read the same count
+    if (t == 0) stage->base = atomicAdd(count, (unsigned long long)n);
+    asm volatile("bar.sync 2, 128;" ::: "memory");
+    const unsigned long long base = stage->base;
+    for (unsigned int i = t; i < n; i += 128)
+      if (base + i < cap) pairs[base + i] = stage->buf[i];
+    asm volatile("bar.sync 2, 128;" ::: "memory");
+    if (t == 0) stage->count = 0;
+    asm volatile("bar.sync 2, 128;" ::: "memory");  // nobody appends for the next tile before the reset
   }
 };
 
@@ -164,8 +193,10 @@ __global__ void __launch_bounds__(kNumThreads, 1)
   uint8_t* smem_a = smem;
   uint8_t* smem_b = smem + kStages * kABytes;
   PipeBarriers* bars = reinterpret_cast<PipeBarriers*>(smem + kStages * kStageBytes);
+  PairStage* pstage = reinterpret_cast<PairStage*>(reinterpret_cast<uint8_t*>(bars) + ((sizeof(PipeBarriers) + 15) & ~size_t(15)));
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (kSelfJoin && threadIdx.x == 0) pstage->count = 0;
 
   if (warp == 0 && lane == 0) {
     ptx::tma_prefetch_desc(&tmap_a);
@@ -247,6 +278,7 @@ __global__ void __launch_bounds__(kNumThreads, 1)
     uint32_t it = 0;
     Top2Epilogue<S> te;
     PairEpilogue pe = args.pe;
+    pe.stage = pstage;
     for (int64_t w = blockIdx.x; w < args.n_work; w += gridDim.x, it++) {
       int a_tile, b_tile;
       decode_work<kSelfJoin>(w, args.n_a_tiles, a_tile, b_tile);
@@ -280,6 +312,7 @@ __global__ void __launch_bounds__(kNumThreads, 1)
       }
       ptx::tc_fence_before_sync();
       ptx::mbar_arrive(&bars->tmem_empty[as]);
+      if (kSelfJoin) pe.flush(t_local);
     }
   }
 

@@ -656,6 +656,12 @@ int launch_merge_topk(const int64_t* in_rows, const double* in_dist, int G, int 
   if (smem > 48 * 1024)
     OMR_CUDA_OK(cudaFuncSetAttribute(merge_topk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   if (shard_stride <= 0) shard_stride = (int64_t)nq * k;
+  static bool carveout_set = false;  // see k_post.cu
+  if (!carveout_set) {
+    OMR_CUDA_OK(cudaFuncSetAttribute(merge_topk_kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                     cudaSharedmemCarveoutMaxShared));
+    carveout_set = true;
+  }
   merge_topk_kernel<<<nq, 256, smem, st>>>(in_rows, in_dist, G, nq, k, shard_stride, P, out_rows, out_dist, out_count);
   OMR_CUDA_OK(cudaGetLastError());
   return 0;
