@@ -32,7 +32,8 @@ DIM = int(os.environ.get("OMNIA_BENCH_DIM", 1536))
 NQ = int(os.environ.get("OMNIA_BENCH_QUERIES", 1024))
 TOPK = int(os.environ.get("OMNIA_BENCH_K", 10))
 N_BATCHES = 4
-METRIC = "recall queries/sec @1Mx1536 top-10"
+METRIC = "recall queries/sec @1Mx1536 top-10" if (N_ROWS, DIM, TOPK) == (1_000_000, 1536, 10) else \
+    f"recall queries/sec @{N_ROWS}x{DIM} top-{TOPK}"
 UNIT = "queries/s"
 
 
@@ -199,7 +200,12 @@ def main():
             dist.barrier(device_ids=[local_rank])
 
     t_setup = time.perf_counter()
-    shard = synth.gauss_unit(N_ROWS, DIM, rank=rank, world=world)
+    local_gen = world > 1 and (N_ROWS > 2_000_000 or os.environ.get("OMNIA_BENCH_LOCALGEN") == "1")
+    if local_gen:   # big sharded stores: every rank draws only its own rows (same distribution, see synth.py)
+        n_local = (N_ROWS - rank + world - 1) // world
+        shard = synth.gauss_unit_local(n_local, DIM, synth.CORPUS_SEED, rank, world)
+    else:
+        shard = synth.gauss_unit(N_ROWS, DIM, rank=rank, world=world)
     sr = ShardedRecall(DIM, N_ROWS, local_rank, force_path=int(os.environ.get("OMNIA_BENCH_PATH", 0)))
     sr.store.bulk_load(shard)
     # query batches: perturbed copies of stored rows, identical on every rank
@@ -223,20 +229,21 @@ def main():
     pipelined = os.environ.get("OMNIA_BENCH_PIPELINE", "1") != "0"
 
     def run_steps(first, count):
-        """`count` steps.  Pipelined: two batches in flight through omr_device_search_begin/_finish, so the
+        """`count` steps.  Pipelined: up to `depth` batches in flight through omr_device_search_begin/_finish, so the
         tail of step i (select, exact rescore, exchange, merge) runs under the scorer of step i+1; every
         step's full answer is complete before run_steps returns."""
         if not pipelined:
             for i in range(first, first + count):
                 sr.search_device(dq[i % N_BATCHES], TOPK)
             return
-        pending = None
+        depth = int(os.environ.get("OMNIA_BENCH_DEPTH", 3))
+        pending = []
         for i in range(first, first + count):
-            h = sr.begin(dq[i % N_BATCHES], TOPK, i & 3)
-            if pending is not None:
-                sr.finish(pending)
-            pending = h
-        sr.finish(pending)
+            pending.append(sr.begin(dq[i % N_BATCHES], TOPK, i & 7))
+            if len(pending) >= depth:
+                sr.finish(pending.pop(0))
+        for h in pending:
+            sr.finish(h)
 
     run_steps(0, args.warmup)
     torch.cuda.synchronize()
@@ -316,7 +323,12 @@ def main():
         achieved = flops / (scorer_ms / 1e3) / 1e12 if scorer_ms > 0 else None
         peak = float(peaks.get("bf16_tflops_sustained", peaks.get("bf16_tflops")))
         roofline = {"bound": "tensor", "kernel": "score_umma_kernel", "achieved": achieved, "peak": peak,
-                    "unit": "TFLOP/s", "frac": (achieved / peak) if achieved else None, "traffic": None,
+                    "unit": "TFLOP/s", "frac": (achieved / peak) if achieved else None,
+                    # dram__bytes_read.sum + dram__bytes_write.sum of one launch, from the ncu --set full capture
+                    # of this same command (profiles/r01_score_umma_ncu_full.txt: 3.0768e9 read + 6.7e7 written
+                    # at sub-bucket 128); only meaningful for the configuration that capture was taken on
+                    "traffic": 3.144e9 if (N_ROWS, DIM, NQ, TOPK, world) == (1_000_000, 1536, 1024, 10, 1) else None,
+                    "algorithmic_bytes": (N_ROWS / world) * DIM * 2 + NQ * DIM * 4 + (N_ROWS / world) / 8,
                     "peak_source": f"bf16_tflops_sustained, {peak_src}: the kernel is timed inside a back-to-back step loop",
                     "frac_of_burst": (achieved / float(peaks["bf16_tflops"])) if achieved else None,
                     "kernel_ms": scorer_ms, "flops_per_launch": flops,
@@ -326,8 +338,8 @@ def main():
             "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "bf16", "data": "synthetic",
             "config": {"workload": workload_name(), "rows": N_ROWS, "dim": DIM, "queries_per_step": NQ, "k": TOPK,
-                       "sharding": f"rows round-robin over {world} GPU(s)",
-                       "pipeline": "2 batches in flight (omr_device_search_begin/_finish)" if pipelined else "none",
+                       "sharding": f"rows round-robin over {world} GPU(s)" + (", shard-local corpus generation" if local_gen else ""),
+                       "pipeline": "%s batches in flight (omr_device_search_begin/_finish)" % os.environ.get("OMNIA_BENCH_DEPTH", 3) if pipelined else "none",
                        "single_step_latency_ms": latency_ms, "scorer_path": int(st1.last_path),
                        "sub_bucket": int(st1.last_sub_bucket), "rescore_width": int(st1.last_rescore_width),
                        "l2": "inputs larger than L2: the bf16 matrix streamed every step is %.2f GB" % (N_ROWS / world * DIM * 2 / 1e9),

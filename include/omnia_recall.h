@@ -154,7 +154,9 @@ typedef struct omr_hit {
  * the cosine_ann CTEs (internal/memory/store.go:240-261,
  * internal/memory/retrieve_multi_tier_hybrid.go:78-96).  query_filter[i] picks the filter
  * of query i (NULL = filter 0 for all).  hits is [nq][k]; counts[i] <= k entries are valid,
- * nearest first, ties by row id. */
+ * nearest first, ties by row id.  Calls made concurrently from several threads are coalesced: the
+ * calls that arrive while a search is running are answered together by ONE pass over the matrix
+ * (the dedup-on-write micro-batching of internal/memory/api/service_write.go:129-141, 213-228). */
 OMR_API int omr_search(omr_store* s, const float* queries, int32_t nq, int32_t dim, const omr_filter* filters,
                int32_t n_filters, const int32_t* query_filter, int32_t k, omr_hit* hits, int32_t* counts);
 
@@ -211,7 +213,7 @@ OMR_API int omr_device_search(omr_store* s, const float* d_queries, int32_t nq, 
 /* Pipelined form of omr_device_search, for servers that keep the GPU busy with back-to-back
  * batches: _begin enqueues the batch on an internal stream (ordered after what `stream` already
  * holds) and returns at once; _finish(ticket) waits for that batch, runs the exact fallback if a
- * certificate failed, and orders `stream` after the results.  Up to two batches may be in flight, so
+ * certificate failed, and orders `stream` after the results.  Up to four batches may be in flight, so
  * the select / rescore tail of batch i runs underneath the scorer of batch i+1.  Inputs, bitmaps and
  * outputs of a batch must stay untouched between its _begin and its _finish. */
 OMR_API int omr_device_search_begin(omr_store* s, const float* d_queries, int32_t nq, const uint32_t* d_bitmaps,
@@ -259,6 +261,8 @@ typedef struct omr_stats {
   int32_t num_sms;
   double scorer_ms_sum;      /* device time of the approximate scorer, summed (profiling on) */
   int64_t scorer_timed;      /* batches that sum covers */
+  int64_t host_calls;        /* omr_search / omr_search_rows calls */
+  int64_t host_batches;      /* searches they were coalesced into (concurrent calls share one pass) */
 } omr_stats;
 OMR_API int omr_get_stats(const omr_store* s, omr_stats* out);
 /* Brackets the approximate scorer (the dominant kernel) with CUDA events on the search stream

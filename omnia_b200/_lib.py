@@ -69,7 +69,8 @@ class Stats(C.Structure):
     _fields_ = [("kernel_launches", C.c_int64), ("searches", C.c_int64), ("queries", C.c_int64),
                 ("rescued_rows", C.c_int64), ("fallback_queries", C.c_int64), ("last_path", C.c_int32),
                 ("last_sub_bucket", C.c_int32), ("last_rescore_width", C.c_int32), ("num_sms", C.c_int32),
-                ("scorer_ms_sum", C.c_double), ("scorer_timed", C.c_int64)]
+                ("scorer_ms_sum", C.c_double), ("scorer_timed", C.c_int64), ("host_calls", C.c_int64),
+                ("host_batches", C.c_int64)]
 
 
 # name -> (restype, argtypes).  tests/test_abi.py checks this table against the header.

@@ -9,6 +9,8 @@
 // the metadata so that row-state edits are one small cudaMemcpy.
 #include <algorithm>
 #include <atomic>
+#include <condition_variable>
+#include <deque>
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
@@ -204,7 +206,8 @@ struct omr_store {
     cudaStream_t caller = nullptr;
     FinalizeArgs fa;
   };
-  Lane lanes[3];
+  static constexpr int kLanes = 5;   // lane 0: synchronous calls; lanes 1..4: batches in flight
+  Lane lanes[kLanes];
   DevBuf<double> w_sel_dist, w_exact, w_maxdist, w_out_dist, w_pair_sim;
   DevBuf<int32_t> w_sel_rows, w_extra_items, w_qgroup, w_out_count, w_idx;
   DevBuf<float> w_sel_bound, w_queries, w_stage;
@@ -220,6 +223,20 @@ struct omr_store {
   bool legacy_post = false;  // OMR_LEGACY_POST=1: use the unfused select/rescore/finalize chain
 
   std::atomic<int64_t> st_launches{0}, st_searches{0}, st_queries{0}, st_rescued{0}, st_fallback{0};
+  // Coalescing of concurrent host calls (dedup-on-write micro-batching): while one
+  // search runs, the calls that arrive queue up and the next leader takes them all as ONE batch.
+  struct HostReq {
+    const float* q; int nq; const omr_filter* filters; int n_filters; const int32_t* qf; int k;
+    omr_hit* hits; int32_t* counts; int64_t* rows; double* dist;
+    int rc = 0; bool done = false; std::string err;
+  };
+  std::mutex bq_mu;
+  std::condition_variable bq_cv;
+  std::deque<HostReq*> bq;
+  bool bq_leader = false;
+  std::atomic<int64_t> st_host_calls{0}, st_host_batches{0};
+  int submit(HostReq& r);
+  void run_batch(std::vector<HostReq*>& batch);
   // optional device timing of the dominant kernel (the approximate scorer), for bench.py's roofline
   bool profiling = false;
   double scorer_ms_sum = 0.0;
@@ -444,7 +461,7 @@ int omr_store::device_search(const float* d_q, int nq, const uint32_t* d_bitmaps
 
 // Waits for every batch of the begin/finish pipeline that is still in flight (before the store mutates).
 int omr_store::drain() {
-  for (int i = 1; i < 3; i++)
+  for (int i = 1; i < kLanes; i++)
     if (lanes[i].busy && !lanes[i].immediate) OMR_CUDA_OK(cudaStreamSynchronize(lanes[i].stream));
   return 0;
 }
@@ -575,7 +592,9 @@ int omr_store::enqueue(Lane& L, const float* d_q, int nq, const uint32_t* d_bitm
       pa.row_base = cfg.row_base; pa.row_stride = cfg.row_stride;
       pa.out_rows = d_rows; pa.out_dist = d_dist; pa.out_count = d_count;
       pa.fail_list = L.fail_list.p; pa.fail_count = fail_count; pa.rescued_total = extra_total;
-      pa.sort_cap = k <= 16 ? 512 : 2048;   // 512 keeps the block under 30 KB so it fits beside a scorer CTA
+      // small enough that a block (fp64 query + sort arrays + 4 KB) stays under ~30 KB and fits beside a
+      // scorer CTA of the next batch in flight
+      pa.sort_cap = k <= 16 ? 512 : (k <= 128 ? 1024 : 2048);
       if (post_timing) {
         if ((rc = L.timing.reserve((size_t)qpad * 8))) return rc;
         pa.timing = L.timing.p;
@@ -728,6 +747,126 @@ int omr_store::host_search(const float* queries, int nq, const omr_filter* filte
     for (int j = 0; j < ocnt[i]; j++) fill_hit(&hits[(size_t)i * k + j], orow[(size_t)i * k + j], odist[(size_t)i * k + j]);
   }
   return 0;
+}
+
+static bool same_cstr(const char* a, const char* b) { return (!a && !b) || (a && b && strcmp(a, b) == 0); }
+static bool same_filter(const omr_filter& a, const omr_filter& b) {
+  if (!same_cstr(a.workspace_id, b.workspace_id) || !same_cstr(a.virtual_user_id, b.virtual_user_id) ||
+      !same_cstr(a.agent_id, b.agent_id) || a.user_mode != b.user_mode || a.agent_mode != b.agent_mode ||
+      a.n_kinds != b.n_kinds || a.n_purposes != b.n_purposes || a.min_confidence != b.min_confidence ||
+      a.now_us != b.now_us)
+    return false;
+  if (!(a.max_distance == b.max_distance || (a.max_distance != a.max_distance && b.max_distance != b.max_distance)))
+    return false;
+  for (int i = 0; i < a.n_kinds; i++)
+    if (!same_cstr(a.kinds[i], b.kinds[i])) return false;
+  for (int i = 0; i < a.n_purposes; i++)
+    if (!same_cstr(a.purposes[i], b.purposes[i])) return false;
+  return true;
+}
+
+// Runs the requests of one batch as a single search (their callers are blocked in submit(), so every
+// pointer they passed stays valid).  Identical filters share one bitmap.
+void omr_store::run_batch(std::vector<HostReq*>& batch) {
+  std::lock_guard<std::mutex> lk(mu);
+  cudaSetDevice(cfg.device);
+  st_host_batches++;
+  auto run_one = [&](HostReq* r) {
+    r->rc = host_search(r->q, r->nq, r->filters, r->n_filters, r->qf, r->k, r->hits, r->counts, r->rows, r->dist);
+    if (r->rc) r->err = g_err;
+  };
+  if (batch.size() == 1) {
+    run_one(batch[0]);
+    return;
+  }
+  const int k = batch[0]->k;
+  int tq = 0;
+  for (HostReq* r : batch) tq += r->nq;
+  std::vector<float> q((size_t)tq * dim);
+  std::vector<omr_filter> filters;
+  std::vector<int32_t> qf((size_t)tq);
+  int off = 0;
+  bool ok = true;
+  for (HostReq* r : batch) {
+    memcpy(q.data() + (size_t)off * dim, r->q, (size_t)r->nq * dim * 4);
+    std::vector<int> map((size_t)std::max(r->n_filters, 0));
+    for (int f = 0; f < r->n_filters; f++) {
+      int hit = -1;
+      for (size_t g = 0; g < filters.size() && hit < 0; g++)
+        if (same_filter(filters[g], r->filters[f])) hit = (int)g;
+      if (hit < 0) {
+        hit = (int)filters.size();
+        filters.push_back(r->filters[f]);
+      }
+      map[f] = hit;
+    }
+    for (int i = 0; i < r->nq; i++) {
+      const int f = r->qf ? r->qf[i] : 0;
+      if (f < 0 || f >= r->n_filters) { ok = false; break; }
+      qf[(size_t)off + i] = map[f];
+    }
+    off += r->nq;
+  }
+  std::vector<int64_t> rows((size_t)tq * k);
+  std::vector<double> dist((size_t)tq * k);
+  std::vector<int32_t> cnt((size_t)tq);
+  int rc = ok ? host_search(q.data(), tq, filters.data(), (int)filters.size(), qf.data(), k, nullptr, cnt.data(),
+                            rows.data(), dist.data())
+              : OMR_E_INVALID;
+  if (rc) {  // one bad request must not fail its neighbours: run them one by one for exact attribution
+    for (HostReq* r : batch) run_one(r);
+    return;
+  }
+  off = 0;
+  for (HostReq* r : batch) {
+    for (int i = 0; i < r->nq; i++) {
+      const size_t src = (size_t)(off + i) * k, dst = (size_t)i * k;
+      r->counts[i] = cnt[(size_t)off + i];
+      if (r->rows) {
+        memcpy(r->rows + dst, rows.data() + src, (size_t)k * 8);
+        memcpy(r->dist + dst, dist.data() + src, (size_t)k * 8);
+      } else {
+        for (int j = 0; j < r->counts[i]; j++) fill_hit(&r->hits[dst + j], rows[src + j], dist[src + j]);
+      }
+    }
+    r->rc = 0;
+    off += r->nq;
+  }
+}
+
+int omr_store::submit(HostReq& req) {
+  st_host_calls++;
+  std::unique_lock<std::mutex> lk(bq_mu);
+  bq.push_back(&req);
+  while (!req.done) {
+    if (!bq_leader) {
+      bq_leader = true;
+      std::vector<HostReq*> batch;
+      const int k = bq.front()->k;
+      int tq = 0, tf = 0;
+      for (auto it = bq.begin(); it != bq.end();) {
+        HostReq* r = *it;
+        if (r->k == k && (batch.empty() || (tq + r->nq <= 4096 && tf + r->n_filters <= 64))) {
+          batch.push_back(r);
+          tq += r->nq;
+          tf += r->n_filters;
+          it = bq.erase(it);
+        } else {
+          ++it;
+        }
+      }
+      lk.unlock();
+      run_batch(batch);
+      lk.lock();
+      for (HostReq* r : batch) r->done = true;
+      bq_leader = false;
+      bq_cv.notify_all();
+    } else {
+      bq_cv.wait(lk);
+    }
+  }
+  if (req.rc) g_err = req.err;
+  return req.rc;
 }
 
 // ================================ C ABI =========================================
@@ -1000,9 +1139,9 @@ int omr_search(omr_store* s, const float* queries, int32_t nq, int32_t dim, cons
   if (dim != s->dim)
     return fail_msg(OMR_E_DIM, "memory: similar observations: different vector dimensions %d and %d", s->dim, dim);
   if (k <= 0) k = 5;  // DefaultDuplicateCandidateLimit, internal/memory/types.go:137-141
-  std::lock_guard<std::mutex> lk(s->mu);
-  cudaSetDevice(s->cfg.device);
-  return s->host_search(queries, nq, filters, n_filters, query_filter, k, hits, counts);
+  if (nq <= 0) return OMR_OK;
+  omr_store::HostReq r{queries, nq, filters, n_filters, query_filter, k, hits, counts, nullptr, nullptr};
+  return s->submit(r);
 }
 
 int omr_search_rows(omr_store* s, const float* queries, int32_t nq, int32_t dim, const omr_filter* filters,
@@ -1012,9 +1151,9 @@ int omr_search_rows(omr_store* s, const float* queries, int32_t nq, int32_t dim,
   if (dim != s->dim)
     return fail_msg(OMR_E_DIM, "memory: similar observations: different vector dimensions %d and %d", s->dim, dim);
   if (k <= 0) k = 5;
-  std::lock_guard<std::mutex> lk(s->mu);
-  cudaSetDevice(s->cfg.device);
-  return s->host_search(queries, nq, filters, n_filters, query_filter, k, nullptr, counts, rows, distances);
+  if (nq <= 0) return OMR_OK;
+  omr_store::HostReq r{queries, nq, filters, n_filters, query_filter, k, nullptr, counts, rows, distances};
+  return s->submit(r);
 }
 
 int omr_cosine_ranked(omr_store* s, const float* query, int32_t dim, const omr_filter* filter, int32_t fanout,
@@ -1083,9 +1222,9 @@ int omr_device_search_begin(omr_store* s, const float* d_queries, int32_t nq, co
   std::lock_guard<std::mutex> lk(s->mu);
   cudaSetDevice(s->cfg.device);
   int idx = -1;
-  for (int i = 1; i < 3; i++)
+  for (int i = 1; i < omr_store::kLanes; i++)
     if (!s->lanes[i].busy) { idx = i; break; }
-  if (idx < 0) return fail_msg(OMR_E_CAPACITY, "memory: two batches are already in flight; finish one first");
+  if (idx < 0) return fail_msg(OMR_E_CAPACITY, "memory: %d batches are already in flight; finish one first", omr_store::kLanes - 1);
   omr_store::Lane& L = s->lanes[idx];
   cudaStream_t caller = (cudaStream_t)stream;
   // the lane's stream picks up after whatever the caller already enqueued (its inputs)
@@ -1111,7 +1250,7 @@ int omr_device_search_begin(omr_store* s, const float* d_queries, int32_t nq, co
 }
 
 int omr_device_search_finish(omr_store* s, int32_t ticket) {
-  if (!s || ticket < 1 || ticket > 2) return fail_msg(OMR_E_INVALID, "memory: omr_device_search_finish: bad ticket %d", ticket);
+  if (!s || ticket < 1 || ticket >= omr_store::kLanes) return fail_msg(OMR_E_INVALID, "memory: omr_device_search_finish: bad ticket %d", ticket);
   std::lock_guard<std::mutex> lk(s->mu);
   cudaSetDevice(s->cfg.device);
   omr_store::Lane& L = s->lanes[ticket];
@@ -1309,6 +1448,8 @@ int omr_get_stats(const omr_store* s, omr_stats* out) {
   out->last_sub_bucket = s->last_S;
   out->last_rescore_width = s->last_K2;
   out->num_sms = s->num_sms;
+  out->host_calls = s->st_host_calls.load();
+  out->host_batches = s->st_host_batches.load();
   out->scorer_ms_sum = s->scorer_ms_sum;
   out->scorer_timed = s->scorer_timed;
   return OMR_OK;

@@ -31,6 +31,24 @@ def gauss_unit_chunk(c: int, dim: int, seed: int = CORPUS_SEED) -> np.ndarray:
     return _normalize(rng.standard_normal((CHUNK, dim), np.float32))
 
 
+def gauss_unit_local(n_local: int, dim: int, seed: int, rank: int, world: int) -> np.ndarray:
+    """A shard of a gauss-unit corpus generated WITHOUT producing the other shards' rows: rank r of
+    `world` draws its n_local rows from its own streams.  Same distribution as gauss_unit, but not the
+    same rows; for throughput runs on stores too large to generate world times over (bench.py says so)."""
+    from concurrent.futures import ThreadPoolExecutor
+    import os
+
+    def one(c: int) -> np.ndarray:
+        rng = np.random.default_rng([seed, 1_000_003 + 7919 * world + rank, c])
+        m = min(CHUNK, n_local - c * CHUNK)
+        return _normalize(rng.standard_normal((m, dim), np.float32))
+
+    n_chunks = (n_local + CHUNK - 1) // CHUNK
+    workers = min(n_chunks, max(1, (os.cpu_count() or 8) // max(1, min(world, 8))), 16)
+    with ThreadPoolExecutor(max_workers=workers) as ex:
+        return np.ascontiguousarray(np.concatenate(list(ex.map(one, range(n_chunks))), axis=0))
+
+
 def gauss_unit(n: int, dim: int, seed: int = CORPUS_SEED, rank: int = 0, world: int = 1) -> np.ndarray:
     """(i) L2-normalised standard-normal rows; with world > 1, the rows rank::world of the
     n-row corpus (round-robin row sharding)."""

@@ -43,10 +43,11 @@ def test_pipelined_equals_synchronous(n, dim, nq, k, path):
         for w, g in zip(want, got):
             assert np.array_equal(w[2], g[2]) and np.array_equal(w[0], g[0]) and np.array_equal(w[1], g[1])
         # a third begin without a finish is refused, and a stale ticket too
-        t1 = s.device_search_begin(batches[0], k, *o2[0], stream=stream)
-        t2 = s.device_search_begin(batches[1], k, *o2[1], stream=stream)
+        keep = [outs(nq, k) for _ in range(5)]          # output buffers must outlive their batch
+        tickets = [s.device_search_begin(batches[i % 5], k, *keep[i], stream=stream) for i in range(4)]
         with pytest.raises(RecallError, match="already in flight"):
-            s.device_search_begin(batches[2], k, *outs(nq, k), stream=stream)
-        s.device_search_finish(t1); s.device_search_finish(t2)
+            s.device_search_begin(batches[2], k, *keep[4], stream=stream)
+        for t in tickets:
+            s.device_search_finish(t)
         with pytest.raises(RecallError, match="not in flight"):
-            s.device_search_finish(t1)
+            s.device_search_finish(tickets[0])
