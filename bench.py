@@ -206,7 +206,9 @@ def main():
         shard = synth.gauss_unit_local(n_local, DIM, synth.CORPUS_SEED, rank, world)
     else:
         shard = synth.gauss_unit(N_ROWS, DIM, rank=rank, world=world)
-    sr = ShardedRecall(DIM, N_ROWS, local_rank, force_path=int(os.environ.get("OMNIA_BENCH_PATH", 0)))
+    exchange = os.environ.get("OMNIA_BENCH_EXCHANGE", "nccl")
+    sr = ShardedRecall(DIM, N_ROWS, local_rank, exchange=exchange, nq_max=NQ, k_max=TOPK,
+                       force_path=int(os.environ.get("OMNIA_BENCH_PATH", 0)))
     sr.store.bulk_load(shard)
     # query batches: perturbed copies of stored rows, identical on every rank
     hq = []
@@ -340,7 +342,8 @@ def main():
             "config": {"workload": workload_name(), "rows": N_ROWS, "dim": DIM, "queries_per_step": NQ, "k": TOPK,
                        "sharding": f"rows round-robin over {world} GPU(s)" + (", shard-local corpus generation" if local_gen else ""),
                        "pipeline": "%s batches in flight (omr_device_search_begin/_finish)" % os.environ.get("OMNIA_BENCH_DEPTH", 3) if pipelined else "none",
-                       "single_step_latency_ms": latency_ms, "scorer_path": int(st1.last_path),
+                       "single_step_latency_ms": latency_ms,
+                       "exchange": ("fused peer-memory scatter + on-device flags" if exchange == "p2p" else "NCCL allgather + merge kernel") if world > 1 else "none", "scorer_path": int(st1.last_path),
                        "sub_bucket": int(st1.last_sub_bucket), "rescore_width": int(st1.last_rescore_width),
                        "l2": "inputs larger than L2: the bf16 matrix streamed every step is %.2f GB" % (N_ROWS / world * DIM * 2 / 1e9),
                        "rescued_rows": int(st1.rescued_rows - st0.rescued_rows),

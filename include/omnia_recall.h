@@ -221,6 +221,28 @@ OMR_API int omr_device_search_begin(omr_store* s, const float* d_queries, int32_
                                     int32_t k, int64_t* d_rows, double* d_dist, int32_t* d_count, void* stream,
                                     int32_t* ticket);
 OMR_API int omr_device_search_finish(omr_store* s, int32_t ticket);
+/* ---- fused candidate exchange over NVLink peer memory -------------------------------------
+ * Row-sharded stores, one process per GPU.  Instead of an NCCL allgather issued by
+ * the host, every rank's local answer is stored straight into every rank's exchange buffer by a kernel
+ * that runs right behind the local search (st.global on CUDA-IPC mapped peer memory = NVLink writes,
+ * published with a system-scope release flag), and the merge kernel waits on those flags on the device.
+ *   1. every rank: omr_exchange_alloc -> omr_ipc_export of the returned buffer; the 64-byte handles are
+ *      exchanged by the host code (any transport) and passed to omr_exchange_setup, [world][64] in rank order;
+ *   2. per batch, on every rank, with the SAME slot sequence: omr_device_search_exchange_begin(..., slot, ...)
+ *      then omr_device_search_exchange_finish(ticket, outputs): d_rows/d_dist/d_count receive the GLOBAL
+ *      top-k once `stream` (the one given to _begin) drains.
+ * Use at least 2 * (batches in flight) + 1 slots so a slot is never rewritten before every rank merged it.
+ * A merge that waits ~4 s for a peer raises an error reported by the next call instead of hanging. */
+OMR_API int omr_exchange_alloc(omr_store* s, int32_t world, int32_t nq_max, int32_t k_max, int32_t slots,
+                               void** d_buf, int64_t* bytes);
+OMR_API int omr_ipc_export(const void* d_ptr, uint8_t handle[64]);
+OMR_API int omr_exchange_setup(omr_store* s, int32_t rank, int32_t world, const uint8_t* handles);
+OMR_API int omr_device_search_exchange_begin(omr_store* s, const float* d_queries, int32_t nq,
+                                             const uint32_t* d_bitmaps, int32_t n_groups,
+                                             const int32_t* d_query_group, const double* d_max_distance, int32_t k,
+                                             int32_t slot, void* stream, int32_t* ticket);
+OMR_API int omr_device_search_exchange_finish(omr_store* s, int32_t ticket, int64_t* d_rows, double* d_dist,
+                                              int32_t* d_count);
 /* Row-sharded stores: merges the G per-shard answers gathered into [G][nq][k]
  * (the gather itself is an NCCL allgather done by the host code).
  * shard_stride = elements between consecutive shards' [nq][k] blocks (0 = nq*k), so rows and

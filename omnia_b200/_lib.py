@@ -102,6 +102,13 @@ SIGNATURES = {
                                           C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                           C.POINTER(C.c_int32)]),
     "omr_device_search_finish": (C.c_int, [C.c_void_p, C.c_int32]),
+    "omr_exchange_alloc": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.POINTER(C.c_void_p),
+                                     C.POINTER(C.c_int64)]),
+    "omr_ipc_export": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "omr_exchange_setup": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.c_void_p]),
+    "omr_device_search_exchange_begin": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_int32, C.c_void_p,
+                                                   C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.POINTER(C.c_int32)]),
+    "omr_device_search_exchange_finish": (C.c_int, [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p]),
     "omr_device_merge_topk": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_int64, C.c_void_p,
                                         C.c_void_p, C.c_void_p, C.c_void_p]),
     "omr_exact_topk_noalloc": (C.c_int, [C.c_void_p, C.c_int64, C.c_int32, C.c_int64, C.c_void_p, C.c_int32, C.c_void_p,

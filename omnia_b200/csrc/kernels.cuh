@@ -107,6 +107,25 @@ int launch_select_exact(const double* dist, int64_t n, const int32_t* slot_query
 int launch_merge_topk(const int64_t* in_rows, const double* in_dist, int G, int nq, int k, int64_t shard_stride,
                       int64_t* out_rows, double* out_dist, int32_t* out_count, cudaStream_t st);
 
+// ---- fused candidate exchange over NVLink peer memory (k_exchange.cu) ---------------
+constexpr int kMaxWorld = 16;
+struct ExchangeView {
+  void* peers[kMaxWorld];  // exchange buffer of every rank as mapped in THIS process (own buffer at [rank])
+  int world = 0, rank = 0, slots = 0;
+  int64_t slot_stride = 0;  // bytes of one (slot, rank) data region: 2 * nq_max * k_max * 8
+  __host__ __device__ size_t data_offset(int slot, int r) const { return ((size_t)slot * world + r) * (size_t)slot_stride; }
+  __host__ __device__ size_t flag_offset(int slot, int r) const {
+    return (size_t)slots * world * (size_t)slot_stride + ((size_t)slot * world + r) * 8;
+  }
+  __host__ __device__ size_t total_bytes() const { return flag_offset(slots, 0); }
+};
+int launch_exchange_scatter(const ExchangeView& x, const int64_t* local, int nq, int k, int slot,
+                            unsigned long long epoch, const int32_t* fail_count, unsigned int* done_blocks,
+                            cudaStream_t st);
+int launch_exchange_merge(const ExchangeView& x, int slot, unsigned long long epoch, int nq, int k,
+                          int64_t* out_rows, double* out_dist, int32_t* out_count, unsigned int* error_word,
+                          cudaStream_t st);
+
 // ---- near-duplicate self-join (k_score_umma.cu / k_select.cu) ----------------
 struct PairCand {
   int32_t a, b;

@@ -205,6 +205,11 @@ struct omr_store {
     int nq = 0, k = 0, K2 = 0, K2x = 0, qpad = 0, nfail_known = -1;
     cudaStream_t caller = nullptr;
     FinalizeArgs fa;
+    // fused exchange: this batch's local answer [2][nq][k] + counts, its slot and epoch
+    DevBuf<int64_t> xlocal;
+    DevBuf<int32_t> xcount;
+    int xslot = -1, xnq = 0, xk = 0, nfail_seen = 0;
+    unsigned long long xepoch = 0;
   };
   static constexpr int kLanes = 5;   // lane 0: synchronous calls; lanes 1..4: batches in flight
   Lane lanes[kLanes];
@@ -235,6 +240,14 @@ struct omr_store {
   std::deque<HostReq*> bq;
   bool bq_leader = false;
   std::atomic<int64_t> st_host_calls{0}, st_host_batches{0};
+  // fused exchange state (omr_exchange_*)
+  ExchangeView xv;
+  void* xbuf = nullptr;               // this rank's exchange buffer (cudaMalloc, exported through CUDA IPC)
+  std::vector<void*> xopened;         // peer mappings to close
+  std::vector<unsigned long long> xslot_epoch;
+  int xnq_max = 0, xk_max = 0;
+  DevBuf<unsigned int> xwords;        // [0..15] scatter block counters, [16] error word
+  PinBuf<unsigned int> xerr_pin;
   int submit(HostReq& r);
   void run_batch(std::vector<HostReq*>& batch);
   // optional device timing of the dominant kernel (the approximate scorer), for bench.py's roofline
@@ -334,12 +347,16 @@ void omr_store::destroy() {
     if (p) cudaFree(p);
   for (Lane& L : lanes) {
     if (L.stream) cudaStreamSynchronize(L.stream);
+    L.xlocal.release(); L.xcount.release();
     L.qn.release(); L.qnorm2.release(); L.cand.release(); L.fail_list.release(); L.counters.release();
     L.extra_cnt.release(); L.timing.release(); L.pin.release();
     for (cudaEvent_t e : {L.ev_in, L.ev_done, L.ev0, L.ev1})
       if (e) cudaEventDestroy(e);
     if (L.stream) cudaStreamDestroy(L.stream);
   }
+  for (void* p : xopened) cudaIpcCloseMemHandle(p);
+  if (xbuf) cudaFree(xbuf);
+  xwords.release(); xerr_pin.release();
   w_sel_dist.release(); w_exact.release(); w_maxdist.release();
   w_out_dist.release(); w_pair_sim.release(); w_sel_rows.release();
   w_extra_items.release(); w_qgroup.release(); w_out_count.release();
@@ -620,9 +637,11 @@ int omr_store::enqueue(Lane& L, const float* d_q, int nq, const uint32_t* d_bitm
 // Host side of a batch: waits for `st`, reads the counters and runs the exact fallback for the
 // (rare) queries whose certificate failed.
 int omr_store::complete(Lane& L, cudaStream_t st) {
+  L.nfail_seen = 0;
   if (L.nq <= 0) return 0;
   int rc;
   int nfail = L.nfail_known;
+  L.nfail_seen = 0;
   if (nfail < 0) {
     OMR_CUDA_OK(cudaStreamSynchronize(st));
     st_rescued += L.pin.p[0];
@@ -634,6 +653,7 @@ int omr_store::complete(Lane& L, cudaStream_t st) {
       scorer_timed++;
     }
   }
+  L.nfail_seen = nfail;
   if (nfail > 0) {
     // Exact fallback: score every eligible row of the failing queries in fp64.
     const int nq = L.nq, k = L.k, K2 = L.K2, K2x = L.K2x, qpad = L.qpad;
@@ -1266,6 +1286,151 @@ int omr_device_search_finish(omr_store* s, int32_t ticket) {
     }
   }
   L.busy = false;
+  return rc;
+}
+
+// ---- fused exchange over peer memory ---------------------------------------------------------
+
+int omr_exchange_alloc(omr_store* s, int32_t world, int32_t nq_max, int32_t k_max, int32_t slots, void** d_buf,
+                       int64_t* bytes) {
+  if (!s || !d_buf || !bytes) return fail_msg(OMR_E_INVALID, "memory: omr_exchange_alloc: null argument");
+  if (world < 1 || world > kMaxWorld || nq_max < 1 || k_max < 1 || slots < 1 || slots > 64)
+    return fail_msg(OMR_E_INVALID, "memory: omr_exchange_alloc: world 1..%d, slots 1..64", kMaxWorld);
+  std::lock_guard<std::mutex> lk(s->mu);
+  cudaSetDevice(s->cfg.device);
+  if (s->xbuf) return fail_msg(OMR_E_INVALID, "memory: the exchange buffer of this store is already allocated");
+  ExchangeView v;
+  v.world = world; v.slots = slots; v.rank = 0;
+  v.slot_stride = (int64_t)2 * nq_max * k_max * 8;
+  const size_t total = v.total_bytes();
+  OMR_CUDA_OK(cudaMalloc(&s->xbuf, total));
+  OMR_CUDA_OK(cudaMemset(s->xbuf, 0, total));   // flags start at epoch 0; the first batch of a slot is epoch 1
+  s->xv = v;
+  s->xnq_max = nq_max; s->xk_max = k_max;
+  s->xslot_epoch.assign((size_t)slots, 0ull);
+  int rc;
+  if ((rc = s->xwords.reserve(16 + 16 * omr_store::kLanes))) return rc;   // [0] error word, then 16 block counters per lane
+  OMR_CUDA_OK(cudaMemset(s->xwords.p, 0, (16 + 16 * omr_store::kLanes) * sizeof(unsigned int)));
+  if ((rc = s->xerr_pin.reserve(4))) return rc;
+  s->xerr_pin.p[0] = 0;
+  *d_buf = s->xbuf;
+  *bytes = (int64_t)total;
+  return OMR_OK;
+}
+
+int omr_ipc_export(const void* d_ptr, uint8_t handle[64]) {
+  if (!d_ptr || !handle) return fail_msg(OMR_E_INVALID, "memory: omr_ipc_export: null argument");
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "CUDA IPC handle size");
+  cudaIpcMemHandle_t h;
+  OMR_CUDA_OK(cudaIpcGetMemHandle(&h, const_cast<void*>(d_ptr)));
+  memcpy(handle, &h, 64);
+  return OMR_OK;
+}
+
+int omr_exchange_setup(omr_store* s, int32_t rank, int32_t world, const uint8_t* handles /*[world][64]*/) {
+  if (!s || !handles) return fail_msg(OMR_E_INVALID, "memory: omr_exchange_setup: null argument");
+  std::lock_guard<std::mutex> lk(s->mu);
+  cudaSetDevice(s->cfg.device);
+  if (!s->xbuf || world != s->xv.world || rank < 0 || rank >= world)
+    return fail_msg(OMR_E_INVALID, "memory: omr_exchange_setup: allocate first, with the same world size");
+  s->xv.rank = rank;
+  for (int p = 0; p < world; p++) {
+    if (p == rank) {
+      s->xv.peers[p] = s->xbuf;
+      continue;
+    }
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handles + 64 * p, 64);
+    void* ptr = nullptr;
+    OMR_CUDA_OK(cudaIpcOpenMemHandle(&ptr, h, cudaIpcMemLazyEnablePeerAccess));
+    s->xv.peers[p] = ptr;
+    s->xopened.push_back(ptr);
+  }
+  return OMR_OK;
+}
+
+int omr_device_search_exchange_begin(omr_store* s, const float* d_queries, int32_t nq, const uint32_t* d_bitmaps,
+                                     int32_t n_groups, const int32_t* d_query_group, const double* d_max_distance,
+                                     int32_t k, int32_t slot, void* stream, int32_t* ticket) {
+  if (!s || !d_queries || !ticket) return fail_msg(OMR_E_INVALID, "memory: omr_device_search_exchange_begin: null argument");
+  (void)n_groups;
+  std::lock_guard<std::mutex> lk(s->mu);
+  cudaSetDevice(s->cfg.device);
+  if (!s->xbuf || s->xv.peers[s->xv.world - 1] == nullptr) return fail_msg(OMR_E_INVALID, "memory: call omr_exchange_setup first");
+  if (nq < 1 || nq > s->xnq_max || k < 1 || k > s->xk_max || slot < 0 || slot >= s->xv.slots)
+    return fail_msg(OMR_E_CAPACITY, "memory: batch (%d queries, k=%d, slot %d) exceeds the exchange buffer (%d, %d, %d slots)",
+                    nq, k, slot, s->xnq_max, s->xk_max, s->xv.slots);
+  if (s->xerr_pin.p[0]) return fail_msg(OMR_E_CUDA, "memory: gpu: a peer never published its answer (exchange timed out)");
+  int idx = -1;
+  for (int i = 1; i < omr_store::kLanes; i++)
+    if (!s->lanes[i].busy) { idx = i; break; }
+  if (idx < 0) return fail_msg(OMR_E_CAPACITY, "memory: %d batches are already in flight; finish one first", omr_store::kLanes - 1);
+  omr_store::Lane& L = s->lanes[idx];
+  int rc;
+  if ((rc = L.xlocal.reserve((size_t)2 * nq * k))) return rc;
+  if ((rc = L.xcount.reserve((size_t)nq))) return rc;
+  cudaStream_t caller = (cudaStream_t)stream;
+  OMR_CUDA_OK(cudaEventRecord(L.ev_in, caller));
+  OMR_CUDA_OK(cudaStreamWaitEvent(L.stream, L.ev_in, 0));
+  bool fused = true;
+  int64_t* lrows = L.xlocal.p;
+  double* ldist = reinterpret_cast<double*>(L.xlocal.p + (size_t)nq * k);
+  rc = s->enqueue(L, d_queries, nq, d_bitmaps, d_query_group, d_max_distance, k, lrows, ldist, L.xcount.p, L.stream, &fused);
+  if (rc) return rc;
+  L.caller = caller;
+  L.xslot = slot;
+  L.xnq = nq;
+  L.xk = k;
+  L.xepoch = ++s->xslot_epoch[(size_t)slot];
+  L.immediate = false;
+  if (!fused || L.nfail_known >= 0) {
+    // unfused chain / exact-only path / empty store: finish the local answer now; _finish publishes it
+    if ((rc = s->complete(L, L.stream))) return rc;
+    L.immediate = true;
+  } else {
+    // publish straight from the device unless a certificate failed (then _finish publishes after the fallback)
+    if ((rc = launch_exchange_scatter(s->xv, L.xlocal.p, nq, k, slot, L.xepoch, L.counters.p + 1,
+                                      s->xwords.p + 16 + 16 * idx, L.stream)))
+      return rc;
+    s->st_launches++;
+  }
+  L.busy = true;
+  *ticket = idx;
+  return OMR_OK;
+}
+
+int omr_device_search_exchange_finish(omr_store* s, int32_t ticket, int64_t* d_rows, double* d_dist, int32_t* d_count) {
+  if (!s || !d_rows || !d_dist || !d_count || ticket < 1 || ticket >= omr_store::kLanes)
+    return fail_msg(OMR_E_INVALID, "memory: omr_device_search_exchange_finish: bad argument");
+  std::lock_guard<std::mutex> lk(s->mu);
+  cudaSetDevice(s->cfg.device);
+  omr_store::Lane& L = s->lanes[ticket];
+  if (!L.busy || L.xslot < 0) return fail_msg(OMR_E_INVALID, "memory: ticket %d is not an exchange batch in flight", ticket);
+  int rc = OMR_OK;
+  bool publish = L.immediate;
+  if (!L.immediate) {
+    rc = s->complete(L, L.stream);
+    publish = L.nfail_seen > 0;   // the device held its flag back: publish the repaired answer
+  }
+  if (rc == OMR_OK) {
+    if (publish) {
+      rc = launch_exchange_scatter(s->xv, L.xlocal.p, L.xnq, L.xk, L.xslot, L.xepoch, nullptr,
+                                   s->xwords.p + 16 + 16 * ticket, L.stream);
+      s->st_launches++;
+    }
+    if (rc == OMR_OK) {
+      rc = launch_exchange_merge(s->xv, L.xslot, L.xepoch, L.xnq, L.xk, d_rows, d_dist, d_count, s->xwords.p, L.stream);
+      s->st_launches++;
+    }
+    if (rc == OMR_OK) {
+      cudaError_t e = cudaMemcpyAsync(s->xerr_pin.p, s->xwords.p, sizeof(unsigned int), cudaMemcpyDeviceToHost, L.stream);
+      if (e == cudaSuccess) e = cudaEventRecord(L.ev_done, L.stream);
+      if (e == cudaSuccess) e = cudaStreamWaitEvent(L.caller, L.ev_done, 0);
+      if (e != cudaSuccess) rc = fail_cuda(e, "exchange hand-off", __FILE__, __LINE__);
+    }
+  }
+  L.busy = false;
+  L.xslot = -1;
   return rc;
 }
 

@@ -39,7 +39,8 @@ def gather_candidates(rows: torch.Tensor, dist_: torch.Tensor, group=None) -> Tu
 class ShardedRecall:
     """The local shard plus the exchange step.  With no process group it is a single shard."""
 
-    def __init__(self, dim: int, n_rows_total: int, device: int, group=None, **store_kw):
+    def __init__(self, dim: int, n_rows_total: int, device: int, group=None, exchange: str = "nccl",
+                 nq_max: int = 1024, k_max: int = 128, slots: int = 8, **store_kw):
         self.group = group
         live = dist.is_available() and dist.is_initialized()
         self.rank = dist.get_rank(group) if live else 0
@@ -52,6 +53,26 @@ class ShardedRecall:
         # (ordered after the caller's stream at begin()) never waits behind a collective
         self._comm = torch.cuda.Stream(device=self.device) if torch.cuda.is_available() else None
         self._slot_ev = {}   # slot -> event of the last exchange that read / wrote the slot's buffers
+        # exchange = "p2p": the library's fused exchange (peer-memory writes + on-device flags) instead of
+        # an NCCL allgather; the process group is then only used once, to swap the 64-byte IPC handles
+        self.exchange = exchange if self.world > 1 else "none"
+        self.slots = slots
+        if self.exchange == "p2p":
+            self._setup_p2p(nq_max, k_max, slots)
+
+    def _setup_p2p(self, nq_max: int, k_max: int, slots: int) -> None:
+        import ctypes as C
+        from . import _lib as L
+        lib = L.load()
+        buf, nbytes = C.c_void_p(), C.c_int64(0)
+        L.check(lib.omr_exchange_alloc(self.store.handle, self.world, nq_max, k_max, slots, C.byref(buf), C.byref(nbytes)))
+        handle = (C.c_uint8 * 64)()
+        L.check(lib.omr_ipc_export(buf, handle))
+        gathered = [None] * self.world
+        dist.all_gather_object(gathered, bytes(handle), group=self.group)
+        blob = (C.c_uint8 * (64 * self.world)).from_buffer_copy(b"".join(gathered))
+        L.check(lib.omr_exchange_setup(self.store.handle, self.rank, self.world, blob))
+        dist.barrier(group=self.group)   # nobody writes into a peer before every mapping exists
 
     def _buffers(self, nq: int, k: int, slot: int = 0):
         key = (nq, k, slot)
@@ -71,6 +92,10 @@ class ShardedRecall:
     def search_device(self, d_queries: torch.Tensor, k: int, d_bitmaps=None, d_query_group=None, d_max_distance=None):
         """Global top-k for device-resident queries; returns (rows, dist, count) device tensors."""
         nq = d_queries.shape[0]
+        if self.exchange == "p2p":
+            self._sync_slot = (getattr(self, "_sync_slot", -1) + 1) % self.slots
+            r, d, c, _ = self.finish(self.begin(d_queries, k, self._sync_slot, d_bitmaps, d_query_group, d_max_distance))
+            return r, d, c
         b = self._buffers(nq, k)
         stream = torch.cuda.current_stream(self.device).cuda_stream
         self.store.device_search(d_queries, k, b["lr"], b["ld"], b["lc"], d_bitmaps, 0, d_query_group,
@@ -93,6 +118,15 @@ class ShardedRecall:
         nq = d_queries.shape[0]
         b = self._buffers(nq, k, slot)
         cur = torch.cuda.current_stream(self.device)
+        if self.exchange == "p2p":
+            import ctypes as C
+            from . import _lib as L
+            p = lambda t: None if t is None else t.data_ptr()
+            ticket = C.c_int32(0)
+            L.check(L.load().omr_device_search_exchange_begin(
+                self.store.handle, d_queries.data_ptr(), nq, p(d_bitmaps), 0, p(d_query_group), p(d_max_distance), k,
+                slot % self.slots, cur.cuda_stream, C.byref(ticket)))
+            return (ticket.value, nq, k, slot)
         if slot in self._slot_ev:               # the slot's previous exchange must be done with its buffers
             cur.wait_event(self._slot_ev[slot])
         stream = cur.cuda_stream
@@ -106,8 +140,15 @@ class ShardedRecall:
         marks their completion (wait on it, or synchronise the device, before reading the tensors)."""
         ticket, nq, k, slot = handle
         b = self._buffers(nq, k, slot)
-        self.store.device_search_finish(ticket)
         cur = torch.cuda.current_stream(self.device)
+        if self.exchange == "p2p":
+            from . import _lib as L
+            L.check(L.load().omr_device_search_exchange_finish(self.store.handle, ticket, b["r"].data_ptr(),
+                                                               b["d"].data_ptr(), b["c"].data_ptr()))
+            ev = torch.cuda.Event()
+            ev.record(cur)
+            return b["r"], b["d"], b["c"], ev
+        self.store.device_search_finish(ticket)
         if self.world == 1:
             ev = torch.cuda.Event()
             ev.record(cur)

@@ -22,10 +22,17 @@ def main():
     ok = True
     for nq, k in ((4, 10), (200, 10), (64, 100)):
         queries = synth.queries_from(full, nq, seed=nq)
-        sr = ShardedRecall(dim, n, local)
+        sr = ShardedRecall(dim, n, local, exchange=os.environ.get("EXCHANGE", "nccl"), nq_max=256, k_max=128)
         sr.store.bulk_load(full[rank::world])
-        r, d, c = sr.search_device(torch.from_numpy(queries).cuda(), k)
+        dq = torch.from_numpy(queries).cuda()
+        r, d, c = sr.search_device(dq, k)
         torch.cuda.synchronize()
+        # the pipelined form must give the same answer
+        hs = [sr.begin(dq, k, s) for s in range(3)]
+        outs = [sr.finish(h) for h in hs]
+        torch.cuda.synchronize()
+        for o in outs:
+            assert torch.equal(o[0], r) and torch.equal(o[1], d) and torch.equal(o[2], c), "pipelined answer differs"
         r, d, c = r.cpu().numpy(), d.cpu().numpy(), c.cpu().numpy()
         if rank == 0:
             from oracle import oracle as O
