@@ -10,8 +10,9 @@
 //                            -- plain st.global on peer pointers mapped through CUDA IPC, i.e.
 //                            NVLink / NVSwitch writes -- then publishes a per-(slot, rank) epoch flag
 //                            with system-scope release semantics.
-//   exchange_merge_kernel    (every rank) waits with system-scope acquire loads until all `world`
-//                            flags of the slot carry the batch's epoch, then merges G*k -> k per query.
+//   exchange_wait_kernel     (every rank, one warp) waits with system-scope acquire loads until all
+//                            `world` flags of the slot carry the batch's epoch;
+//   exchange_merge_kernel    then merges G*k -> k per query, reading the slot in place.
 //
 // Ranks run on DIFFERENT GPUs, so a merge kernel spinning on a peer's flag cannot starve that peer.
 // The spin is bounded (about four seconds of clock64): on expiry the kernel raises an error word the
@@ -61,7 +62,25 @@ __global__ void __launch_bounds__(256) exchange_scatter_kernel(ExchangeView x, c
   }
 }
 
-// One block per query: wait for the slot's flags, then the same bitonic merge as merge_topk_kernel.
+// One warp: wait until every rank's flag of the slot carries this batch's epoch.  Kept apart from the
+// merge so that only `world` threads poll instead of `world` threads in each of nq blocks.
+__global__ void __launch_bounds__(32) exchange_wait_kernel(ExchangeView x, int slot, unsigned long long epoch,
+                                                           unsigned int* __restrict__ error_word) {
+  const uint8_t* own = reinterpret_cast<const uint8_t*>(x.peers[x.rank]);
+  if ((int)threadIdx.x < x.world) {
+    const unsigned long long* f = reinterpret_cast<const unsigned long long*>(own + x.flag_offset(slot, threadIdx.x));
+    const long long t0 = clock64();
+    while (ld_acquire_sys(f) != epoch) {
+      if (clock64() - t0 > 8000000000ll) {  // ~4 s: a peer died or the callers disagree about the batch order
+        atomicExch(error_word, 1u);
+        break;
+      }
+      __nanosleep(100);
+    }
+  }
+}
+
+// One block per query: the same bitonic merge as merge_topk_kernel, reading the slot in place.
 __global__ void __launch_bounds__(256) exchange_merge_kernel(ExchangeView x, int slot, unsigned long long epoch,
                                                              int nq, int k, int P, int64_t* __restrict__ out_rows,
                                                              double* __restrict__ out_dist,
@@ -71,18 +90,8 @@ __global__ void __launch_bounds__(256) exchange_merge_kernel(ExchangeView x, int
   double* sd = reinterpret_cast<double*>(esm);
   int64_t* sr = reinterpret_cast<int64_t*>(sd + P);
   const uint8_t* own = reinterpret_cast<const uint8_t*>(x.peers[x.rank]);
-  if (threadIdx.x < x.world) {
-    const unsigned long long* f = reinterpret_cast<const unsigned long long*>(own + x.flag_offset(slot, threadIdx.x));
-    const long long t0 = clock64();
-    while (ld_acquire_sys(f) != epoch) {
-      if (clock64() - t0 > 8000000000ll) {  // ~4 s: a peer died or the callers disagree about the batch order
-        atomicExch(error_word, 1u);
-        break;
-      }
-      __nanosleep(200);
-    }
-  }
-  __syncthreads();
+  (void)epoch;
+  (void)error_word;
   const int q = blockIdx.x;
   const int G = x.world;
   for (int i = threadIdx.x; i < P; i += blockDim.x) {
@@ -159,6 +168,8 @@ int launch_exchange_merge(const ExchangeView& x, int slot, unsigned long long ep
   }
   if (smem > 48 * 1024)
     OMR_CUDA_OK(cudaFuncSetAttribute(exchange_merge_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  exchange_wait_kernel<<<1, 32, 0, st>>>(x, slot, epoch, error_word);
+  OMR_CUDA_OK(cudaGetLastError());
   exchange_merge_kernel<<<nq, 256, smem, st>>>(x, slot, epoch, nq, k, P, out_rows, out_dist, out_count, error_word);
   OMR_CUDA_OK(cudaGetLastError());
   return 0;
