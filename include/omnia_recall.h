@@ -167,6 +167,18 @@ OMR_API int omr_search_rows(omr_store* s, const float* queries, int32_t nq, int3
                             int32_t n_filters, const int32_t* query_filter, int32_t k, int64_t* rows,
                             double* distances, int32_t* counts);
 
+/* Pipelined form of omr_search_rows for a serving loop: _begin stages the batch (host->device copy,
+ * bitmaps, search, device->host read-back) on an internal stream and returns at once; _finish(ticket)
+ * waits for it and fills the caller's arrays.  Up to four batches may be in flight, so the copies and the
+ * select / rescore tail of one batch overlap the scorer of the next.  `queries` must stay valid until
+ * _finish when it is page-locked memory (it is then copied from directly); pageable memory is copied
+ * before _begin returns.  Filters are consumed before _begin returns. */
+OMR_API int omr_search_rows_begin(omr_store* s, const float* queries, int32_t nq, int32_t dim,
+                                  const omr_filter* filters, int32_t n_filters, const int32_t* query_filter,
+                                  int32_t k, int32_t* ticket);
+OMR_API int omr_search_rows_finish(omr_store* s, int32_t ticket, int64_t* rows, double* distances,
+                                   int32_t* counts);
+
 /* The whole cosine arm of the hybrid query: cosine_ann (top 4*fanout observations) ->
  * cosine (nearest observation per entity) -> cosine_ranked (LIMIT fanout)
  * (internal/memory/store.go:240-272).  hits[i] is the entity's nearest observation,

@@ -91,6 +91,9 @@ SIGNATURES = {
                              C.c_int32, C.c_void_p, C.c_void_p]),
     "omr_search_rows": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.POINTER(Filter), C.c_int32,
                                   C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "omr_search_rows_begin": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.POINTER(Filter), C.c_int32,
+                                        C.c_void_p, C.c_int32, C.POINTER(C.c_int32)]),
+    "omr_search_rows_finish": (C.c_int, [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p]),
     "omr_cosine_ranked": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.POINTER(Filter), C.c_int32, C.c_void_p,
                                     C.POINTER(C.c_int32)]),
     "omr_selfjoin": (C.c_int, [C.c_void_p, C.POINTER(SelfJoinOpts), C.c_void_p, C.c_int64, C.POINTER(C.c_int64)]),

@@ -210,6 +210,16 @@ struct omr_store {
     DevBuf<int32_t> xcount;
     int xslot = -1, xnq = 0, xk = 0, nfail_seen = 0;
     unsigned long long xepoch = 0;
+    // host-buffer batches in flight (omr_search_rows_begin/_finish)
+    DevBuf<float> hq;
+    DevBuf<int32_t> hgroup, hcount;
+    DevBuf<double> hmaxd, hdist;
+    DevBuf<int64_t> hrows;
+    DevBuf<uint32_t> hbitmaps;
+    DevBuf<DeviceFilter> hfilters;
+    PinBuf<uint8_t> hin, hout;
+    int hnq = 0, hk = 0;
+    bool host_batch = false;
   };
   static constexpr int kLanes = 5;   // lane 0: synchronous calls; lanes 1..4: batches in flight
   Lane lanes[kLanes];
@@ -348,6 +358,8 @@ void omr_store::destroy() {
   for (Lane& L : lanes) {
     if (L.stream) cudaStreamSynchronize(L.stream);
     L.xlocal.release(); L.xcount.release();
+    L.hq.release(); L.hgroup.release(); L.hcount.release(); L.hmaxd.release(); L.hdist.release(); L.hrows.release();
+    L.hbitmaps.release(); L.hfilters.release(); L.hin.release(); L.hout.release();
     L.qn.release(); L.qnorm2.release(); L.cand.release(); L.fail_list.release(); L.counters.release();
     L.extra_cnt.release(); L.timing.release(); L.pin.release();
     for (cudaEvent_t e : {L.ev_in, L.ev_done, L.ev0, L.ev1})
@@ -1176,6 +1188,114 @@ int omr_search_rows(omr_store* s, const float* queries, int32_t nq, int32_t dim,
   return s->submit(r);
 }
 
+// ---- host buffers, pipelined ------------------------------------------------------------------
+
+int omr_search_rows_begin(omr_store* s, const float* queries, int32_t nq, int32_t dim, const omr_filter* filters,
+                          int32_t n_filters, const int32_t* query_filter, int32_t k, int32_t* ticket) {
+  if (!s || !queries || !ticket) return fail_msg(OMR_E_INVALID, "memory: omr_search_rows_begin: null argument");
+  if (dim != s->dim)
+    return fail_msg(OMR_E_DIM, "memory: similar observations: different vector dimensions %d and %d", s->dim, dim);
+  if (nq <= 0) return fail_msg(OMR_E_INVALID, "memory: omr_search_rows_begin: empty batch");
+  if (n_filters <= 0 || !filters) return fail_msg(OMR_E_WORKSPACE, "memory: workspace_id is required");
+  if (k <= 0) k = 5;
+  std::lock_guard<std::mutex> lk(s->mu);
+  cudaSetDevice(s->cfg.device);
+  int idx = -1;
+  for (int i = 1; i < omr_store::kLanes; i++)
+    if (!s->lanes[i].busy) { idx = i; break; }
+  if (idx < 0) return fail_msg(OMR_E_CAPACITY, "memory: %d batches are already in flight; finish one first", omr_store::kLanes - 1);
+  omr_store::Lane& L = s->lanes[idx];
+  int rc;
+  const size_t qbytes = (size_t)nq * s->dim * 4;
+  const size_t fbytes = (size_t)n_filters * sizeof(DeviceFilter);
+  // pinned staging: filters | max_dist | query_group | (queries, unless the caller's buffer is page-locked)
+  const size_t off_m = (fbytes + 15) & ~size_t(15), off_g = off_m + (size_t)nq * 8, off_q = (off_g + (size_t)nq * 4 + 15) & ~size_t(15);
+  if ((rc = L.hin.reserve(off_q + qbytes))) return rc;
+  DeviceFilter* df = reinterpret_cast<DeviceFilter*>(L.hin.p);
+  double* pm = reinterpret_cast<double*>(L.hin.p + off_m);
+  int32_t* pg = reinterpret_cast<int32_t*>(L.hin.p + off_g);
+  std::vector<double> fmax((size_t)n_filters);
+  for (int i = 0; i < n_filters; i++)
+    if ((rc = s->to_device_filter(filters[i], &df[i], &fmax[i]))) return rc;
+  for (int i = 0; i < nq; i++) {
+    const int g = query_filter ? query_filter[i] : 0;
+    if (g < 0 || g >= n_filters) return fail_msg(OMR_E_INVALID, "memory: query %d names filter %d of %d", i, g, n_filters);
+    pg[i] = g;
+    pm[i] = fmax[g];
+  }
+  const float* qsrc = reinterpret_cast<const float*>(L.hin.p + off_q);
+  {
+    cudaPointerAttributes attr{};
+    if (cudaPointerGetAttributes(&attr, queries) == cudaSuccess && attr.type == cudaMemoryTypeHost) qsrc = queries;
+    else { cudaGetLastError(); memcpy(L.hin.p + off_q, queries, qbytes); }
+  }
+  if ((rc = L.hq.reserve((size_t)nq * s->dim))) return rc;
+  if ((rc = L.hgroup.reserve((size_t)nq))) return rc;
+  if ((rc = L.hmaxd.reserve((size_t)nq))) return rc;
+  if ((rc = L.hfilters.reserve((size_t)n_filters))) return rc;
+  if ((rc = L.hbitmaps.reserve((size_t)n_filters * s->words()))) return rc;
+  if ((rc = L.hrows.reserve((size_t)nq * k))) return rc;
+  if ((rc = L.hdist.reserve((size_t)nq * k))) return rc;
+  if ((rc = L.hcount.reserve((size_t)nq))) return rc;
+  if ((rc = L.hout.reserve((size_t)nq * k * 16 + (size_t)nq * 4))) return rc;
+  cudaStream_t st = L.stream;
+  OMR_CUDA_OK(cudaMemcpyAsync(L.hq.p, qsrc, qbytes, cudaMemcpyHostToDevice, st));
+  OMR_CUDA_OK(cudaMemcpyAsync(L.hgroup.p, pg, (size_t)nq * 4, cudaMemcpyHostToDevice, st));
+  OMR_CUDA_OK(cudaMemcpyAsync(L.hmaxd.p, pm, (size_t)nq * 8, cudaMemcpyHostToDevice, st));
+  OMR_CUDA_OK(cudaMemcpyAsync(L.hfilters.p, df, fbytes, cudaMemcpyHostToDevice, st));
+  if ((rc = launch_build_bitmaps(s->meta(), s->n, (int)s->words(), L.hfilters.p, n_filters, L.hbitmaps.p, st))) return rc;
+  s->st_launches++;
+  bool fused = true;
+  if ((rc = s->enqueue(L, L.hq.p, nq, L.hbitmaps.p, L.hgroup.p, L.hmaxd.p, k, L.hrows.p, L.hdist.p, L.hcount.p, st, &fused)))
+    return rc;
+  L.immediate = false;
+  if (!fused || L.nfail_known >= 0) {
+    if ((rc = s->complete(L, st))) return rc;
+    L.immediate = true;
+  }
+  int64_t* orow = reinterpret_cast<int64_t*>(L.hout.p);
+  OMR_CUDA_OK(cudaMemcpyAsync(orow, L.hrows.p, (size_t)nq * k * 8, cudaMemcpyDeviceToHost, st));
+  OMR_CUDA_OK(cudaMemcpyAsync(L.hout.p + (size_t)nq * k * 8, L.hdist.p, (size_t)nq * k * 8, cudaMemcpyDeviceToHost, st));
+  OMR_CUDA_OK(cudaMemcpyAsync(L.hout.p + (size_t)nq * k * 16, L.hcount.p, (size_t)nq * 4, cudaMemcpyDeviceToHost, st));
+  L.hnq = nq;
+  L.hk = k;
+  L.host_batch = true;
+  L.busy = true;
+  *ticket = idx;
+  return OMR_OK;
+}
+
+int omr_search_rows_finish(omr_store* s, int32_t ticket, int64_t* rows, double* distances, int32_t* counts) {
+  if (!s || !rows || !distances || !counts || ticket < 1 || ticket >= omr_store::kLanes)
+    return fail_msg(OMR_E_INVALID, "memory: omr_search_rows_finish: bad argument");
+  std::lock_guard<std::mutex> lk(s->mu);
+  cudaSetDevice(s->cfg.device);
+  omr_store::Lane& L = s->lanes[ticket];
+  if (!L.busy || !L.host_batch) return fail_msg(OMR_E_INVALID, "memory: ticket %d is not a host batch in flight", ticket);
+  int rc = OMR_OK;
+  const size_t nk = (size_t)L.hnq * L.hk;
+  if (!L.immediate) {
+    rc = s->complete(L, L.stream);
+    if (rc == OMR_OK && L.nfail_seen > 0) {   // the exact fallback rewrote some answers after the first read-back
+      cudaMemcpyAsync(L.hout.p, L.hrows.p, nk * 8, cudaMemcpyDeviceToHost, L.stream);
+      cudaMemcpyAsync(L.hout.p + nk * 8, L.hdist.p, nk * 8, cudaMemcpyDeviceToHost, L.stream);
+      cudaMemcpyAsync(L.hout.p + nk * 16, L.hcount.p, (size_t)L.hnq * 4, cudaMemcpyDeviceToHost, L.stream);
+    }
+  }
+  if (rc == OMR_OK) {
+    cudaError_t e = cudaStreamSynchronize(L.stream);
+    if (e != cudaSuccess) rc = fail_cuda(e, "cudaStreamSynchronize", __FILE__, __LINE__);
+  }
+  if (rc == OMR_OK) {
+    memcpy(rows, L.hout.p, nk * 8);
+    memcpy(distances, L.hout.p + nk * 8, nk * 8);
+    memcpy(counts, L.hout.p + nk * 16, (size_t)L.hnq * 4);
+  }
+  L.busy = false;
+  L.host_batch = false;
+  return rc;
+}
+
 int omr_cosine_ranked(omr_store* s, const float* query, int32_t dim, const omr_filter* filter, int32_t fanout,
                       omr_hit* hits, int32_t* count) {
   if (!s || !query || !filter || !hits || !count) return fail_msg(OMR_E_INVALID, "memory: omr_cosine_ranked: null argument");
@@ -1274,7 +1394,7 @@ int omr_device_search_finish(omr_store* s, int32_t ticket) {
   std::lock_guard<std::mutex> lk(s->mu);
   cudaSetDevice(s->cfg.device);
   omr_store::Lane& L = s->lanes[ticket];
-  if (!L.busy) return fail_msg(OMR_E_INVALID, "memory: ticket %d is not in flight", ticket);
+  if (!L.busy || L.host_batch || L.xslot >= 0) return fail_msg(OMR_E_INVALID, "memory: ticket %d is not in flight", ticket);
   int rc = OMR_OK;
   if (!L.immediate) {
     rc = s->complete(L, L.stream);   // waits for the lane, runs the exact fallback if a certificate failed

@@ -277,6 +277,25 @@ class GPUMemoryStore:
                                           dist.ctypes.data, counts.ctypes.data))
         return rows, dist, counts
 
+    def search_rows_begin(self, queries, filters: Sequence[FilterSpec], k: int,
+                          query_filter: Optional[np.ndarray] = None) -> int:
+        """omr_search_rows_begin: stage a host batch and return its ticket (at most four in flight)."""
+        q = np.ascontiguousarray(queries, np.float32)
+        if q.ndim == 1:
+            q = q[None, :]
+        qf = None if query_filter is None else np.ascontiguousarray(query_filter, np.int32)
+        fa = _filters_array(filters)
+        ticket = C.c_int32(0)
+        L.check(self._lib.omr_search_rows_begin(self._h, q.ctypes.data, q.shape[0], q.shape[1], fa, len(filters),
+                                                None if qf is None else qf.ctypes.data, k, C.byref(ticket)))
+        return ticket.value
+
+    def search_rows_finish(self, ticket: int, out):
+        rows, dist, counts = out
+        L.check(self._lib.omr_search_rows_finish(self._h, ticket, rows.ctypes.data, dist.ctypes.data,
+                                                 counts.ctypes.data))
+        return rows, dist, counts
+
     def find_similar_observations(self, scope: Dict[str, str], query_embedding, k: int,
                                   min_similarity: float, now_us: int = 0) -> List[SimilarObservation]:
         """FindSimilarObservations (store_read.go:243-306): most similar first, similarity >= min."""

@@ -51,3 +51,34 @@ def test_pipelined_equals_synchronous(n, dim, nq, k, path):
             s.device_search_finish(t)
         with pytest.raises(RecallError, match="not in flight"):
             s.device_search_finish(tickets[0])
+
+
+def test_host_buffer_pipeline_equals_synchronous_call():
+    """omr_search_rows_begin/_finish with filters, from pageable and from page-locked query buffers."""
+    from omnia_b200 import FilterSpec
+    n, dim, nq, k = 40_000, 128, 96, 10
+    corpus = synth.gauss_unit(n, dim)
+    ws = (np.arange(n) % 2).astype(np.uint32)
+    batches = [synth.queries_from(corpus, nq, seed=s) for s in range(6)]
+    pinned = [torch.from_numpy(b).pin_memory().numpy() for b in batches]
+    flt = [FilterSpec("w0"), FilterSpec("w1", max_distance=0.8)]
+    qf = (np.arange(nq) % 2).astype(np.int32)
+    with GPUMemoryStore(dim, n) as s:
+        s.bulk_load(corpus, workspaces=["w0", "w1"], workspace_idx=ws)
+        want = [s.search_rows(b, flt, k, qf) for b in batches]
+        for src in (batches, pinned):
+            outs = [(np.empty((nq, k), np.int64), np.empty((nq, k), np.float64), np.empty(nq, np.int32)) for _ in src]
+            pend = []
+            for i, b in enumerate(src):
+                pend.append((s.search_rows_begin(b, flt, k, qf), i))
+                if len(pend) == 3:
+                    tkt, j = pend.pop(0)
+                    s.search_rows_finish(tkt, outs[j])
+            for tkt, j in pend:
+                s.search_rows_finish(tkt, outs[j])
+            for w, g in zip(want, outs):
+                assert all(np.array_equal(a, b) for a, b in zip(w, g))
+        with pytest.raises(RecallError, match="different vector dimensions"):
+            s.search_rows_begin(np.zeros((2, 3), np.float32), flt, k)
+        with pytest.raises(RecallError, match="workspace_id is required"):
+            s.search_rows_begin(batches[0], [FilterSpec("")], k)
