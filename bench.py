@@ -110,20 +110,29 @@ class ClockSampler:
 
 # ------------------------------------------------------------------ CPU baseline / reference arm
 
+def host_threads() -> int:
+    """Every host core this process may use (torchrun exports OMP_NUM_THREADS=1, which must not throttle
+    the CPU arm: the thread count is passed to the oracle explicitly)."""
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return max(1, os.cpu_count() or 1)
+
+
 def cpu_scan_rate(corpus: np.ndarray, queries: np.ndarray, target_s: float):
     """Times the CPU restatement (oracle_vec: pgvector's loop built with pgvector's flags, exact
     sequential scan + top-k, OpenMP over queries) on a bounded sample.  Returns (qps, n, secs, threads)."""
     from oracle import oracle as O
-    threads = O.max_threads()
+    threads = host_threads()
     probe = queries[:threads]
-    O.search(corpus, probe[:1], TOPK, variant=O.VARIANT_F32_VEC)          # page the corpus in
+    O.search(corpus, probe[:1], TOPK, variant=O.VARIANT_F32_VEC, threads=threads)          # page the corpus in
     t0 = time.perf_counter()
-    O.search(corpus, probe, TOPK, variant=O.VARIANT_F32_VEC)
+    O.search(corpus, probe, TOPK, variant=O.VARIANT_F32_VEC, threads=threads)
     t_round = time.perf_counter() - t0
     rounds = max(1, int(target_s / max(t_round, 1e-3)))
     n = min(len(queries), threads * rounds)
     t0 = time.perf_counter()
-    O.search(corpus, queries[:n], TOPK, variant=O.VARIANT_F32_VEC)
+    O.search(corpus, queries[:n], TOPK, variant=O.VARIANT_F32_VEC, threads=threads)
     dt = time.perf_counter() - t0
     return n / dt, n, dt, threads
 
@@ -138,19 +147,19 @@ def run_reference(args, rank: int):
     from oracle import oracle as O
     corpus = synth.gauss_unit(N_ROWS, DIM)
     queries = synth.queries_from(corpus, NQ)
-    threads = O.max_threads()
+    threads = host_threads()
     total = args.steps + args.warmup
     per_step = min(6.0, 150.0 / max(1, total))
-    O.search(corpus, queries[:1], TOPK, variant=O.VARIANT_F32_VEC)
+    O.search(corpus, queries[:1], TOPK, variant=O.VARIANT_F32_VEC, threads=threads)
     t0 = time.perf_counter()
-    O.search(corpus, queries[:threads], TOPK, variant=O.VARIANT_F32_VEC)
+    O.search(corpus, queries[:threads], TOPK, variant=O.VARIANT_F32_VEC, threads=threads)
     t_round = time.perf_counter() - t0
     n = min(NQ, threads * max(1, int(per_step / max(t_round, 1e-3))))
     times = []
     for i in range(total):
         q = np.roll(queries, -i * 7, axis=0)[:n]
         t0 = time.perf_counter()
-        O.search(corpus, q, TOPK, variant=O.VARIANT_F32_VEC)
+        O.search(corpus, q, TOPK, variant=O.VARIANT_F32_VEC, threads=threads)
         if i >= args.warmup:
             times.append(time.perf_counter() - t0)
     ms = 1e3 * float(np.mean(times))
