@@ -197,6 +197,10 @@ typedef struct omr_selfjoin_opts {
   int32_t limit;             /* MaxBucketsPerPass; <= 0 = no limit */
   int32_t require_same_kind; /* e1.kind = e2.kind */
   int32_t require_mutable;   /* both mutability = 'mutable' */
+  int32_t part_index;        /* block partition of the pair space: this call scans part part_index ... */
+  int32_t part_count;        /* ... of part_count (0 or 1 = the whole join).  With the matrix replicated on G
+                                GPUs, rank r runs part r of G and the G pair lists are concatenated
+                                (SURVEY.md section 8e); each part applies `limit` to its own pairs. */
 } omr_selfjoin_opts;
 
 typedef struct omr_pair {

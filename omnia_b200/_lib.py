@@ -57,7 +57,8 @@ class Hit(C.Structure):
 
 class SelfJoinOpts(C.Structure):
     _fields_ = [("workspace_id", C.c_char_p), ("similarity_floor", C.c_float), ("limit", C.c_int32),
-                ("require_same_kind", C.c_int32), ("require_mutable", C.c_int32)]
+                ("require_same_kind", C.c_int32), ("require_mutable", C.c_int32), ("part_index", C.c_int32),
+                ("part_count", C.c_int32)]
 
 
 class Pair(C.Structure):

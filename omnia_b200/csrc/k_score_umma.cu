@@ -151,7 +151,8 @@ template <bool kSelfJoin, int S>
 struct KernelArgs {
   int n_a_tiles;   // recall: query tiles; self-join: unused
   int n_b_tiles;   // 256-row tiles of the store
-  int64_t n_work;  // total (a tile, b tile) work items
+  int64_t n_work;  // (a tile, b tile) work items of this launch
+  int64_t work_first, work_step;  // global item = work_first + w * work_step (self-join partitions; 0 / 1 otherwise)
   int k_blocks;
   int nq;          // real queries; tiles are padded with zero queries beyond it
   int n_stages;    // TMA ring depth in use (<= kStages); experiments only, normally kStages
@@ -226,7 +227,7 @@ __global__ void __launch_bounds__(kNumThreads, 1)
       uint32_t phase = 0;
       for (int64_t w = blockIdx.x; w < args.n_work; w += gridDim.x) {
         int a_tile, b_tile;
-        decode_work<kSelfJoin>(w, args.n_a_tiles, a_tile, b_tile);
+        decode_work<kSelfJoin>(args.work_first + w * args.work_step, args.n_a_tiles, a_tile, b_tile);
         for (int kb = 0; kb < args.k_blocks; kb++) {
           ptx::mbar_wait(&bars->empty[stage], phase ^ 1);
           ptx::mbar_arrive_expect_tx(&bars->full[stage], kStageBytes);
@@ -281,7 +282,7 @@ __global__ void __launch_bounds__(kNumThreads, 1)
     pe.stage = pstage;
     for (int64_t w = blockIdx.x; w < args.n_work; w += gridDim.x, it++) {
       int a_tile, b_tile;
-      decode_work<kSelfJoin>(w, args.n_a_tiles, a_tile, b_tile);
+      decode_work<kSelfJoin>(args.work_first + w * args.work_step, args.n_a_tiles, a_tile, b_tile);
       const uint32_t as = it & 1, aphase = (it >> 1) & 1;
       if (!kSelfJoin) {
         const int q = a_tile * kQueryTile + t_local;
@@ -471,6 +472,8 @@ int launch_recall2_s(const CUtensorMap& tmap_q, const CUtensorMap& tmap_rows_hal
   a.n_a_tiles = n_qtiles256;
   a.n_b_tiles = n_tiles;
   a.n_work = (int64_t)n_qtiles256 * n_tiles;
+  a.work_first = 0;
+  a.work_step = 1;
   a.k_blocks = k_blocks;
   a.nq = nq;
   a.bitmaps = bitmaps;
@@ -495,6 +498,8 @@ int launch_recall_s(const CUtensorMap& tmap_q, const CUtensorMap& tmap_rows, int
   a.n_a_tiles = n_qtiles;
   a.n_b_tiles = n_tiles;
   a.n_work = (int64_t)n_qtiles * n_tiles;
+  a.work_first = 0;
+  a.work_step = 1;
   a.k_blocks = k_blocks;
   a.nq = nq;
   a.bitmaps = bitmaps;
@@ -547,14 +552,19 @@ int launch_score_umma2(const CUtensorMap& tmap_q, const CUtensorMap& tmap_rows_h
 }
 
 int launch_selfjoin_umma(const CUtensorMap& tmap_a, const CUtensorMap& tmap_b, int64_t n, int k_blocks,
-                         float threshold, const uint32_t* member_bitmap, PairCand* pairs, unsigned long long cap,
+                         int part_index, int part_count, float threshold, const uint32_t* member_bitmap, PairCand* pairs, unsigned long long cap,
                          unsigned long long* pair_count, int num_sms, cudaStream_t st) {
   if (n <= 0) return 0;
   const int64_t nb = (n + kTileRows - 1) / kTileRows;
   KernelArgs<true, 256> a{};
   a.n_a_tiles = (int)(2 * nb);
   a.n_b_tiles = (int)nb;
-  a.n_work = nb * (nb + 1);  // sum over jb of (2jb + 2)
+  const int64_t total = nb * (nb + 1);  // sum over jb of (2jb + 2)
+  if (part_count < 1) part_count = 1;
+  a.work_first = part_index;          // partition p of P takes the items p, p+P, p+2P, ... (interleaved: balanced)
+  a.work_step = part_count;
+  a.n_work = part_index < total ? (total - part_index + part_count - 1) / part_count : 0;
+  if (a.n_work == 0) return 0;
   a.k_blocks = k_blocks;
   a.pe.member = member_bitmap;
   a.pe.pairs = pairs;

@@ -131,7 +131,7 @@ struct PairCand {
   int32_t a, b;
 };
 int launch_selfjoin_umma(const CUtensorMap& tmap_a, const CUtensorMap& tmap_b, int64_t n, int k_blocks,
-                         float threshold, const uint32_t* member_bitmap, PairCand* pairs, unsigned long long cap,
+                         int part_index, int part_count, float threshold, const uint32_t* member_bitmap, PairCand* pairs, unsigned long long cap,
                          unsigned long long* pair_count, int num_sms, cudaStream_t st);
 int launch_pair_rescore(const ShardView& sh, const PairCand* pairs, unsigned long long n_pairs, double* sim,
                         cudaStream_t st);

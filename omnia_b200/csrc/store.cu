@@ -1609,6 +1609,9 @@ int omr_selfjoin(omr_store* s, const omr_selfjoin_opts* o, omr_pair* out, int64_
   if ((rc = s->w_member.reserve(member.size()))) return rc;
   OMR_CUDA_OK(cudaMemcpyAsync(s->w_member.p, member.data(), member.size() * 4, cudaMemcpyHostToDevice, st));
   if ((rc = s->w_pair_count.reserve(1))) return rc;
+  const int part_count = o->part_count > 0 ? o->part_count : 1;
+  const int part_index = o->part_index;
+  if (part_index < 0 || part_index >= part_count) return fail_msg(OMR_E_INVALID, "memory: self-join part %d of %d", part_index, part_count);
   const double floor_d = (double)o->similarity_floor;  // float32 widened once, as Postgres does
   const float thr = (float)(floor_d - (double)s->margin);
   unsigned long long pcap = std::max<unsigned long long>(s->w_pairs.n, 1ull << 20);
@@ -1616,7 +1619,7 @@ int omr_selfjoin(omr_store* s, const omr_selfjoin_opts* o, omr_pair* out, int64_
   for (int attempt = 0; attempt < 2; attempt++) {
     if ((rc = s->w_pairs.reserve((size_t)pcap))) return rc;
     OMR_CUDA_OK(cudaMemsetAsync(s->w_pair_count.p, 0, 8, st));
-    if ((rc = launch_selfjoin_umma(ta, tb, m, s->pitch / kBlockK, thr, s->w_member.p, s->w_pairs.p, pcap,
+    if ((rc = launch_selfjoin_umma(ta, tb, m, s->pitch / kBlockK, part_index, part_count, thr, s->w_member.p, s->w_pairs.p, pcap,
                                    s->w_pair_count.p, s->num_sms, st)))
       return rc;
     s->st_launches++;

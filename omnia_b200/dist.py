@@ -166,3 +166,22 @@ class ShardedRecall:
 
     def close(self):
         self.store.close()
+
+
+def sharded_selfjoin(store: GPUMemoryStore, workspace_id: str, similarity_floor: float, max_buckets_per_pass: int = 100,
+                     group=None, **kw):
+    """Near-duplicate self-join block-partitioned over the ranks: every rank holds the
+    whole matrix (C4's 3 GB bf16 replicate easily), scans part `rank` of `world` of the tile-pair space, and the
+    variable-length pair lists are exchanged (counts first, then payload, via all_gather_object) and merged:
+    ORDER BY similarity DESC, LIMIT n.  Returns the same list on every rank."""
+    live = dist.is_available() and dist.is_initialized()
+    rank = dist.get_rank(group) if live else 0
+    world = dist.get_world_size(group) if live else 1
+    mine = store.run_entity_duplicate_candidates(workspace_id, similarity_floor, max_buckets_per_pass,
+                                                 part_index=rank, part_count=world, **kw)
+    if world == 1:
+        return mine
+    parts = [None] * world
+    dist.all_gather_object(parts, mine, group=group)
+    merged = sorted((p for part in parts for p in part), key=lambda p: (-p.similarity, p.canonical_row, p.dupe_row))
+    return merged[:max_buckets_per_pass] if max_buckets_per_pass > 0 else merged

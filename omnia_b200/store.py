@@ -307,6 +307,20 @@ class GPUMemoryStore:
         return [SimilarObservation(id_str(hits[j].observation_id), id_str(hits[j].entity_id),
                                    1.0 - hits[j].distance, hits[j].row) for j in range(int(counts[0]))]
 
+    def pre_write_dedup(self, scope: Dict[str, str], embedding, *,
+                        auto_supersede_above: float = DEFAULT_AUTO_SUPERSEDE_SIMILARITY,
+                        surface_duplicates_above: float = DEFAULT_SURFACE_DUPLICATE_SIMILARITY,
+                        candidate_limit: int = DEFAULT_DUPLICATE_CANDIDATE_LIMIT, now_us: int = 0):
+        """The embedding-similarity branch of SaveMemoryWithResult (internal/memory/api/service_write.go:63-104,
+        213-228): FindSimilarObservations(scope, vec, candidateLimit, surfaceDuplicatesAbove); a top match at or
+        above autoSupersedeAbove routes to AppendObservationToEntity (auto-supersede), anything else lands
+        normally with the matches surfaced as PotentialDuplicates.
+        Returns ("auto_supersede", top_match, matches) or ("insert", None, matches)."""
+        matches = self.find_similar_observations(scope, embedding, candidate_limit, surface_duplicates_above, now_us)
+        if matches and matches[0].similarity >= auto_supersede_above:
+            return "auto_supersede", matches[0], matches
+        return "insert", None, matches
+
     def cosine_ranked(self, flt: FilterSpec, query_embedding, fanout: int):
         """cosine_ann -> cosine -> cosine_ranked (store.go:240-272): [(entity_id, cos_dist, cos_rn)]."""
         q = np.ascontiguousarray(query_embedding, np.float32).reshape(-1)
@@ -319,10 +333,12 @@ class GPUMemoryStore:
     # -- consolidation -----------------------------------------------------------
     def run_entity_duplicate_candidates(self, workspace_id: str, similarity_floor: float = 0.85,
                                         max_buckets_per_pass: int = 100, require_same_kind: bool = True,
-                                        require_mutable: bool = True) -> List[DuplicatePair]:
-        """RunEntityDuplicateCandidates (consolidation_prefilter.go:176-203; defaults worker.go:432-451)."""
+                                        require_mutable: bool = True, part_index: int = 0,
+                                        part_count: int = 1) -> List[DuplicatePair]:
+        """RunEntityDuplicateCandidates (consolidation_prefilter.go:176-203; defaults worker.go:432-451).
+        part_index / part_count: scan only that block partition of the pair space (multi-GPU, see dist.py)."""
         opts = L.SelfJoinOpts(_cstr(workspace_id), float(similarity_floor), int(max_buckets_per_pass),
-                              int(require_same_kind), int(require_mutable))
+                              int(require_same_kind), int(require_mutable), int(part_index), int(part_count))
         cap = max_buckets_per_pass if max_buckets_per_pass > 0 else 1 << 16
         while True:
             out = (L.Pair * max(1, cap))()

@@ -180,3 +180,22 @@ def test_cosine_arm_keeps_nearest_observation_per_entity():
         assert [(e, rn) for e, _, rn in got] == [(str(e12), 1), (str(e10), 2), (str(e11), 3)]
         assert np.allclose([d for _, d, _ in got], [0.05, 0.1, 0.2], atol=1e-6)
         assert len(s.cosine_ranked(FilterSpec(WS1), one_hot(0), 2)) == 2          # LIMIT fanout
+
+
+def test_pre_write_dedup_thresholds():
+    # service_write.go:63-104 with the defaults of types.go:137-141 (0.95 / 0.85, 5 candidates);
+    # mirrors TestMemoryService_AutoSupersedesByEmbeddingSimilarity (internal/memory/api/service_test.go:898-942)
+    with new_store() as s:
+        scope = {SCOPE_WORKSPACE_ID: WS1, SCOPE_VIRTUAL_USER_ID: "u1"}
+        def mix(c):
+            v = np.zeros(DIM, np.float32); v[0] = c; v[1] = math.sqrt(1 - c * c); return v
+        ids = {}
+        for name, c in [("same", 0.99), ("close", 0.90), ("far", 0.50)]:
+            ids[name] = save(s, scope, mix(c))[0]
+        action, top, matches = s.pre_write_dedup(scope, one_hot(0))
+        assert action == "auto_supersede" and top.observation_id == ids["same"]
+        assert [m.observation_id for m in matches] == [ids["same"], ids["close"]]      # >= 0.85 only, nearest first
+        s.supersede(ids["same"])
+        action, top, matches = s.pre_write_dedup(scope, one_hot(0))
+        assert action == "insert" and top is None and [m.observation_id for m in matches] == [ids["close"]]
+        assert s.pre_write_dedup({SCOPE_WORKSPACE_ID: WS1, SCOPE_VIRTUAL_USER_ID: "someone-else"}, one_hot(0))[2] == []

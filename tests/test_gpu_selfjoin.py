@@ -66,3 +66,22 @@ def test_selfjoin_is_scoped_to_one_workspace_and_float32_floor():
                              np.array([[0] * 15 + [0], [0] * 15 + [1]], np.uint8), 0.99, variant=O.VARIANT_F64)
         g, _ = gpu_pairs(s, "w0", 0.99)
         assert len(g) == len(a)
+
+
+@pytest.mark.parametrize("parts", [2, 3, 8])
+def test_block_partitions_of_the_pair_space_union_to_the_whole_join(parts):
+    """The multi-GPU form: G ranks with a replicated matrix each scan one interleaved
+    partition of the tile pairs; here the G parts run one after another on one GPU."""
+    n, dim = 5000, 128
+    corpus, _ = synth.planted_dups(n, dim, n_pairs=60)
+    with GPUMemoryStore(dim, n) as s:
+        s.bulk_load(corpus)
+        whole, _ = gpu_pairs(s, "default", 0.9)
+        union = []
+        for p in range(parts):
+            got, _ = gpu_pairs(s, "default", 0.9, part_index=p, part_count=parts)
+            union += got
+        assert len(union) == len(whole) and sorted(union) == sorted(whole)
+        assert len(whole) >= 30
+        top5 = sorted(union, key=lambda t: (-t[2], t[0], t[1]))[:5]
+        assert top5 == whole[:5]
