@@ -24,7 +24,8 @@ __global__ void __launch_bounds__(256) normalize_rows_kernel(const float* __rest
                                                              int pitch, int64_t row0,
                                                              __nv_bfloat16* __restrict__ out_bf16,
                                                              float* __restrict__ out_f32,
-                                                             double* __restrict__ norm2, int64_t n_pad) {
+                                                             double* __restrict__ norm2, int64_t n_pad,
+                                                             int32_t* __restrict__ bad_flag) {
   const int lane = threadIdx.x & 31;
   const int64_t r = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   if (r >= n_pad) return;
@@ -52,6 +53,8 @@ __global__ void __launch_bounds__(256) normalize_rows_kernel(const float* __rest
     ob[i] = __float2bfloat16_rn(v * inv);
   }
   if (lane == 0 && norm2) norm2[row0 + r] = ss;
+  // a NaN element makes the sum NaN, an infinite one makes it +inf (fp64 cannot overflow on fp32 squares)
+  if (lane == 0 && bad_flag && !isfinite(ss)) atomicOr(bad_flag, ss != ss ? 1 : 2);
 }
 
 __device__ __forceinline__ bool scope_ok(uint32_t col, uint32_t want, int mode) {
@@ -102,13 +105,13 @@ int launch_ingest_rows(const float* src, int64_t n, int dim, int pitch, int64_t 
   if (n <= 0) return 0;
   const int warps = 8;
   normalize_rows_kernel<<<(unsigned)((n + warps - 1) / warps), warps * 32, 0, st>>>(
-      src, n, dim, pitch, row0, rows_bf16, rows_f32, norm2, n);
+      src, n, dim, pitch, row0, rows_bf16, rows_f32, norm2, n, nullptr);
   OMR_CUDA_OK(cudaGetLastError());
   return 0;
 }
 
 int launch_prep_queries(const float* q, int nq, int qpad, int dim, int pitch, __nv_bfloat16* qn, double* qnorm2,
-                        cudaStream_t st) {
+                        int32_t* bad_flag, cudaStream_t st) {
   const int warps = 8;
   static bool carveout_set = false;  // see k_post.cu: query preparation of batch i+1 runs beside scorer CTAs of batch i
   if (!carveout_set) {
@@ -117,7 +120,7 @@ int launch_prep_queries(const float* q, int nq, int qpad, int dim, int pitch, __
     carveout_set = true;
   }
   normalize_rows_kernel<<<(unsigned)((qpad + warps - 1) / warps), warps * 32, 0, st>>>(
-      q, nq, dim, pitch, 0, qn, nullptr, qnorm2, qpad);
+      q, nq, dim, pitch, 0, qn, nullptr, qnorm2, qpad, bad_flag);
   OMR_CUDA_OK(cudaGetLastError());
   return 0;
 }

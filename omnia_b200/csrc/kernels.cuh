@@ -10,8 +10,9 @@ namespace omr {
 // ---- ingest / query preparation (k_ingest.cu) ------------------------------
 int launch_ingest_rows(const float* src, int64_t n, int dim, int pitch, int64_t row0, __nv_bfloat16* rows_bf16,
                        float* rows_f32, double* norm2, cudaStream_t st);
+// bad_flag (nullable): set to 1 / 2 when a query holds a NaN / an infinite element
 int launch_prep_queries(const float* q, int nq, int qpad, int dim, int pitch, __nv_bfloat16* qn, double* qnorm2,
-                        cudaStream_t st);
+                        int32_t* bad_flag, cudaStream_t st);
 constexpr uint32_t kAnyWorkspaceId = 0xFFFFFFFFu;  // DeviceFilter.workspace wildcard
 int launch_build_bitmaps(RowMetaView meta, int64_t n, int words_per_group, const DeviceFilter* filters,
                          int n_filters, uint32_t* bitmaps, cudaStream_t st);

@@ -560,7 +560,7 @@ int omr_store::enqueue(Lane& L, const float* d_q, int nq, const uint32_t* d_bitm
   int32_t* fail_count = L.counters.p + 1;
   const ShardView sh = view();
 
-  rc = launch_prep_queries(d_q, nq, qpad, dim, pitch, L.qn.p, L.qnorm2.p, st);
+  rc = launch_prep_queries(d_q, nq, qpad, dim, pitch, L.qn.p, L.qnorm2.p, L.counters.p + 2, st);
   if (rc) return rc;
   st_launches++;
 
@@ -581,6 +581,7 @@ int omr_store::enqueue(Lane& L, const float* d_q, int nq, const uint32_t* d_bitm
     if (rc) return rc;
     st_launches++;
     L.nfail_known = nq;
+    OMR_CUDA_OK(cudaMemcpyAsync(L.pin.p, L.counters.p, 3 * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
     return 0;
   }
   L.nfail_known = -1;
@@ -640,7 +641,7 @@ int omr_store::enqueue(Lane& L, const float* d_q, int nq, const uint32_t* d_bitm
       if ((rc = launch_finalize_extra(fa, st))) return rc;
       st_launches += 5;
     }
-    OMR_CUDA_OK(cudaMemcpyAsync(L.pin.p, L.counters.p, 2 * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+    OMR_CUDA_OK(cudaMemcpyAsync(L.pin.p, L.counters.p, 3 * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
     L.timed = profiling;
   }
   return 0;
@@ -654,8 +655,12 @@ int omr_store::complete(Lane& L, cudaStream_t st) {
   int rc;
   int nfail = L.nfail_known;
   L.nfail_seen = 0;
+  OMR_CUDA_OK(cudaStreamSynchronize(st));
+  // pgvector refuses non-finite elements when the query vector is parsed, so the reference's statement
+  // fails as a whole; the query-preparation kernel flags them
+  if (L.pin.p[2] & 1) return fail_msg(OMR_E_INVALID, "memory: NaN not allowed in vector");
+  if (L.pin.p[2] & 2) return fail_msg(OMR_E_INVALID, "memory: infinite value not allowed in vector");
   if (nfail < 0) {
-    OMR_CUDA_OK(cudaStreamSynchronize(st));
     st_rescued += L.pin.p[0];
     nfail = L.pin.p[1];
     if (L.timed) {
@@ -777,6 +782,17 @@ int omr_store::host_search(const float* queries, int nq, const omr_filter* filte
   for (int i = 0; i < nq; i++) {
     counts[i] = ocnt[i];
     for (int j = 0; j < ocnt[i]; j++) fill_hit(&hits[(size_t)i * k + j], orow[(size_t)i * k + j], odist[(size_t)i * k + j]);
+  }
+  return 0;
+}
+
+// pgvector refuses non-finite elements when a vector is parsed ("NaN not allowed in vector", "infinite value
+// not allowed in vector").  Single vectors are checked here on the host; query batches on the device.
+static int check_finite(const float* v, size_t count) {
+  for (size_t i = 0; i < count; i++) {
+    if (v[i] != v[i]) return fail_msg(OMR_E_INVALID, "memory: NaN not allowed in vector");
+    if (v[i] > 3.402823466e38f || v[i] < -3.402823466e38f)
+      return fail_msg(OMR_E_INVALID, "memory: infinite value not allowed in vector");
   }
   return 0;
 }
@@ -1055,6 +1071,7 @@ int omr_upsert(omr_store* s, const omr_row* row, const float* vec, int32_t dim) 
   if (!s || !row || !vec) return fail_msg(OMR_E_INVALID, "memory: omr_upsert: null argument");
   if (dim != s->dim) return fail_msg(OMR_E_DIM, "memory: embedding dimension mismatch: got %d, store has %d", dim, s->dim);
   if (!row->workspace_id || !row->workspace_id[0]) return fail_msg(OMR_E_WORKSPACE, "memory: workspace_id is required");
+  if (int frc = check_finite(vec, (size_t)dim)) return frc;
   std::lock_guard<std::mutex> lk(s->mu);
   cudaSetDevice(s->cfg.device);
   if (int drc = s->drain()) return drc;
@@ -1096,6 +1113,7 @@ int omr_upsert(omr_store* s, const omr_row* row, const float* vec, int32_t dim) 
 int omr_update_embedding(omr_store* s, const uint8_t entity_id[16], const float* vec, int32_t dim) {
   if (!s || !entity_id || !vec) return fail_msg(OMR_E_INVALID, "memory: omr_update_embedding: null argument");
   if (dim != s->dim) return fail_msg(OMR_E_DIM, "memory: embedding dimension mismatch: got %d, store has %d", dim, s->dim);
+  if (int frc = check_finite(vec, (size_t)dim)) return frc;
   std::lock_guard<std::mutex> lk(s->mu);
   cudaSetDevice(s->cfg.device);
   if (int drc = s->drain()) return drc;
@@ -1698,7 +1716,7 @@ int omr_debug_candidate_keys(omr_store* s, const float* queries, int32_t nq, int
   if ((rc = s->lanes[0].cand.reserve((size_t)qpad * kpq))) return rc;
   if ((rc = s->ensure_live(st))) return rc;
   OMR_CUDA_OK(cudaMemcpyAsync(s->w_queries.p, queries, (size_t)nq * s->dim * 4, cudaMemcpyHostToDevice, st));
-  if ((rc = launch_prep_queries(s->w_queries.p, nq, qpad, s->dim, s->pitch, s->lanes[0].qn.p, s->lanes[0].qnorm2.p, st))) return rc;
+  if ((rc = launch_prep_queries(s->w_queries.p, nq, qpad, s->dim, s->pitch, s->lanes[0].qn.p, s->lanes[0].qnorm2.p, nullptr, st))) return rc;
   if (path == 1) {
     for (int q0 = 0; q0 < nq; q0 += 8) {
       const int c = std::min(8, nq - q0);
@@ -1765,7 +1783,7 @@ int omr_debug_time_scorer(omr_store* s, int32_t nq, int32_t path, int32_t S, int
   if (nq > s->n) return fail_msg(OMR_E_INVALID, "memory: omr_debug_time_scorer needs nq <= rows");
   OMR_CUDA_OK(cudaMemcpy2DAsync(s->w_queries.p, (size_t)s->dim * 4, s->d_f32, (size_t)s->pitch * 4, (size_t)s->dim * 4, nq,
                                 cudaMemcpyDeviceToDevice, st));
-  if ((rc = launch_prep_queries(s->w_queries.p, nq, qpad, s->dim, s->pitch, L.qn.p, L.qnorm2.p, st))) return rc;
+  if ((rc = launch_prep_queries(s->w_queries.p, nq, qpad, s->dim, s->pitch, L.qn.p, L.qnorm2.p, nullptr, st))) return rc;
   if (L.tmap_q_ptr != L.qn.p || L.tmap_q_rows != L.qn.n / s->pitch) {
     if ((rc = s->make_tmap(&L.tmap_q, L.qn.p, L.qn.n / s->pitch, kQueryTile))) return rc;
     L.tmap_q_ptr = L.qn.p;

@@ -199,3 +199,19 @@ def test_pre_write_dedup_thresholds():
         action, top, matches = s.pre_write_dedup(scope, one_hot(0))
         assert action == "insert" and top is None and [m.observation_id for m in matches] == [ids["close"]]
         assert s.pre_write_dedup({SCOPE_WORKSPACE_ID: WS1, SCOPE_VIRTUAL_USER_ID: "someone-else"}, one_hot(0))[2] == []
+
+
+def test_non_finite_vectors_are_refused_like_pgvector():
+    # pgvector rejects NaN / infinity when a vector is parsed, so the reference's statement fails as a whole
+    with new_store() as s:
+        scope = {SCOPE_WORKSPACE_ID: WS1}
+        save(s, scope, one_hot(1))
+        bad = one_hot(2); bad[5] = np.nan
+        inf = one_hot(2); inf[5] = np.inf
+        with pytest.raises(RecallError, match="NaN not allowed in vector"):
+            s.find_similar_observations(scope, bad, 5, 0.5)
+        with pytest.raises(RecallError, match="infinite value not allowed in vector"):
+            s.cosine_ranked(FilterSpec(WS1), inf, 10)
+        with pytest.raises(RecallError, match="NaN not allowed"):
+            s.upsert(uuid.uuid4(), uuid.uuid4(), scope, bad)
+        assert len(s.find_similar_observations(scope, one_hot(1), 5, 0.5)) == 1      # the store is unharmed
