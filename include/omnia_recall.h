@@ -128,6 +128,31 @@ OMR_API int omr_set_entity_flags(omr_store* s, const uint8_t entity_id[16], uint
 OMR_API int omr_set_valid_until(omr_store* s, const uint8_t observation_id[16], int64_t valid_until_us);
 OMR_API int omr_set_confidence(omr_store* s, const uint8_t observation_id[16], float confidence);
 OMR_API int omr_delete_entity(omr_store* s, const uint8_t entity_id[16]); /* hard delete, store_delete.go:60-103 */
+/* Hard delete of one observation: tombstone GC (internal/memory/tombstone.go:124) and the
+ * superseded-grace purge (internal/memory/supersession_store.go:43). */
+OMR_API int omr_delete_observation(omr_store* s, const uint8_t observation_id[16]);
+/* DeleteAll / BatchDelete (internal/memory/store_delete.go:60-125): hard-deletes the entities of a
+ * workspace, narrowed to one user when virtual_user_id is non-empty; limit <= 0 means no limit
+ * (DeleteAll), limit > 0 deletes at most that many entities (BatchDelete).  *deleted (may be NULL)
+ * receives the number of entities removed. */
+OMR_API int omr_delete_scope(omr_store* s, const char* workspace_id, const char* virtual_user_id, int64_t limit,
+                             int64_t* deleted);
+/* Consolidation Rescope (internal/memory/postgres/consolidation_writes.go:75-92): rewrites
+ * virtual_user_id / agent_id of the entities that own the target observations ("" or NULL = SQL NULL,
+ * the statement's NULLIF); every resident row of those entities follows.  Unknown ids match nothing. */
+OMR_API int omr_rescope(omr_store* s, const uint8_t* observation_ids /*[n][16]*/, int32_t n,
+                        const char* virtual_user_id, const char* agent_id);
+/* Consolidation MergeEntities (consolidation_writes.go:104-127): the observations of merge_ids move to
+ * canonical_id and take its entity-level columns (workspace, user, agent, kind, purpose, forgotten,
+ * mutability) when the canonical entity has a resident row; the merged entities are left empty, which
+ * is what their forgotten = true amounts to for recall. */
+OMR_API int omr_merge_entities(omr_store* s, const uint8_t canonical_id[16], const uint8_t* merge_ids /*[n][16]*/,
+                               int32_t n);
+/* Drops every row and identity map; capacity, dimension and device buffers stay.  The embedding
+ * dimension change (internal/memory/postgres/embedding_schema.go:125-151 drops and recreates the
+ * column, discarding all vectors) is omr_close + omr_open at the new dimension; omr_clear is the
+ * same flush when the dimension is unchanged (re-embed with a new model, reembed_worker.go:181-218). */
+OMR_API int omr_clear(omr_store* s);
 
 /* ---- recall ------------------------------------------------------------------
  * The WHERE clause of the recall queries (reference row a8). */

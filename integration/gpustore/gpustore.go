@@ -21,6 +21,8 @@ import (
 	"github.com/google/uuid"
 
 	"github.com/altairalabs/omnia/internal/memory"
+	"github.com/altairalabs/omnia/internal/memory/consolidation"
+	"github.com/altairalabs/omnia/internal/memory/postgres"
 )
 
 // Store is a drop-in memory.Store. Everything delegates to the embedded Postgres store
@@ -234,5 +236,99 @@ func (s *Store) Delete(ctx context.Context, scope map[string]string, memoryID st
 	}
 	id := uuid.MustParse(memoryID)
 	C.omr_set_entity_flags(s.h, (*C.uint8_t)(unsafe.Pointer(&id[0])), C.OMR_ROW_FORGOTTEN, 0)
+	return nil
+}
+
+// DeleteAll mirrors the hard delete of store_delete.go:60-87 (cascade included: rows go with their entity).
+func (s *Store) DeleteAll(ctx context.Context, scope map[string]string) error {
+	if err := s.PostgresMemoryStore.DeleteAll(ctx, scope); err != nil {
+		return err
+	}
+	_, err := s.deleteScope(scope, 0)
+	return err
+}
+
+// BatchDelete mirrors store_delete.go:89-125.  Postgres picks which `limit` entities go, so the GPU
+// side deletes by the ids the statement returned rather than by its own iteration order.
+func (s *Store) BatchDelete(ctx context.Context, scope map[string]string, limit int) (int, error) {
+	ids, err := s.PostgresMemoryStore.BatchDeleteReturningIDs(ctx, scope, limit) // DELETE ... RETURNING id
+	if err != nil {
+		return 0, err
+	}
+	for _, e := range ids {
+		id := uuid.MustParse(e)
+		C.omr_delete_entity(s.h, (*C.uint8_t)(unsafe.Pointer(&id[0])))
+	}
+	return len(ids), nil
+}
+
+func (s *Store) deleteScope(scope map[string]string, limit int64) (int64, error) {
+	ws := C.CString(scope[memory.ScopeWorkspaceID])
+	defer C.free(unsafe.Pointer(ws))
+	var user *C.char
+	if u := scope[memory.ScopeVirtualUserID]; u != "" {
+		user = C.CString(u)
+		defer C.free(unsafe.Pointer(user))
+	}
+	var n C.int64_t
+	if rc := C.omr_delete_scope(s.h, ws, user, C.int64_t(limit), &n); rc != C.OMR_OK {
+		return 0, lastErr(rc)
+	}
+	return int64(n), nil
+}
+
+// ConsolidationWriter wraps postgres.ConsolidationWriter so the scope and entity rewrites of
+// internal/memory/postgres/consolidation_writes.go:63-160 reach the device-side row metadata.
+type ConsolidationWriter struct {
+	*postgres.ConsolidationWriter
+	gpu *Store
+}
+
+func idBlock(ids []string) []byte {
+	out := make([]byte, 0, 16*len(ids))
+	for _, s := range ids {
+		id := uuid.MustParse(s)
+		out = append(out, id[:]...)
+	}
+	return out
+}
+
+func (w *ConsolidationWriter) Rescope(ctx context.Context, rw consolidation.RescopeWrite) error {
+	if err := w.ConsolidationWriter.Rescope(ctx, rw); err != nil || len(rw.TargetIDs) == 0 {
+		return err
+	}
+	ids := idBlock(rw.TargetIDs)
+	user, agent := C.CString(rw.NewScope.UserID), C.CString(rw.NewScope.AgentID)
+	defer C.free(unsafe.Pointer(user))
+	defer C.free(unsafe.Pointer(agent))
+	if rc := C.omr_rescope(w.gpu.h, (*C.uint8_t)(unsafe.Pointer(&ids[0])), C.int32_t(len(rw.TargetIDs)), user, agent); rc != C.OMR_OK {
+		return lastErr(rc)
+	}
+	return nil
+}
+
+func (w *ConsolidationWriter) MergeEntities(ctx context.Context, mw consolidation.MergeWrite) error {
+	if err := w.ConsolidationWriter.MergeEntities(ctx, mw); err != nil || len(mw.MergeIDs) == 0 {
+		return err
+	}
+	canon := uuid.MustParse(mw.CanonicalID)
+	ids := idBlock(mw.MergeIDs)
+	if rc := C.omr_merge_entities(w.gpu.h, (*C.uint8_t)(unsafe.Pointer(&canon[0])),
+		(*C.uint8_t)(unsafe.Pointer(&ids[0])), C.int32_t(len(mw.MergeIDs))); rc != C.OMR_OK {
+		return lastErr(rc)
+	}
+	return nil
+}
+
+// Supersede, Invalidate, Discard and Rescore (consolidation_writes.go:63-73, 94-104, 129-160) map onto
+// omr_set_row_flags / omr_set_valid_until / omr_set_confidence one target id at a time.
+func (w *ConsolidationWriter) Supersede(ctx context.Context, sw consolidation.SupersedeWrite) error {
+	if err := w.ConsolidationWriter.Supersede(ctx, sw); err != nil {
+		return err
+	}
+	for _, t := range sw.TargetIDs {
+		id := uuid.MustParse(t)
+		C.omr_set_row_flags(w.gpu.h, (*C.uint8_t)(unsafe.Pointer(&id[0])), C.OMR_ROW_SUPERSEDED, 0)
+	}
 	return nil
 }

@@ -88,6 +88,11 @@ SIGNATURES = {
     "omr_set_valid_until": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64]),
     "omr_set_confidence": (C.c_int, [C.c_void_p, C.c_void_p, C.c_float]),
     "omr_delete_entity": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "omr_delete_observation": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "omr_delete_scope": (C.c_int, [C.c_void_p, C.c_char_p, C.c_char_p, C.c_int64, C.POINTER(C.c_int64)]),
+    "omr_rescope": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_char_p, C.c_char_p]),
+    "omr_merge_entities": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32]),
+    "omr_clear": (C.c_int, [C.c_void_p]),
     "omr_search": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.POINTER(Filter), C.c_int32, C.c_void_p,
                              C.c_int32, C.c_void_p, C.c_void_p]),
     "omr_search_rows": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.POINTER(Filter), C.c_int32,

@@ -1159,6 +1159,153 @@ int omr_delete_entity(omr_store* s, const uint8_t entity_id[16]) {
   return omr_set_entity_flags(s, entity_id, kRowDeleted, OMR_ROW_HAS_EMBEDDING);
 }
 
+int omr_delete_observation(omr_store* s, const uint8_t observation_id[16]) {
+  return omr_set_row_flags(s, observation_id, kRowDeleted, OMR_ROW_HAS_EMBEDDING);
+}
+
+// Pushes the metadata of a set of rows: one range copy when the set is large, row by row otherwise.
+static int push_rows(omr_store* s, const std::vector<int64_t>& rows) {
+  if (rows.empty()) return OMR_OK;
+  if (rows.size() > 64) {
+    const auto mm = std::minmax_element(rows.begin(), rows.end());
+    return s->push_meta(*mm.first, *mm.second - *mm.first + 1);
+  }
+  for (int64_t r : rows)
+    if (int rc = s->push_meta(r, 1)) return rc;
+  return OMR_OK;
+}
+
+static bool entity_is_live(const omr_store* s, uint32_t ent) {
+  for (int64_t r : s->entity_rows[ent])
+    if (!(s->h_flags[r] & kRowDeleted)) return true;
+  return false;
+}
+
+int omr_delete_scope(omr_store* s, const char* workspace_id, const char* virtual_user_id, int64_t limit,
+                     int64_t* deleted) {
+  if (deleted) *deleted = 0;
+  if (!s) return fail_msg(OMR_E_INVALID, "memory: null argument");
+  if (!workspace_id || !workspace_id[0]) return fail_msg(OMR_E_WORKSPACE, "memory: workspace_id is required");
+  std::lock_guard<std::mutex> lk(s->mu);
+  cudaSetDevice(s->cfg.device);
+  if (int drc = s->drain()) return drc;
+  uint32_t ws = 0, user = 0;
+  if (!s->ws_names.lookup(workspace_id, &ws)) return OMR_OK;  // nothing stored under this workspace
+  const bool by_user = virtual_user_id && virtual_user_id[0];
+  if (by_user && !s->user_names.lookup(virtual_user_id, &user)) return OMR_OK;
+  std::vector<int64_t> touched;
+  int64_t count = 0;
+  for (uint32_t e = 0; e < (uint32_t)s->entity_rows.size(); e++) {
+    if (limit > 0 && count >= limit) break;
+    const auto& rows = s->entity_rows[e];
+    if (rows.empty() || !entity_is_live(s, e)) continue;
+    const int64_t r0 = rows[0];  // entity-level columns are the same on every row of the entity
+    if (s->h_ws[r0] != ws || (by_user && s->h_user[r0] != user)) continue;
+    for (int64_t r : rows) {
+      s->h_flags[r] = (uint8_t)((s->h_flags[r] | kRowDeleted) & ~OMR_ROW_HAS_EMBEDDING);
+      touched.push_back(r);
+    }
+    count++;
+  }
+  if (deleted) *deleted = count;
+  if (touched.size() > 64) {
+    const auto mm = std::minmax_element(touched.begin(), touched.end());
+    OMR_CUDA_OK(cudaMemcpy(s->d_flags + *mm.first, s->h_flags.data() + *mm.first, (size_t)(*mm.second - *mm.first + 1),
+                           cudaMemcpyHostToDevice));
+    s->live_dirty = true;
+    return OMR_OK;
+  }
+  for (int64_t r : touched)
+    if (int rc = s->push_flag(r)) return rc;
+  return OMR_OK;
+}
+
+int omr_rescope(omr_store* s, const uint8_t* observation_ids, int32_t n, const char* virtual_user_id,
+                const char* agent_id) {
+  if (!s || (n > 0 && !observation_ids)) return fail_msg(OMR_E_INVALID, "memory: null argument");
+  std::lock_guard<std::mutex> lk(s->mu);
+  cudaSetDevice(s->cfg.device);
+  if (int drc = s->drain()) return drc;
+  const uint32_t user = (virtual_user_id && virtual_user_id[0]) ? s->user_names.intern(virtual_user_id) : 0;
+  const uint32_t agent = (agent_id && agent_id[0]) ? s->agent_names.intern(agent_id) : 0;
+  std::vector<int64_t> touched;
+  std::vector<uint32_t> done;
+  for (int32_t i = 0; i < n; i++) {
+    auto it = s->obs_row.find(key_of(observation_ids + 16 * (size_t)i));
+    if (it == s->obs_row.end() || (s->h_flags[it->second] & kRowDeleted)) continue;
+    const uint32_t ent = s->h_entity[it->second];
+    if (std::find(done.begin(), done.end(), ent) != done.end()) continue;
+    done.push_back(ent);
+    for (int64_t r : s->entity_rows[ent]) {
+      s->h_user[r] = user;
+      s->h_agent[r] = agent;
+      touched.push_back(r);
+    }
+  }
+  return push_rows(s, touched);
+}
+
+int omr_merge_entities(omr_store* s, const uint8_t canonical_id[16], const uint8_t* merge_ids, int32_t n) {
+  if (!s || !canonical_id || (n > 0 && !merge_ids)) return fail_msg(OMR_E_INVALID, "memory: null argument");
+  std::lock_guard<std::mutex> lk(s->mu);
+  cudaSetDevice(s->cfg.device);
+  if (int drc = s->drain()) return drc;
+  const uint32_t canon = entity_of(s, key_of(canonical_id));
+  // entity-level columns of the canonical entity, when it has a resident row to read them from
+  int64_t src = -1;
+  for (int64_t r : s->entity_rows[canon])
+    if (!(s->h_flags[r] & kRowDeleted)) { src = r; break; }
+  const uint8_t entity_bits = (uint8_t)(OMR_ROW_FORGOTTEN | OMR_ROW_MUTABLE);
+  std::vector<int64_t> touched;
+  for (int32_t i = 0; i < n; i++) {
+    auto it = s->entity_idx.find(key_of(merge_ids + 16 * (size_t)i));
+    if (it == s->entity_idx.end() || it->second == canon) continue;
+    const uint32_t ent = it->second;
+    for (int64_t r : s->entity_rows[ent]) {
+      s->h_entity[r] = canon;
+      s->entity_rows[canon].push_back(r);
+      if (src >= 0) {
+        s->h_ws[r] = s->h_ws[src]; s->h_user[r] = s->h_user[src]; s->h_agent[r] = s->h_agent[src];
+        s->h_kind[r] = s->h_kind[src]; s->h_purpose[r] = s->h_purpose[src];
+        s->h_flags[r] = (uint8_t)((s->h_flags[r] & ~entity_bits) | (s->h_flags[src] & entity_bits));
+      }
+      touched.push_back(r);
+    }
+    s->entity_rows[ent].clear();
+    s->entity_latest[ent] = -1;
+  }
+  if (touched.empty()) return OMR_OK;
+  // the representative (the row UpdateEmbedding targets, the row the self-join reads) is the newest
+  // live embedded row of the merged entity
+  int64_t rep = -1;
+  for (int64_t r : s->entity_rows[canon]) {
+    if (s->h_flags[r] & kRowEntityRep) touched.push_back(r);
+    s->h_flags[r] &= (uint8_t)~kRowEntityRep;
+    if (!(s->h_flags[r] & kRowDeleted) && r > rep) rep = r;
+  }
+  if (rep < 0 && !s->entity_rows[canon].empty())
+    rep = *std::max_element(s->entity_rows[canon].begin(), s->entity_rows[canon].end());
+  if (rep >= 0) {
+    s->h_flags[rep] |= kRowEntityRep;
+    touched.push_back(rep);
+  }
+  s->entity_latest[canon] = rep;
+  return push_rows(s, touched);
+}
+
+int omr_clear(omr_store* s) {
+  if (!s) return fail_msg(OMR_E_INVALID, "memory: null argument");
+  std::lock_guard<std::mutex> lk(s->mu);
+  cudaSetDevice(s->cfg.device);
+  if (int drc = s->drain()) return drc;
+  s->n = 0;
+  grow_host(s, 0);
+  s->entity_id.clear(); s->entity_latest.clear(); s->entity_rows.clear();
+  s->obs_row.clear(); s->entity_idx.clear();
+  s->live_dirty = true;
+  return OMR_OK;
+}
+
 int omr_set_valid_until(omr_store* s, const uint8_t observation_id[16], int64_t valid_until_us) {
   if (!s || !observation_id) return fail_msg(OMR_E_INVALID, "memory: null argument");
   std::lock_guard<std::mutex> lk(s->mu);

@@ -237,6 +237,36 @@ class GPUMemoryStore:
     def delete_entity(self, entity_id: IdLike) -> None:
         L.check(self._lib.omr_delete_entity(self._h, id_bytes(entity_id)))
 
+    def delete_observation(self, observation_id: IdLike) -> None:
+        """Hard delete of one observation (tombstone.go:124, supersession_store.go:43)."""
+        L.check(self._lib.omr_delete_observation(self._h, id_bytes(observation_id)))
+
+    def delete_all(self, scope: Dict[str, str]) -> int:
+        """DeleteAll (store_delete.go:60-87): every entity of the workspace, or of one user in it."""
+        return self.batch_delete(scope, 0)
+
+    def batch_delete(self, scope: Dict[str, str], limit: int) -> int:
+        """BatchDelete (store_delete.go:89-125): at most `limit` entities; returns the count."""
+        n = C.c_int64(0)
+        L.check(self._lib.omr_delete_scope(self._h, _cstr(scope.get(SCOPE_WORKSPACE_ID, "")),
+                                           _cstr(scope.get(SCOPE_VIRTUAL_USER_ID) or None), int(limit), C.byref(n)))
+        return int(n.value)
+
+    def rescope(self, observation_ids: Sequence[IdLike], user_id: str = "", agent_id: str = "") -> None:
+        """ConsolidationWriter.Rescope (postgres/consolidation_writes.go:75-92)."""
+        buf = b"".join(id_bytes(o) for o in observation_ids)
+        L.check(self._lib.omr_rescope(self._h, buf, len(observation_ids), _cstr(user_id or None),
+                                      _cstr(agent_id or None)))
+
+    def merge_entities(self, canonical_id: IdLike, merge_ids: Sequence[IdLike]) -> None:
+        """ConsolidationWriter.MergeEntities (postgres/consolidation_writes.go:104-127)."""
+        buf = b"".join(id_bytes(e) for e in merge_ids)
+        L.check(self._lib.omr_merge_entities(self._h, id_bytes(canonical_id), buf, len(merge_ids)))
+
+    def clear(self) -> None:
+        """Drops every row (re-embed flush; a dimension change is close + reopen)."""
+        L.check(self._lib.omr_clear(self._h))
+
     # -- recall ----------------------------------------------------------------
     def search(self, queries, filters: Sequence[FilterSpec], k: int, query_filter: Optional[np.ndarray] = None):
         """Batched `ORDER BY embedding <=> q LIMIT k`.  Returns (rows [nq,k] int64 (-1 pad),

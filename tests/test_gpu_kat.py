@@ -215,3 +215,74 @@ def test_non_finite_vectors_are_refused_like_pgvector():
         with pytest.raises(RecallError, match="NaN not allowed"):
             s.upsert(uuid.uuid4(), uuid.uuid4(), scope, bad)
         assert len(s.find_similar_observations(scope, one_hot(1), 5, 0.5)) == 1      # the store is unharmed
+
+
+def test_consolidation_writes_and_scope_deletes_move_the_mask():
+    # Rescope / MergeEntities (postgres/consolidation_writes.go:75-127), tombstone GC
+    # (tombstone.go:124), DeleteAll / BatchDelete (store_delete.go:60-125), and the re-embed flush
+    with new_store() as s:
+        v = one_hot(7)
+        ws = {SCOPE_WORKSPACE_ID: WS1}
+        alice = {SCOPE_WORKSPACE_ID: WS1, SCOPE_VIRTUAL_USER_ID: "alice"}
+        bob = {SCOPE_WORKSPACE_ID: WS1, SCOPE_VIRTUAL_USER_ID: "bob"}
+        other = {SCOPE_WORKSPACE_ID: WS2, SCOPE_VIRTUAL_USER_ID: "alice"}
+        a = [save(s, alice, v) for _ in range(3)]
+        b = [save(s, bob, v) for _ in range(2)]
+        o = [save(s, other, v) for _ in range(2)]
+        def count(scope):
+            return len(s.find_similar_observations(scope, v, 50, 0.5))
+        assert (count(alice), count(bob), count(ws), count(other)) == (3, 2, 5, 2)
+
+        # Rescope: alice's first entity becomes bob's; a second observation of that entity follows it
+        extra = uuid.uuid4()
+        s.upsert(extra, a[0][1], alice, v)
+        assert count(alice) == 4
+        s.rescope([a[0][0]], user_id="bob")
+        assert (count(alice), count(bob)) == (2, 4)
+        s.rescope([uuid.uuid4()], user_id="carol")                        # unknown id: UPDATE matches nothing
+        assert count({SCOPE_WORKSPACE_ID: WS1, SCOPE_VIRTUAL_USER_ID: "carol"}) == 0
+        s.rescope([b[0][0]], user_id="")                                  # NULLIF($1, '') -> institutional row
+        assert count(bob) == 3
+        f = FilterSpec(WS1, None, MATCH_NULL_ONLY, None, None, now_us=0)
+        assert int(s.search(v[None, :], [f], 50)[2][0]) == 1
+
+        # MergeEntities: alice's remaining two entities collapse onto the first; per-entity dedup sees one
+        ranked = s.cosine_ranked(FilterSpec(WS1, "alice", now_us=0), v, 50)
+        assert len(ranked) == 2
+        s.merge_entities(a[1][1], [a[2][1]])
+        ranked = s.cosine_ranked(FilterSpec(WS1, "alice", now_us=0), v, 50)
+        assert [r[0] for r in ranked] == [a[1][1]] and count(alice) == 2
+        s.forget(a[1][1])                                                  # the canonical now owns both rows
+        assert count(alice) == 0
+        # rows merged into a bob entity take bob's entity-level columns
+        s.merge_entities(b[1][1], [a[1][1]])
+        assert count(bob) == 5 and count(alice) == 0
+        s.update_embedding(b[1][1], one_hot(8))                            # targets the newest row of the merged entity
+        assert len(s.find_similar_observations(bob, one_hot(8), 5, 0.9)) == 1 and count(bob) == 4
+
+        # tombstone GC of one observation
+        s.delete_observation(extra)
+        assert count(bob) == 3
+        with pytest.raises(NotFound):
+            s.delete_observation(uuid.uuid4())
+
+        # BatchDelete in pages, then DeleteAll of the workspace; the other workspace is untouched
+        with pytest.raises(RecallError, match="workspace_id is required"):
+            s.delete_all({})
+        assert s.batch_delete(bob, 1) == 1
+        total = 1
+        while True:
+            nd = s.batch_delete(bob, 1)
+            if nd == 0:
+                break
+            total += nd
+        assert total == 2 and count(bob) == 0                              # a[0] and b[1] (which absorbed a[1], a[2])
+        assert s.delete_all(ws) == 1 and count(ws) == 0
+        assert s.delete_all({SCOPE_WORKSPACE_ID: "no-such-workspace"}) == 0
+        assert count(other) == 2
+
+        # flush and reload (re-embed with a new model of the same dimension)
+        s.clear()
+        assert len(s) == 0 and count(other) == 0
+        save(s, other, v)
+        assert count(other) == 1
