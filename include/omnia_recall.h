@@ -238,6 +238,26 @@ typedef struct omr_pair {
 /* Writes min(found, cap) pairs ordered by similarity DESC; *found is the total. */
 OMR_API int omr_selfjoin(omr_store* s, const omr_selfjoin_opts* opts, omr_pair* out, int64_t cap, int64_t* found);
 
+/* ---- Memory Galaxy projection input: PCA over resident rows ----------
+ * The reference loads one row per live entity (LoadProjectionInputs,
+ * internal/memory/projection_store.go:33-62), keeps at most Cap of them and reduces their
+ * embeddings to PCADims columns (PCAReduce, ee/pkg/memory/projection/pca.go:28-67: gonum centres
+ * the columns, takes an SVD and multiplies the UNCENTRED matrix by the first k right singular
+ * vectors, in float64).  The parts that grow with the row count run on the GPU from the fp32 master
+ * rows; the D x D symmetric eigenproblem in between does not depend on the row count and is the
+ * caller's (gonum EigenSym in Go, LAPACK in the Python mirror).
+ *
+ * omr_projection_rows: the newest eligible row of each entity that has one under `filter`
+ * (single-tier scope semantics; rows without an embedding never qualify), in ascending row order.
+ * Writes min(found, cap) rows. */
+OMR_API int omr_projection_rows(omr_store* s, const omr_filter* filter, int64_t* rows, int64_t cap, int64_t* found);
+/* mean[dim] and the sample covariance cov[dim][dim] (divisor n - 1, as gonum's stat.PC) of the
+ * listed rows, float64.  n >= 2; rows are store row ids (as omr_search_rows returns with row_stride 1). */
+OMR_API int omr_pca_moments(omr_store* s, const int64_t* rows, int64_t n, double* mean, double* cov);
+/* out[n][k] = X * basis with X the listed fp32 rows widened to float64 (NOT centred, as the
+ * reference's proj.Mul(m, vecs)); basis is [dim][k] row-major. */
+OMR_API int omr_pca_project(omr_store* s, const int64_t* rows, int64_t n, const double* basis, int32_t k, double* out);
+
 /* ---- device-pointer entry points ----------------------------------------------
  * Same recall, with queries, bitmaps and results in device memory and the work enqueued
  * on `stream`.  d_bitmaps is [n_groups][omr_bitmap_words()] (NULL = every live row),

@@ -93,6 +93,9 @@ SIGNATURES = {
     "omr_rescope": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_char_p, C.c_char_p]),
     "omr_merge_entities": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32]),
     "omr_clear": (C.c_int, [C.c_void_p]),
+    "omr_projection_rows": (C.c_int, [C.c_void_p, C.POINTER(Filter), C.c_void_p, C.c_int64, C.POINTER(C.c_int64)]),
+    "omr_pca_moments": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]),
+    "omr_pca_project": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int32, C.c_void_p]),
     "omr_search": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.POINTER(Filter), C.c_int32, C.c_void_p,
                              C.c_int32, C.c_void_p, C.c_void_p]),
     "omr_search_rows": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.POINTER(Filter), C.c_int32,

@@ -138,4 +138,14 @@ int launch_pair_rescore(const ShardView& sh, const PairCand* pairs, unsigned lon
                         cudaStream_t st);
 int launch_gather_rows(const ShardView& sh, const int32_t* idx, int64_t m, __nv_bfloat16* dst, cudaStream_t st);
 
+// ---- PCA moments / projection over resident rows (k_pca.cu) -------------------
+int pca_mean_chunks(int64_t n);
+int pca_cov_splits(int64_t n, int dim, int num_sms);
+// colsum_partial [n_chunks][dim], cov_partial [n_splits][dim][dim], mean [dim], cov [dim][dim]; n >= 2
+int launch_pca_moments(const ShardView& sh, const int64_t* rows, int64_t n, double* colsum_partial, int n_chunks,
+                       double* mean, double* cov_partial, int n_splits, double* cov, cudaStream_t st);
+// out [n][k] = rows_f32[rows] * basis, basis [dim][k] row-major
+int launch_pca_project(const ShardView& sh, const int64_t* rows, int64_t n, const double* basis, int k, double* out,
+                       cudaStream_t st);
+
 }  // namespace omr

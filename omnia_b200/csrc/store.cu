@@ -1842,6 +1842,101 @@ int omr_selfjoin(omr_store* s, const omr_selfjoin_opts* o, omr_pair* out, int64_
 
 // Diagnostics: runs only query preparation + one scorer and returns the raw packed keys
 // ([nq][n_tiles * (256 / S) * 2] int32, host), so tests can check a scorer in isolation.
+// ---- PCA over resident rows (k_pca.cu) ---------------------------------------------------------
+
+int omr_projection_rows(omr_store* s, const omr_filter* filter, int64_t* rows, int64_t cap, int64_t* found) {
+  if (found) *found = 0;
+  if (!s || !filter || (cap > 0 && !rows)) return fail_msg(OMR_E_INVALID, "memory: omr_projection_rows: null argument");
+  std::lock_guard<std::mutex> lk(s->mu);
+  cudaSetDevice(s->cfg.device);
+  if (int drc = s->drain()) return drc;
+  if (s->n == 0) return OMR_OK;
+  DeviceFilter df;
+  double unused;
+  int rc;
+  if ((rc = s->to_device_filter(*filter, &df, &unused))) return rc;
+  if ((rc = s->w_filters.reserve(64))) return rc;
+  if ((rc = s->w_bitmaps.reserve((size_t)s->words()))) return rc;
+  OMR_CUDA_OK(cudaMemcpyAsync(s->w_filters.p, &df, sizeof df, cudaMemcpyHostToDevice, s->stream));
+  if ((rc = launch_build_bitmaps(s->meta(), s->n, (int)s->words(), s->w_filters.p, 1, s->w_bitmaps.p, s->stream))) return rc;
+  s->st_launches++;
+  const size_t nw = (size_t)((s->n + 31) / 32);
+  std::vector<uint32_t> bits(nw);
+  OMR_CUDA_OK(cudaMemcpyAsync(bits.data(), s->w_bitmaps.p, nw * 4, cudaMemcpyDeviceToHost, s->stream));
+  OMR_CUDA_OK(cudaStreamSynchronize(s->stream));
+  // newest eligible row per entity: rows are appended in arrival order, so "newest" is the largest index
+  std::vector<int64_t> best(s->entity_rows.size(), -1);
+  for (int64_t r = 0; r < s->n; r++)
+    if (bits[(size_t)(r >> 5)] >> (r & 31) & 1u) best[s->h_entity[r]] = r;
+  std::vector<int64_t> picked;
+  for (int64_t r : best)
+    if (r >= 0) picked.push_back(r);
+  std::sort(picked.begin(), picked.end());
+  if (found) *found = (int64_t)picked.size();
+  const int64_t w = std::min<int64_t>(cap, (int64_t)picked.size());
+  for (int64_t i = 0; i < w; i++) rows[i] = picked[(size_t)i];
+  return OMR_OK;
+}
+
+static int pca_stage_rows(omr_store* s, const int64_t* rows, int64_t n) {
+  for (int64_t i = 0; i < n; i++)
+    if (rows[i] < 0 || rows[i] >= s->n)
+      return fail_msg(OMR_E_INVALID, "memory: projection row %lld outside the store (%lld rows)", (long long)rows[i],
+                      (long long)s->n);
+  int rc = s->w_out_rows.reserve((size_t)n);
+  if (rc) return rc;
+  OMR_CUDA_OK(cudaMemcpyAsync(s->w_out_rows.p, rows, (size_t)n * 8, cudaMemcpyHostToDevice, s->stream));
+  return 0;
+}
+
+int omr_pca_moments(omr_store* s, const int64_t* rows, int64_t n, double* mean, double* cov) {
+  if (!s || !rows || !mean || !cov) return fail_msg(OMR_E_INVALID, "memory: omr_pca_moments: null argument");
+  if (n < 2) return fail_msg(OMR_E_INVALID, "memory: projection: PCA needs at least 2 rows, got %lld", (long long)n);
+  std::lock_guard<std::mutex> lk(s->mu);
+  cudaSetDevice(s->cfg.device);
+  if (int drc = s->drain()) return drc;
+  int rc;
+  if ((rc = pca_stage_rows(s, rows, n))) return rc;
+  const int chunks = pca_mean_chunks(n);
+  const int splits = pca_cov_splits(n, s->dim, s->num_sms);
+  const size_t dd = (size_t)s->dim * s->dim;
+  // layout of the fp64 scratch: mean | cov | column-sum partials | covariance partials
+  const size_t need = (size_t)s->dim + dd + (size_t)chunks * s->dim + (size_t)splits * dd;
+  if ((rc = s->w_exact.reserve(need))) return rc;
+  double* d_mean = s->w_exact.p;
+  double* d_cov = d_mean + s->dim;
+  double* d_colsum = d_cov + dd;
+  double* d_part = d_colsum + (size_t)chunks * s->dim;
+  if ((rc = launch_pca_moments(s->view(), s->w_out_rows.p, n, d_colsum, chunks, d_mean, d_part, splits, d_cov, s->stream)))
+    return rc;
+  s->st_launches += 4;
+  OMR_CUDA_OK(cudaMemcpyAsync(mean, d_mean, (size_t)s->dim * 8, cudaMemcpyDeviceToHost, s->stream));
+  OMR_CUDA_OK(cudaMemcpyAsync(cov, d_cov, dd * 8, cudaMemcpyDeviceToHost, s->stream));
+  OMR_CUDA_OK(cudaStreamSynchronize(s->stream));
+  return OMR_OK;
+}
+
+int omr_pca_project(omr_store* s, const int64_t* rows, int64_t n, const double* basis, int32_t k, double* out) {
+  if (!s || !rows || !basis || !out) return fail_msg(OMR_E_INVALID, "memory: omr_pca_project: null argument");
+  if (n <= 0) return OMR_OK;
+  if (k < 1 || k > s->dim) return fail_msg(OMR_E_INVALID, "memory: projection: k must be in 1..%d, got %d", s->dim, k);
+  std::lock_guard<std::mutex> lk(s->mu);
+  cudaSetDevice(s->cfg.device);
+  if (int drc = s->drain()) return drc;
+  int rc;
+  if ((rc = pca_stage_rows(s, rows, n))) return rc;
+  const size_t nb = (size_t)s->dim * k;
+  if ((rc = s->w_exact.reserve(nb + (size_t)n * k))) return rc;
+  double* d_basis = s->w_exact.p;
+  double* d_out = d_basis + nb;
+  OMR_CUDA_OK(cudaMemcpyAsync(d_basis, basis, nb * 8, cudaMemcpyHostToDevice, s->stream));
+  if ((rc = launch_pca_project(s->view(), s->w_out_rows.p, n, d_basis, k, d_out, s->stream))) return rc;
+  s->st_launches++;
+  OMR_CUDA_OK(cudaMemcpyAsync(out, d_out, (size_t)n * k * 8, cudaMemcpyDeviceToHost, s->stream));
+  OMR_CUDA_OK(cudaStreamSynchronize(s->stream));
+  return OMR_OK;
+}
+
 int omr_debug_candidate_keys(omr_store* s, const float* queries, int32_t nq, int32_t path, int32_t S,
                              int32_t* out_keys, int64_t out_len) {
   if (!s || !queries || !out_keys) return fail_msg(OMR_E_INVALID, "memory: omr_debug_candidate_keys: null argument");

@@ -381,6 +381,56 @@ class GPUMemoryStore:
                               (self._lib.omr_kind_name(self._h, p.kind) or b"").decode(), p.canonical_row, p.dupe_row)
                 for p in out[:found.value]]
 
+    # -- Memory Galaxy projection input ------------------------
+    def projection_rows(self, flt: FilterSpec, cap: int = 0) -> np.ndarray:
+        """One row per live entity in scope, newest eligible observation (LoadProjectionInputs,
+        internal/memory/projection_store.go:33-62); `cap` > 0 truncates the list."""
+        found = C.c_int64(0)
+        L.check(self._lib.omr_projection_rows(self._h, C.byref(flt.c), None, 0, C.byref(found)))
+        n = found.value if cap <= 0 else min(cap, found.value)
+        rows = np.empty(max(n, 1), np.int64)
+        L.check(self._lib.omr_projection_rows(self._h, C.byref(flt.c), rows.ctypes.data, n, C.byref(found)))
+        return rows[:n]
+
+    def pca_moments(self, rows):
+        """Column means and sample covariance (float64) of the listed rows, computed on the GPU."""
+        r = np.ascontiguousarray(rows, np.int64)
+        mean = np.empty(self.dim, np.float64)
+        cov = np.empty((self.dim, self.dim), np.float64)
+        L.check(self._lib.omr_pca_moments(self._h, r.ctypes.data, r.shape[0], mean.ctypes.data, cov.ctypes.data))
+        return mean, cov
+
+    def pca_project(self, rows, basis) -> np.ndarray:
+        """X @ basis in float64 over the listed (uncentred) rows; basis is [dim, k]."""
+        r = np.ascontiguousarray(rows, np.int64)
+        b = np.ascontiguousarray(basis, np.float64)
+        out = np.empty((r.shape[0], b.shape[1]), np.float64)
+        L.check(self._lib.omr_pca_project(self._h, r.ctypes.data, r.shape[0], b.ctypes.data, b.shape[1],
+                                          out.ctypes.data))
+        return out
+
+    def pca_reduce(self, rows, k: int) -> np.ndarray:
+        """PCAReduce (ee/pkg/memory/projection/pca.go:28-67) over resident rows.
+
+        k is clamped to min(rows, dim) and to at least 1; a single row is truncated to its first k
+        features; an empty selection is an error.  The moments and the projection run on the GPU, the
+        dim x dim symmetric eigenproblem in between on the host (LAPACK here, gonum EigenSym in Go).
+        Components are ordered by decreasing variance; their signs are the eigensolver's, as the
+        reference's are its SVD's."""
+        r = np.ascontiguousarray(rows, np.int64)
+        n = r.shape[0]
+        if n == 0 or self.dim == 0:
+            raise L.RecallError(L.E_INVALID, f"projection: empty input matrix ({n}x{self.dim})")
+        k = max(1, min(k, self.dim, n))
+        if n < 2:
+            basis = np.zeros((self.dim, k), np.float64)      # firstKCols (pca.go:70-83)
+            basis[np.arange(k), np.arange(k)] = 1.0
+            return self.pca_project(r, basis)
+        _, cov = self.pca_moments(r)
+        w, v = np.linalg.eigh(cov)
+        order = np.argsort(-w, kind="stable")[:k]
+        return self.pca_project(r, v[:, order])
+
     def debug_candidate_keys(self, queries, path: int, S: int) -> np.ndarray:
         q = np.ascontiguousarray(queries, np.float32)
         nq = q.shape[0]

@@ -305,3 +305,30 @@ def selfjoin(rows, member: Optional[np.ndarray], kind: np.ndarray, flags: np.nda
     if limit is not None:
         a, b, s = a[:limit], b[:limit], s[:limit]
     return a, b, s
+
+
+# ---------------------------------------------------------------- projection input (PCA)
+
+def pca_reduce(m, k: int) -> np.ndarray:
+    """PCAReduce, ee/pkg/memory/projection/pca.go:28-67, in float64.
+
+    The decomposition itself lives in a dependency that is not under /root/reference
+    (gonum.org/v1/gonum v0.17.0, go.mod:67; stat.PC.PrincipalComponents): it copies the data, subtracts
+    the column means, takes a thin SVD of the centred copy and returns the right singular vectors
+    (nFeatures x min(nSamples, nFeatures)) ordered by decreasing singular value.  The reference then
+    multiplies the ORIGINAL, uncentred matrix by the first k vectors (pca.go:60).  Restated here with
+    numpy's SVD; the sign of each component is the SVD implementation's choice, so comparisons with
+    this function are made up to a sign per column.  Parity unpinned: the reference's tests check
+    shapes and clamping only (pca_test.go:17-99), and those are what tests/ transcribes."""
+    m = np.ascontiguousarray(m, np.float64)
+    if m.ndim != 2 or m.shape[0] == 0 or m.shape[1] == 0:
+        raise ValueError(f"projection: empty input matrix ({m.shape[0] if m.ndim == 2 else 0}x"
+                         f"{m.shape[1] if m.ndim == 2 else 0})")
+    rows, cols = m.shape
+    k = max(1, min(k, cols, rows))                       # pca.go:33-42
+    if rows < 2:
+        return m[:, :k].copy()                           # firstKCols, pca.go:46-48, 70-83
+    centred = m - m.mean(axis=0)
+    _, _, vt = np.linalg.svd(centred, full_matrices=False)
+    k = min(k, vt.shape[0])                              # pca.go:57-59
+    return m @ vt[:k].T

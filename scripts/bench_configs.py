@@ -108,8 +108,37 @@ def c4():
                            "frac": flops / dt / 1e12 / PEAKS["bf16_tflops_sustained"], "note": "wall time of the whole omr_selfjoin call, host post-processing included"}})
 
 
+def pca():
+    # section 8(f)-4: the Memory Galaxy PCA input.  Default galaxy = 2000 entities x 1536 -> 50 columns;
+    # the large case shows where the kernel, not the 19 MB covariance read-back, sets the time.
+    dim = 1536
+    for n in (2000, 200_000):
+        x = synth.clustered(n, dim, seed=1)
+        with GPUMemoryStore(dim, n) as s:
+            s.bulk_load(x)
+            rows = np.arange(n, dtype=np.int64)
+            for rep in range(3):
+                t0 = time.perf_counter(); mean, cov = s.pca_moments(rows); t_mom = time.perf_counter() - t0
+            t0 = time.perf_counter(); w, v = np.linalg.eigh(cov); t_eig = time.perf_counter() - t0
+            basis = np.ascontiguousarray(v[:, np.argsort(-w, kind="stable")[:50]])
+            for rep in range(3):
+                t0 = time.perf_counter(); out = s.pca_project(rows, basis); t_proj = time.perf_counter() - t0
+        x64 = x.astype(np.float64)
+        t0 = time.perf_counter(); c = x64 - x64.mean(axis=0); ref_cov = c.T @ c / (n - 1); t_cpu_cov = time.perf_counter() - t0
+        err = float(np.abs(cov - ref_cov).max())
+        t_svd = None
+        if n <= 2000:
+            t0 = time.perf_counter(); np.linalg.svd(c, full_matrices=False); t_svd = time.perf_counter() - t0
+        flops = 2.0 * n * dim * (dim + 128) / 2          # upper-triangle tiles of 128
+        emit({"config": f"PCA moments {n} x {dim} (fp64)", "moments_s": t_mom, "host_eigh_s": t_eig, "project_s": t_proj,
+              "cpu_numpy_cov_s": t_cpu_cov, "cpu_numpy_svd_s": t_svd, "max_abs_cov_err": err, "cpu_threads": os.cpu_count(),
+              "roofline": {"bound": "fp64", "achieved": flops / t_mom / 1e12, "peak": 40.0, "unit": "TFLOP/s",
+                           "frac": flops / t_mom / 1e12 / 40.0,
+                           "note": "wall time of omr_pca_moments incl. the covariance D2H; peak is the nominal B200 fp64 figure, unmeasured"}})
+
+
 if __name__ == "__main__":
     os.makedirs("gpurun_out", exist_ok=True)
     which = sys.argv[1:] or ["c5", "small", "c3", "c4"]
     for w in which:
-        {"c5": c5, "small": small, "c3": c3, "c4": c4}[w]()
+        {"c5": c5, "small": small, "c3": c3, "c4": c4, "pca": pca}[w]()
