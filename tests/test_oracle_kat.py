@@ -174,3 +174,23 @@ def test_variants_agree_on_random_data():
     assert np.allclose(d0, d1, rtol=0, atol=2e-6) and np.allclose(d2, d1, rtol=0, atol=2e-6)
     rn, dn = O.numpy_topk(rows, q, 10)
     assert np.array_equal(rn, r1) and np.allclose(dn, d1, atol=2e-6)
+
+
+def test_pca_reduce_restatement_known_answers_and_reference_shapes():
+    # ee/pkg/memory/projection/pca_test.go:17-99 (shapes, clamping, degenerate sets) and a hand-checkable case
+    t = np.linspace(-1.0, 1.0, 21)
+    u = np.array([3.0, 4.0]) / 5.0
+    m = np.outer(t, u) + np.array([10.0, -2.0])               # points on a line, far from the origin
+    out = O.pca_reduce(m, 1)
+    assert out.shape == (21, 1)
+    want = m @ u                                               # the UNCENTRED rows times the first axis (pca.go:60)
+    assert min(np.abs(out[:, 0] - want).max(), np.abs(out[:, 0] + want).max()) < 1e-12
+    data = (np.arange(6 * 8) * 7 % 13 / 13.0).reshape(6, 8)
+    assert O.pca_reduce(data, 3).shape == (6, 3)
+    assert O.pca_reduce(np.array([[1, 0], [0, 1], [1, 1], [0, 0]], float), 50).shape == (4, 2)
+    wide = (np.arange(6 * 1536) * 7 % 97 / 97.0).reshape(6, 1536)
+    assert O.pca_reduce(wide, 50).shape == (6, 6)
+    one = (np.arange(64) / 64.0)[None, :]
+    np.testing.assert_array_equal(O.pca_reduce(one, 50), one[:, :1])
+    with pytest.raises(ValueError, match="empty input matrix"):
+        O.pca_reduce(np.zeros((0, 0)), 50)
