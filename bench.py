@@ -137,6 +137,34 @@ def cpu_scan_rate(corpus: np.ndarray, queries: np.ndarray, target_s: float):
     return n / dt, n, dt, threads
 
 
+def cpu_variants(corpus: np.ndarray, queries: np.ndarray, target_s: float):
+    """SURVEY.md section 8(d) C1 / CPU baseline timing: every CPU arm on the same bounded sample --
+    fp32-seq on one thread (the closest analogue of one Postgres backend doing a sequential scan),
+    fp32-seq, pgvector-flags and fp64 on all threads, and numpy sgemm + argpartition."""
+    from oracle import oracle as O
+    threads = host_threads()
+    t0 = time.perf_counter()
+    O.search(corpus, queries[:1], TOPK, variant=O.VARIANT_F32_SEQ, threads=1)
+    t_one = time.perf_counter() - t0
+    n1 = max(1, min(len(queries), int(target_s / max(t_one, 1e-4))))
+    nt = max(1, min(len(queries), n1 * threads))
+    out = {}
+    for name, variant, th, n in (("fp32_seq_1thread", O.VARIANT_F32_SEQ, 1, n1),
+                                 ("fp32_seq", O.VARIANT_F32_SEQ, threads, nt),
+                                 ("fp32_pgvector_flags", O.VARIANT_F32_VEC, threads, nt),
+                                 ("fp64", O.VARIANT_F64, threads, nt)):
+        t0 = time.perf_counter()
+        O.search(corpus, queries[:n], TOPK, variant=variant, threads=th)
+        dt = time.perf_counter() - t0
+        out[name] = {"value": n / dt, "unit": UNIT, "cores": th, "queries": n, "seconds": round(dt, 4)}
+    t0 = time.perf_counter()
+    O.numpy_topk(corpus, queries[:nt], TOPK)
+    dt = time.perf_counter() - t0
+    out["numpy_sgemm_argpartition"] = {"value": nt / dt, "unit": UNIT, "cores": threads, "queries": nt,
+                                       "seconds": round(dt, 4)}
+    return out
+
+
 def run_reference(args, rank: int):
     """--impl reference: the reference's CPU path for this metric.  The reference computes `<=>` inside
     pgvector (not buildable here: needs PostgreSQL); the timed code is oracle/oracle_vec.c, the same
@@ -394,6 +422,8 @@ def main():
             qps, n, dt, threads = cpu_scan_rate(shard, hq_np[0], 12.0)
             line["cpu_baseline"] = {"value": qps, "unit": UNIT, "cores": threads, "kind": "port",
                                     "sample": f"{n} queries, exact scan of all {N_ROWS} rows each, {dt:.1f} s"}
+            if os.environ.get("OMNIA_BENCH_CPU_VARIANTS") == "1":
+                line["cpu_baseline"]["variants"] = cpu_variants(shard, hq_np[0], 4.0)
         else:
             line["cpu_baseline"] = None
         print(json.dumps(line), flush=True)

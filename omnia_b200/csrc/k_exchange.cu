@@ -166,7 +166,7 @@ int launch_exchange_merge(const ExchangeView& x, int slot, unsigned long long ep
                                      cudaSharedmemCarveoutMaxShared));
     carveout_set = true;
   }
-  if (smem > 48 * 1024)
+  if (smem > 32 * 1024)  // static shared memory counts against the 48 KB default too
     OMR_CUDA_OK(cudaFuncSetAttribute(exchange_merge_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   exchange_wait_kernel<<<1, 32, 0, st>>>(x, slot, epoch, error_word);
   OMR_CUDA_OK(cudaGetLastError());

@@ -509,7 +509,7 @@ int launch_post(const PostArgs& a, cudaStream_t st) {
   if (a.nq <= 0) return 0;
   if (a.sort_cap < kCandCap || (a.sort_cap & 1)) return fail_msg(-1, "post kernel sort capacity %d is too small", a.sort_cap);
   const size_t smem = (size_t)a.sh.pitch * sizeof(double) + (size_t)a.sort_cap * 12 + sizeof(PostSmem);
-  if (smem > 48 * 1024)
+  if (smem > 32 * 1024)  // static shared memory counts against the 48 KB default too
     OMR_CUDA_OK(cudaFuncSetAttribute(post_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   // Same shared-memory carve-out as the scorer (maximum), so that blocks of this kernel can be resident on
   // an SM next to a scorer CTA of the following batch; an SM cannot hold two carve-out configurations.

@@ -605,7 +605,7 @@ int launch_finalize(const FinalizeArgs& a, cudaStream_t st) {
   if (nblocks <= 0) return 0;
   const int P = pow2ceil(a.K2);
   const size_t smem = (size_t)P * 12;
-  if (smem > 48 * 1024)
+  if (smem > 32 * 1024)  // static shared memory counts against the 48 KB default too
     OMR_CUDA_OK(cudaFuncSetAttribute(finalize_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   finalize_kernel<<<nblocks, 256, smem, st>>>(a.K2, a.K2x, P, a.k, a.S, a.sel_rows, a.sel_dist, a.max_dist,
                                               a.sel_bound, a.cand_keys, a.keys_per_query, a.margin, a.bitmaps,
@@ -620,7 +620,7 @@ int launch_finalize_extra(const FinalizeArgs& a, cudaStream_t st) {
   if (a.nq <= 0) return 0;
   const int P = pow2ceil(a.K2x);
   const size_t smem = (size_t)P * 12;
-  if (smem > 48 * 1024)
+  if (smem > 32 * 1024)  // static shared memory counts against the 48 KB default too
     OMR_CUDA_OK(cudaFuncSetAttribute(finalize_extra_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   finalize_extra_kernel<<<a.nq, 256, smem, st>>>(a.K2, a.K2x, P, a.k, a.sel_rows, a.sel_dist, a.max_dist, a.extra_cnt,
                                                  a.row_base, a.row_stride, a.out_rows, a.out_dist, a.out_count);
@@ -653,7 +653,7 @@ int launch_merge_topk(const int64_t* in_rows, const double* in_dist, int G, int 
   const int P = pow2ceil(G * k);
   const size_t smem = (size_t)P * 16;
   if (smem > 200 * 1024) return fail_msg(-2, "merge of %d shards x k=%d exceeds the 12800-entry limit", G, k);
-  if (smem > 48 * 1024)
+  if (smem > 32 * 1024)  // static shared memory counts against the 48 KB default too
     OMR_CUDA_OK(cudaFuncSetAttribute(merge_topk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   if (shard_stride <= 0) shard_stride = (int64_t)nq * k;
   static bool carveout_set = false;  // see k_post.cu

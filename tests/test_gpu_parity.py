@@ -44,6 +44,36 @@ def test_gauss_corpus_matches_oracle(path, n, dim, nq, k):
         assert st.fallback_queries == 0, "random data must certify without the exact fallback"
 
 
+@pytest.mark.parametrize("path", [0, 1, 2, 3])
+@pytest.mark.parametrize("n,dim,nq,k", [
+    (1_500, 2000, 3, 10),        # the widest indexed column (embedding_schema.go:64-68)
+    (5_000, 8, 129, 1),          # one 16-byte row; k = 1; a ragged second query tile
+    (4_097, 1, 4, 3),            # dimension 1: every cosine is +1 or -1, ties everywhere
+    (6_000, 64, 2, 4096),        # the largest k the ABI accepts, k < n
+    (9_000, 32, 2049, 3),        # 17 query tiles, the last with one query
+    (256, 96, 7, 256),           # exactly one row tile, k = n
+    (257, 96, 7, 10),            # one row in the second tile
+])
+def test_limits_of_the_abi(path, n, dim, nq, k):
+    if path == 1 and nq > 64:
+        pytest.skip("the streaming scorer takes 8 queries per pass; large batches belong to the tensor-core path")
+    corpus = synth.gauss_unit(n, dim, seed=n + dim)
+    queries = synth.queries_from(corpus, nq)
+    run_case(corpus, queries, k, path)
+
+
+@pytest.mark.parametrize("path", [0, 1, 2])
+def test_rows_and_queries_of_any_magnitude(path):
+    # cosine ignores magnitudes; pgvector divides by sqrt(na * nb) in double, so 1e-12 .. 1e12 scales are exact
+    n, dim, nq, k = 6_000, 384, 24, 10
+    rng = np.random.default_rng(9)
+    corpus = synth.gauss_unit(n, dim, seed=21)
+    queries = synth.queries_from(corpus, nq)
+    corpus = (corpus * (10.0 ** rng.uniform(-12, 12, (n, 1)))).astype(np.float32)
+    queries = (queries * (10.0 ** rng.uniform(-12, 12, (nq, 1)))).astype(np.float32)
+    run_case(corpus, queries, k, path)
+
+
 @pytest.mark.parametrize("path", [1, 2, 4])
 @pytest.mark.parametrize("S", [32, 64, 128, 256])
 def test_every_sub_bucket_size(path, S):
