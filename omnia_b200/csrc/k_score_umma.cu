@@ -153,6 +153,7 @@ struct KernelArgs {
   int n_b_tiles;   // 256-row tiles of the store
   int64_t n_work;  // (a tile, b tile) work items of this launch
   int64_t work_first, work_step;  // global item = work_first + w * work_step (self-join partitions; 0 / 1 otherwise)
+  int sb;                         // self-join: B tiles per super-block edge (see decode_work)
   int k_blocks;
   int nq;          // real queries; tiles are padded with zero queries beyond it
   int n_stages;    // TMA ring depth in use (<= kStages); experiments only, normally kStages
@@ -167,20 +168,30 @@ struct KernelArgs {
   PairEpilogue pe;
 };
 
-// Work item -> (A tile of 128, B tile of 256).  Recall: a-tile fastest, so the CTAs that
-// run concurrently share B tiles through L2.  Self-join: B tile jb meets A tiles 0..2jb+1
-// (everything at or above the diagonal), jb(jb+1) items come before it.
+// Work item -> (A tile of 128, B tile of 256); false = nothing to do for this item.
+// Recall: a-tile fastest, so the CTAs that run concurrently share B tiles through L2.
+// Self-join: the tile-pair space is cut into super-blocks of (2 sb A tiles) x (sb B tiles) = sb*256 rows on
+// both sides, walked column by column over the upper triangle (I <= J); inside a super-block every pair is
+// an item (a-tile fastest) and the ones below the diagonal or past the end are skipped.  The two row
+// blocks of a super-block (2 x sb x 786 KB bf16 at D = 1536) stay in L2 while its 2 sb^2 tile pairs are
+// computed, so HBM sees each block once per super-block instead of one A tile per tile pair.
 template <bool kSelfJoin>
-__device__ __forceinline__ void decode_work(int64_t w, int n_a_tiles, int& a_tile, int& b_tile) {
+__device__ __forceinline__ bool decode_work(int64_t w, int n_a_tiles, int n_b_tiles, int sb, int& a_tile, int& b_tile) {
   if (!kSelfJoin) {
     b_tile = (int)(w / n_a_tiles);
     a_tile = (int)(w % n_a_tiles);
+    return true;
   } else {
-    int64_t jb = (int64_t)((sqrt(4.0 * (double)w + 1.0) - 1.0) * 0.5);
-    while (jb * (jb + 1) > w) jb--;
-    while ((jb + 1) * (jb + 2) <= w) jb++;
-    b_tile = (int)jb;
-    a_tile = (int)(w - jb * (jb + 1));
+    const int64_t per = 2ll * sb * sb;
+    const int64_t blk = w / per;
+    const int t = (int)(w - blk * per);
+    int64_t J = (int64_t)((sqrt(8.0 * (double)blk + 1.0) - 1.0) * 0.5);
+    while (J * (J + 1) / 2 > blk) J--;
+    while ((J + 1) * (J + 2) / 2 <= blk) J++;
+    const int64_t I = blk - J * (J + 1) / 2;
+    a_tile = (int)(I * 2 * sb) + t % (2 * sb);
+    b_tile = (int)(J * sb) + t / (2 * sb);
+    return a_tile < n_a_tiles && b_tile < n_b_tiles && a_tile <= 2 * b_tile + 1;
   }
 }
 
@@ -227,7 +238,9 @@ __global__ void __launch_bounds__(kNumThreads, 1)
       uint32_t phase = 0;
       for (int64_t w = blockIdx.x; w < args.n_work; w += gridDim.x) {
         int a_tile, b_tile;
-        decode_work<kSelfJoin>(args.work_first + w * args.work_step, args.n_a_tiles, a_tile, b_tile);
+        if (!decode_work<kSelfJoin>(args.work_first + w * args.work_step, args.n_a_tiles, args.n_b_tiles, args.sb, a_tile,
+                                    b_tile))
+          continue;
         for (int kb = 0; kb < args.k_blocks; kb++) {
           ptx::mbar_wait(&bars->empty[stage], phase ^ 1);
           ptx::mbar_arrive_expect_tx(&bars->full[stage], kStageBytes);
@@ -248,8 +261,14 @@ __global__ void __launch_bounds__(kNumThreads, 1)
     int stage = 0;
     uint32_t phase = 0;
     uint32_t it = 0;
-    for (int64_t w = blockIdx.x; w < args.n_work; w += gridDim.x, it++) {
+    for (int64_t w = blockIdx.x; w < args.n_work; w += gridDim.x) {
+      if (kSelfJoin) {
+        int ta, tb;
+        if (!decode_work<kSelfJoin>(args.work_first + w * args.work_step, args.n_a_tiles, args.n_b_tiles, args.sb, ta, tb))
+          continue;
+      }
       const uint32_t as = it & 1, aphase = (it >> 1) & 1;
+      it++;
       ptx::mbar_wait(&bars->tmem_empty[as], aphase ^ 1);
       ptx::tc_fence_after_sync();
       for (int kb = 0; kb < args.k_blocks; kb++) {
@@ -280,10 +299,13 @@ __global__ void __launch_bounds__(kNumThreads, 1)
     Top2Epilogue<S> te;
     PairEpilogue pe = args.pe;
     pe.stage = pstage;
-    for (int64_t w = blockIdx.x; w < args.n_work; w += gridDim.x, it++) {
+    for (int64_t w = blockIdx.x; w < args.n_work; w += gridDim.x) {
       int a_tile, b_tile;
-      decode_work<kSelfJoin>(args.work_first + w * args.work_step, args.n_a_tiles, a_tile, b_tile);
+      if (!decode_work<kSelfJoin>(args.work_first + w * args.work_step, args.n_a_tiles, args.n_b_tiles, args.sb, a_tile,
+                                  b_tile))
+        continue;
       const uint32_t as = it & 1, aphase = (it >> 1) & 1;
+      it++;
       if (!kSelfJoin) {
         const int q = a_tile * kQueryTile + t_local;
         const int g = (args.query_group && q < args.nq) ? __ldg(args.query_group + q) : 0;
@@ -559,7 +581,14 @@ int launch_selfjoin_umma(const CUtensorMap& tmap_a, const CUtensorMap& tmap_b, i
   KernelArgs<true, 256> a{};
   a.n_a_tiles = (int)(2 * nb);
   a.n_b_tiles = (int)nb;
-  const int64_t total = nb * (nb + 1);  // sum over jb of (2jb + 2)
+  // super-block edge: two row blocks of sb * 256 rows must sit in L2 together (126 MB, two dies); 24 tiles =
+  // 18.9 MB per block at pitch 1536, scaled up for narrower rows
+  int sb = 24;
+  if (k_blocks > 0) sb = std::max(8, std::min(96, 24 * 24 / k_blocks));
+  if (const char* e = getenv("OMR_SELFJOIN_SB")) sb = std::max(1, atoi(e));
+  a.sb = sb;
+  const int64_t NB = (nb + sb - 1) / sb;
+  const int64_t total = NB * (NB + 1) / 2 * (2ll * sb * sb);
   if (part_count < 1) part_count = 1;
   a.work_first = part_index;          // partition p of P takes the items p, p+P, p+2P, ... (interleaved: balanced)
   a.work_step = part_count;

@@ -1778,18 +1778,29 @@ int omr_selfjoin(omr_store* s, const omr_selfjoin_opts* o, omr_pair* out, int64_
   const int part_index = o->part_index;
   if (part_index < 0 || part_index >= part_count) return fail_msg(OMR_E_INVALID, "memory: self-join part %d of %d", part_index, part_count);
   const double floor_d = (double)o->similarity_floor;  // float32 widened once, as Postgres does
-  const float thr = (float)(floor_d - (double)s->margin);
+  // Extra candidates cost nothing here, so the join always uses the deterministic bound of the bf16 stage
+  // (2^-8 from the two roundings of unit vectors, plus fp32 accumulation over <= 2048 terms) rather than the
+  // statistical recall margin: the pair set is exact under any rounding pattern.
+  const float thr = (float)(floor_d - std::max((double)s->margin, 4.5e-3));
   unsigned long long pcap = std::max<unsigned long long>(s->w_pairs.n, 1ull << 20);
   unsigned long long cnt = 0;
   for (int attempt = 0; attempt < 2; attempt++) {
     if ((rc = s->w_pairs.reserve((size_t)pcap))) return rc;
     OMR_CUDA_OK(cudaMemsetAsync(s->w_pair_count.p, 0, 8, st));
+    if (s->profiling) OMR_CUDA_OK(cudaEventRecord(s->lanes[0].ev0, st));
     if ((rc = launch_selfjoin_umma(ta, tb, m, s->pitch / kBlockK, part_index, part_count, thr, s->w_member.p, s->w_pairs.p, pcap,
                                    s->w_pair_count.p, s->num_sms, st)))
       return rc;
+    if (s->profiling) OMR_CUDA_OK(cudaEventRecord(s->lanes[0].ev1, st));
     s->st_launches++;
     OMR_CUDA_OK(cudaMemcpyAsync(&cnt, s->w_pair_count.p, 8, cudaMemcpyDeviceToHost, st));
     OMR_CUDA_OK(cudaStreamSynchronize(st));
+    if (s->profiling) {
+      float ms = 0.0f;
+      OMR_CUDA_OK(cudaEventElapsedTime(&ms, s->lanes[0].ev0, s->lanes[0].ev1));
+      s->scorer_ms_sum += ms;
+      s->scorer_timed++;
+    }
     if (cnt <= pcap) break;
     if (attempt == 1) return fail_msg(OMR_E_CAPACITY, "memory: self-join candidate count kept growing");
     pcap = cnt + (cnt >> 3);
@@ -1840,8 +1851,6 @@ int omr_selfjoin(omr_store* s, const omr_selfjoin_opts* o, omr_pair* out, int64_
   return OMR_OK;
 }
 
-// Diagnostics: runs only query preparation + one scorer and returns the raw packed keys
-// ([nq][n_tiles * (256 / S) * 2] int32, host), so tests can check a scorer in isolation.
 // ---- PCA over resident rows (k_pca.cu) ---------------------------------------------------------
 
 int omr_projection_rows(omr_store* s, const omr_filter* filter, int64_t* rows, int64_t cap, int64_t* found) {
@@ -1937,6 +1946,8 @@ int omr_pca_project(omr_store* s, const int64_t* rows, int64_t n, const double* 
   return OMR_OK;
 }
 
+// Diagnostics: runs only query preparation + one scorer and returns the raw packed keys
+// ([nq][n_tiles * (256 / S) * 2] int32, host), so tests can check a scorer in isolation.
 int omr_debug_candidate_keys(omr_store* s, const float* queries, int32_t nq, int32_t path, int32_t S,
                              int32_t* out_keys, int64_t out_len) {
   if (!s || !queries || !out_keys) return fail_msg(OMR_E_INVALID, "memory: omr_debug_candidate_keys: null argument");

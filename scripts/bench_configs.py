@@ -95,17 +95,26 @@ def c4():
     corpus, planted = synth.planted_dups(n, dim, n_pairs=2000)
     with GPUMemoryStore(dim, n) as s:
         s.bulk_load(corpus)
-        for rep in range(2):
-            t0 = time.perf_counter()
-            pairs = s.run_entity_duplicate_candidates("default", 0.92, 0)
-            dt = time.perf_counter() - t0
-        want = {(min(int(i), int(j)), max(int(i), int(j))) for i, j, sim in planted if sim >= float(np.float32(0.92))}
-        got = {(min(p.canonical_row, p.dupe_row), max(p.canonical_row, p.dupe_row)) for p in pairs}
-        flops = 2.0 * dim * n * (n + 256) / 2
-        emit({"config": f"C4: self-join {n} x 1536, cosine >= 0.92", "seconds": dt, "pairs": len(pairs),
-              "planted_above_floor": len(want), "planted_found": len(want & got), "unplanted_pairs": len(got - want),
-              "roofline": {"bound": "tensor", "achieved": flops / dt / 1e12, "peak": PEAKS["bf16_tflops_sustained"], "unit": "TFLOP/s",
-                           "frac": flops / dt / 1e12 / PEAKS["bf16_tflops_sustained"], "note": "wall time of the whole omr_selfjoin call, host post-processing included"}})
+        from bench import ClockSampler
+        for sbv in os.environ.get("C4_SB", "default").split(","):
+          if sbv != "default": os.environ["OMR_SELFJOIN_SB"] = sbv
+          for rep in range(2):
+              s.set_profiling(True)
+              st0 = s.stats()
+              cs = ClockSampler(0, 0.02); cs.start()
+              t0 = time.perf_counter()
+              pairs = s.run_entity_duplicate_candidates("default", 0.92, 0)
+              dt = time.perf_counter() - t0
+              clocks = cs.stop()
+              kernel_ms = s.stats().scorer_ms_sum - st0.scorer_ms_sum
+              s.set_profiling(False)
+          want = {(min(int(i), int(j)), max(int(i), int(j))) for i, j, sim in planted if sim >= float(np.float32(0.92))}
+          got = {(min(p.canonical_row, p.dupe_row), max(p.canonical_row, p.dupe_row)) for p in pairs}
+          flops = 2.0 * dim * n * (n + 256) / 2
+          emit({"config": f"C4: self-join {n} x 1536, cosine >= 0.92", "seconds": dt, "pairs": len(pairs),
+                "kernel_ms": kernel_ms, "clocks": clocks, "sub_block": os.environ.get("OMR_SELFJOIN_SB", "default"), "planted_above_floor": len(want), "planted_found": len(want & got), "unplanted_pairs": len(got - want),
+                "roofline": {"bound": "tensor", "achieved": flops / dt / 1e12, "peak": PEAKS["bf16_tflops_sustained"], "unit": "TFLOP/s",
+                             "frac": flops / dt / 1e12 / PEAKS["bf16_tflops_sustained"], "note": "wall time of the whole omr_selfjoin call, host post-processing included"}})
 
 
 def pca():
