@@ -1,5 +1,5 @@
 """torchrun target: row-sharded recall on real GPUs vs the oracle (used by tests/test_gpu_multi.py).
-    torchrun --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P scripts/dist_check.py"""
+    torchrun --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P tests/dist_check.py"""
 import os
 import sys
 from pathlib import Path

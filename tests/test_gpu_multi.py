@@ -21,7 +21,7 @@ def test_sharded_recall_matches_oracle(world, exchange):
     import os
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
            "--master-addr", "127.0.0.1", "--master-port", str(29600 + world + (10 if exchange == "p2p" else 0)),
-           str(ROOT / "scripts" / "dist_check.py")]
+           str(ROOT / "tests" / "dist_check.py")]
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, env=dict(os.environ, EXCHANGE=exchange))
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
     assert r.stdout.count(": ok") == 3
