@@ -32,6 +32,18 @@ def run(s, steps, block=5, depth=3):
     return [round(evs[i].elapsed_time(evs[i + 1]) / block, 3) for i in range(steps // block)]
 
 
+if os.environ.get("COMPARE_PATHS"):
+    # sustained comparison of scorer variants: 400 steps each, second half reported, alternating
+    stores = {p: GPUMemoryStore(D, N, force_path=p) for p in (2, 4)}
+    for st_ in stores.values():
+        st_.bulk_load(corpus)
+    for rep in range(3):
+        for p, st_ in stores.items():
+            time.sleep(1.0)
+            t = run(st_, 400, block=50)
+            print(json.dumps({"force_path": p, "rep": rep, "ms_per_step_blocks_of_50": t}), flush=True)
+    sys.exit(0)
+
 with GPUMemoryStore(D, N) as s:
     s.bulk_load(corpus)
     run(s, 10)
