@@ -362,10 +362,15 @@ def main():
 
     outs = [(np.empty((NQ, TOPK), np.int64), np.empty((NQ, TOPK), np.float64), np.empty(NQ, np.int32)) for _ in range(4)]
 
+    if world > 1:
+        dstage = [torch.empty_like(dq[0]) for _ in range(8)]
+        hres = [(torch.empty((NQ, TOPK), dtype=torch.int64).pin_memory(), torch.empty((NQ, TOPK), dtype=torch.float64).pin_memory(),
+                 torch.empty(NQ, dtype=torch.int32).pin_memory()) for _ in range(8)]
+
     def run_e2e(first, count):
         """`count` steps through the host-buffer C-ABI calls; every step copies its queries from pinned host
         memory to the device and reads its answer back.  N=1: omr_search_rows_begin/_finish, three batches in
-        flight; N>1: pinned H2D + sharded search + D2H per step."""
+        flight; N>1: pinned H2D + sharded search and exchange + D2H per step, three batches in flight."""
         if world == 1 and pipelined:
             pend = []
             for i in range(first, first + count):
@@ -375,6 +380,29 @@ def main():
                     sr.store.search_rows_finish(t, outs[o])
             for t, o in pend:
                 sr.store.search_rows_finish(t, outs[o])
+            return
+        if world > 1 and pipelined:
+            # N>1: pinned H2D into a per-slot device buffer, sharded search + exchange with three batches in
+            # flight, then the D2H of the merged answer into pinned host memory, all inside the timed region
+            cur = torch.cuda.current_stream(dev)
+            pend = []
+
+            def drain_one():
+                h, j = pend.pop(0)
+                r, dd, c, ev = sr.finish(h)
+                cur.wait_event(ev)
+                hres[j][0].copy_(r, non_blocking=True)
+                hres[j][1].copy_(dd, non_blocking=True)
+                hres[j][2].copy_(c, non_blocking=True)
+
+            for i in range(first, first + count):
+                j = i & 7
+                dstage[j].copy_(hq[i % N_BATCHES], non_blocking=True)
+                pend.append((sr.begin(dstage[j], TOPK, j), j))
+                if len(pend) >= 3:
+                    drain_one()
+            while pend:
+                drain_one()
             return
         for i in range(first, first + count):
             if world == 1:
