@@ -463,9 +463,9 @@ def main():
         roofline = {"bound": "tensor", "kernel": "score_umma_kernel", "achieved": achieved, "peak": peak,
                     "unit": "TFLOP/s", "frac": (achieved / peak) if achieved else None,
                     # dram__bytes_read.sum + dram__bytes_write.sum of one launch, from the ncu --set full capture
-                    # of this same command (profiles/r01_score_umma_ncu_full.txt: 3.0768e9 read + 6.7e7 written
+                    # of this same command (profiles/r01_score_umma_ncu_full_current.txt: 3.0762e9 read + 6.62e7 written
                     # at sub-bucket 128); only meaningful for the configuration that capture was taken on
-                    "traffic": 3.144e9 if (N_ROWS, DIM, NQ, TOPK, world) == (1_000_000, 1536, 1024, 10, 1) else None,
+                    "traffic": 3.1425e9 if (N_ROWS, DIM, NQ, TOPK, world) == (1_000_000, 1536, 1024, 10, 1) else None,
                     "algorithmic_bytes": (N_ROWS / world) * DIM * 2 + NQ * DIM * 4 + (N_ROWS / world) / 8,
                     "peak_source": f"bf16_tflops_sustained, {peak_src}: the kernel is timed inside a back-to-back step loop",
                     "frac_of_burst": (achieved / float(peaks["bf16_tflops"])) if achieved else None,
