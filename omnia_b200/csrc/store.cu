@@ -154,7 +154,7 @@ struct omr_store {
   omr_config cfg{};
   int dim = 0, pitch = 0, num_sms = 148;
   int64_t cap = 0, n = 0;
-  float margin = 1e-3f;
+  float margin = 4.5e-3f;
   std::mutex mu;
   cudaStream_t stream = nullptr;
   EncodeTiledFn encode = nullptr;
@@ -529,11 +529,14 @@ int omr_store::enqueue(Lane& L, const float* d_q, int nq, const uint32_t* d_bitm
   // matrix at ~6.7 TB/s for any batch up to ~128 queries, above the LDG-based streaming scorer for
   // every batch but a single query.
   int path = cfg.force_path > 0 ? cfg.force_path : (nq <= 1 ? 1 : 2);
-  // Expected rescued rows per query ~ k^2 S^2 / (2n).  When even the smallest sub-bucket cannot keep
-  // that small (large k on a small store), the two-stage scheme has nothing to offer: scan exactly.
+  // Expected rescued rows per query ~ m^2 S^2 / (2n), m = rows whose approximate score clears the
+  // certificate's threshold (the k answers plus those inside the margin; 2k allows for as many again).
+  // When even the smallest sub-bucket cannot keep that small (large k on a small store), the two-stage
+  // scheme has nothing to offer: scan exactly.
   if (cfg.sub_bucket == 0 && path != 3) {
-    while (S > 32 && (double)k * k * S * S / (2.0 * (double)n) > 256.0) S >>= 1;
-    if (cfg.force_path == 0 && (double)k * k * S * S / (2.0 * (double)n) > 256.0) path = 3;
+    const double m2 = 4.0 * (double)k * k;
+    while (S > 32 && m2 * S * S / (2.0 * (double)n) > 256.0) S >>= 1;
+    if (cfg.force_path == 0 && m2 * S * S / (2.0 * (double)n) > 1024.0) path = 3;
   }
   const int qtile = path == 4 ? 2 * kQueryTile : kQueryTile;
   const int qpad = (path == 2 || path == 4) ? ((nq + qtile - 1) / qtile) * qtile : std::max(nq, 8);
@@ -948,7 +951,7 @@ int omr_open(const omr_config* cfg, omr_store** out) {
     delete s;
     return fail_msg(OMR_E_CAPACITY, "memory: a shard holds at most 2^31 rows");
   }
-  s->margin = cfg->candidate_margin > 0 ? cfg->candidate_margin : 1e-3f;
+  s->margin = cfg->candidate_margin > 0 ? cfg->candidate_margin : 4.5e-3f;  // deterministic bound, DESIGN.md section 3
   if (const char* e = getenv("OMR_LEGACY_POST")) s->legacy_post = e[0] == '1';
   if (const char* e = getenv("OMR_POST_TIMING")) s->post_timing = e[0] == '1';
   if (const char* e = getenv("OMR_STREAM_LDG")) g_force_ldg_stream = e[0] == '1';
