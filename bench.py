@@ -249,11 +249,14 @@ def main():
     # queries/s for the NCCL allgather at N=8, profiles/r01_exchange_*); NCCL if the IPC mapping cannot be set up.
     exchange = os.environ.get("OMNIA_BENCH_EXCHANGE", "p2p") if world > 1 else "none"
     fpath = int(os.environ.get("OMNIA_BENCH_PATH", 0))
+    # experiment knobs (0 = the library's defaults): candidate margin and first-pass rescore width
+    tune = {"candidate_margin": float(os.environ.get("OMNIA_BENCH_MARGIN", 0.0)),
+            "rescore_width": int(os.environ.get("OMNIA_BENCH_K2", 0))}
     sr = None
     if exchange == "p2p":
         ok = 1
         try:
-            sr = ShardedRecall(DIM, N_ROWS, local_rank, exchange="p2p", nq_max=NQ, k_max=TOPK, force_path=fpath)
+            sr = ShardedRecall(DIM, N_ROWS, local_rank, exchange="p2p", nq_max=NQ, k_max=TOPK, force_path=fpath, **tune)
         except Exception as e:  # noqa: BLE001
             print(f"[bench] rank {rank}: fused exchange unavailable ({e}); falling back to NCCL", file=sys.stderr)
             ok = 0
@@ -265,7 +268,7 @@ def main():
             sr, exchange = None, "nccl"
     if sr is None:
         sr = ShardedRecall(DIM, N_ROWS, local_rank, exchange=exchange if exchange == "nccl" else "nccl",
-                           nq_max=NQ, k_max=TOPK, force_path=fpath)
+                           nq_max=NQ, k_max=TOPK, force_path=fpath, **tune)
     sr.store.bulk_load(shard)
     # query batches: perturbed copies of stored rows, identical on every rank
     hq = []

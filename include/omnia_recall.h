@@ -69,7 +69,7 @@ typedef struct omr_config {
   int64_t capacity;         /* rows this shard can hold */
   int64_t row_base;         /* global row id = row_base + local_row * row_stride */
   int64_t row_stride;       /* 0 is read as 1 */
-  float candidate_margin;   /* bf16 stage error allowance in cosine units; <= 0 -> 4.5e-3, the deterministic bound */
+  float candidate_margin;   /* bf16 stage error allowance in cosine units; <= 0 -> 1e-3 (>= 14 sigma); 4.5e-3 = the deterministic bound */
   int32_t sub_bucket;       /* 0 = choose from k; else 32 / 64 / 128 / 256 */
   int32_t rescore_width;    /* 0 = choose from k; candidates rescored exactly per query */
   int32_t force_path;       /* 0 auto, 1 streaming scorer, 2 tensor-core scorer (one CTA per tile),

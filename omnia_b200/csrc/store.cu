@@ -154,7 +154,7 @@ struct omr_store {
   omr_config cfg{};
   int dim = 0, pitch = 0, num_sms = 148;
   int64_t cap = 0, n = 0;
-  float margin = 4.5e-3f;
+  float margin = 1e-3f;
   std::mutex mu;
   cudaStream_t stream = nullptr;
   EncodeTiledFn encode = nullptr;
@@ -951,7 +951,7 @@ int omr_open(const omr_config* cfg, omr_store** out) {
     delete s;
     return fail_msg(OMR_E_CAPACITY, "memory: a shard holds at most 2^31 rows");
   }
-  s->margin = cfg->candidate_margin > 0 ? cfg->candidate_margin : 4.5e-3f;  // deterministic bound, DESIGN.md section 3
+  s->margin = cfg->candidate_margin > 0 ? cfg->candidate_margin : 1e-3f;  // 4.5e-3 = deterministic bound, DESIGN.md section 3
   if (const char* e = getenv("OMR_LEGACY_POST")) s->legacy_post = e[0] == '1';
   if (const char* e = getenv("OMR_POST_TIMING")) s->post_timing = e[0] == '1';
   if (const char* e = getenv("OMR_STREAM_LDG")) g_force_ldg_stream = e[0] == '1';
