@@ -363,7 +363,7 @@ __global__ void __launch_bounds__(1024) select_exact_kernel(const double* __rest
                                                             int32_t* __restrict__ sel_rows,
                                                             double* __restrict__ sel_dist) {
   __shared__ RadixState rs;
-  __shared__ uint32_t s_out, s_eq;
+  __shared__ uint32_t s_out;
   __shared__ unsigned long long s_finite;
   const int slot = blockIdx.x;
   const int q = slot_query[slot];
@@ -373,7 +373,6 @@ __global__ void __launch_bounds__(1024) select_exact_kernel(const double* __rest
   const unsigned long long kInf = 0x7FF0000000000000ull;
   if (threadIdx.x == 0) {
     s_out = 0;
-    s_eq = 0;
     s_finite = 0;
     rs.prefix = 0;
     rs.mask = 0;
