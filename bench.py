@@ -251,7 +251,8 @@ def main():
     fpath = int(os.environ.get("OMNIA_BENCH_PATH", 0))
     # experiment knobs (0 = the library's defaults): candidate margin and first-pass rescore width
     tune = {"candidate_margin": float(os.environ.get("OMNIA_BENCH_MARGIN", 0.0)),
-            "rescore_width": int(os.environ.get("OMNIA_BENCH_K2", 0))}
+            "rescore_width": int(os.environ.get("OMNIA_BENCH_K2", 0)),
+            "sub_bucket": int(os.environ.get("OMNIA_BENCH_S", 0))}
     sr = None
     if exchange == "p2p":
         ok = 1
@@ -336,7 +337,7 @@ def main():
     run_steps(0, args.warmup)
     torch.cuda.synchronize()
     barrier()
-    sampler = ClockSampler(local_rank)
+    sampler = ClockSampler(local_rank, float(os.environ.get("OMNIA_BENCH_SAMPLER_S", 0.004)))
     st0 = sr.store.stats()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     if rank == 0:
