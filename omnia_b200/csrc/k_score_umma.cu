@@ -360,19 +360,43 @@ struct __align__(8) PipeBarriers2 {
   uint64_t tmem_empty[2];
   uint32_t tmem_base;
 };
-constexpr int kSmemBytes2 = kStages2 * kStageBytes2 + (int)sizeof(PipeBarriers2) + 1024;
+constexpr int kSmemBytes2 = kStages2 * kStageBytes2 + (int)sizeof(PipeBarriers2) + kPairStageBytes + 1024;
 
-template <int S>
+// Work item of the pair kernel -> (A tile of 256 rows, B tile of 256 rows).  Self-join: super-blocks of
+// sb x sb tiles over the upper triangle, as decode_work, at 256-row granularity on both sides.
+template <bool kSelfJoin>
+__device__ __forceinline__ bool decode_work2(int64_t w, int n_a_tiles, int n_b_tiles, int sb, int& a_tile, int& b_tile) {
+  if (!kSelfJoin) {
+    b_tile = (int)(w / n_a_tiles);
+    a_tile = (int)(w % n_a_tiles);
+    return true;
+  } else {
+    const int64_t per = (int64_t)sb * sb;
+    const int64_t blk = w / per;
+    const int t = (int)(w - blk * per);
+    int64_t J = (int64_t)((sqrt(8.0 * (double)blk + 1.0) - 1.0) * 0.5);
+    while (J * (J + 1) / 2 > blk) J--;
+    while ((J + 1) * (J + 2) / 2 <= blk) J++;
+    const int64_t I = blk - J * (J + 1) / 2;
+    a_tile = (int)(I * sb) + t % sb;
+    b_tile = (int)(J * sb) + t / sb;
+    return a_tile < n_a_tiles && b_tile < n_b_tiles && a_tile <= b_tile;
+  }
+}
+
+template <bool kSelfJoin, int S>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kNumThreads, 1)
     score_umma2_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_rows,
-                       const KernelArgs<false, S> args) {
+                       const KernelArgs<kSelfJoin, S> args) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* smem_a = smem;
   uint8_t* smem_b = smem + kStages2 * kABytes;
   PipeBarriers2* bars = reinterpret_cast<PipeBarriers2*>(smem + kStages2 * kStageBytes2);
+  PairStage* pstage = reinterpret_cast<PairStage*>(reinterpret_cast<uint8_t*>(bars) + ((sizeof(PipeBarriers2) + 15) & ~size_t(15)));
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (kSelfJoin && threadIdx.x == 0) pstage->count = 0;
   const uint32_t rank = ptx::cluster_ctarank();
   const bool leader = rank == 0;
   const int64_t cluster = ptx::cluster_id_x(), n_clusters = ptx::cluster_nctaid_x();
@@ -405,7 +429,10 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kNumThreads, 1)
       int stage = 0;
       uint32_t phase = 0;
       for (int64_t w = cluster; w < args.n_work; w += n_clusters) {
-        const int b_tile = (int)(w / args.n_a_tiles), a_tile = (int)(w % args.n_a_tiles);
+        int a_tile, b_tile;
+        if (!decode_work2<kSelfJoin>(args.work_first + w * args.work_step, args.n_a_tiles, args.n_b_tiles, args.sb, a_tile,
+                                     b_tile))
+          continue;
         for (int kb = 0; kb < args.k_blocks; kb++) {
           ptx::mbar_wait(&bars->empty[stage], phase ^ 1);
           if (leader) ptx::mbar_arrive_expect_tx(&bars->full[stage], 2 * kStageBytes2);
@@ -413,7 +440,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kNumThreads, 1)
           ptx::tma_load_2d_2sm(smem_a + stage * kABytes, &tmap_q, &bars->full[stage], kb * kBlockK,
                                a_tile * 2 * kQueryTile + (int)rank * kQueryTile, ptx::kEvictLast);
           ptx::tma_load_2d_2sm(smem_b + stage * kHalfBBytes, &tmap_rows, &bars->full[stage], kb * kBlockK,
-                               b_tile * kTileRows + (int)rank * (kTileRows / 2), ptx::kEvictNormal);
+                               b_tile * kTileRows + (int)rank * (kTileRows / 2),
+                               kSelfJoin ? ptx::kEvictLast : ptx::kEvictNormal);
           if (++stage == kStages2) {
             stage = 0;
             phase ^= 1;
@@ -426,8 +454,14 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kNumThreads, 1)
     constexpr uint32_t idesc = ptx::make_idesc_bf16(2 * kQueryTile, kTileRows);
     int stage = 0;
     uint32_t phase = 0, it = 0;
-    for (int64_t w = cluster; w < args.n_work; w += n_clusters, it++) {
+    for (int64_t w = cluster; w < args.n_work; w += n_clusters) {
+      if (kSelfJoin) {
+        int ta, tb;
+        if (!decode_work2<kSelfJoin>(args.work_first + w * args.work_step, args.n_a_tiles, args.n_b_tiles, args.sb, ta, tb))
+          continue;
+      }
       const uint32_t as = it & 1, aphase = (it >> 1) & 1;
+      it++;
       ptx::mbar_wait(&bars->tmem_empty[as], aphase ^ 1);
       ptx::tc_fence_after_sync();
       for (int kb = 0; kb < args.k_blocks; kb++) {
@@ -456,14 +490,25 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kNumThreads, 1)
     const uint32_t lane_addr = tmem_base + ((uint32_t)(quarter * 32) << 16);
     uint32_t it = 0;
     Top2Epilogue<S> te;
-    for (int64_t w = cluster; w < args.n_work; w += n_clusters, it++) {
-      const int b_tile = (int)(w / args.n_a_tiles), a_tile = (int)(w % args.n_a_tiles);
+    PairEpilogue pe = args.pe;
+    pe.stage = pstage;
+    for (int64_t w = cluster; w < args.n_work; w += n_clusters) {
+      int a_tile, b_tile;
+      if (!decode_work2<kSelfJoin>(args.work_first + w * args.work_step, args.n_a_tiles, args.n_b_tiles, args.sb, a_tile,
+                                   b_tile))
+        continue;
       const uint32_t as = it & 1, aphase = (it >> 1) & 1;
+      it++;
       const int q = a_tile * 2 * kQueryTile + (int)rank * kQueryTile + t_local;
-      const int g = (args.query_group && q < args.nq) ? __ldg(args.query_group + q) : 0;
-      te.bitmap_row = args.bitmaps + (int64_t)g * args.words_per_group;
-      te.out = args.cand_keys + (int64_t)q * args.keys_per_query;
-      te.begin_tile();
+      if (!kSelfJoin) {
+        const int g = (args.query_group && q < args.nq) ? __ldg(args.query_group + q) : 0;
+        te.bitmap_row = args.bitmaps + (int64_t)g * args.words_per_group;
+        te.out = args.cand_keys + (int64_t)q * args.keys_per_query;
+        te.begin_tile();
+      } else {
+        pe.row_a = q;
+        pe.a_member = (__ldg(pe.member + (pe.row_a >> 5)) >> (pe.row_a & 31)) & 1u;
+      }
       ptx::mbar_wait(&bars->tmem_full[as], aphase);
       ptx::tc_fence_after_sync();
 #pragma unroll 1
@@ -473,11 +518,17 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kNumThreads, 1)
         ptx::tmem_ld_32x32(lane_addr + as * kTileRows + c * 32, v0);
         ptx::tmem_ld_32x32(lane_addr + as * kTileRows + (c + 1) * 32, v1);
         ptx::tmem_ld_wait();
-        te.chunk(b_tile, c, v0);
-        te.chunk(b_tile, c + 1, v1);
+        if (!kSelfJoin) {
+          te.chunk(b_tile, c, v0);
+          te.chunk(b_tile, c + 1, v1);
+        } else {
+          pe.chunk(b_tile, c, v0);
+          pe.chunk(b_tile, c + 1, v1);
+        }
       }
       ptx::tc_fence_before_sync();
       ptx::mbar_arrive_cluster(&bars->tmem_empty[as], 0);
+      if (kSelfJoin) pe.flush(t_local);
     }
   }
 
@@ -503,7 +554,7 @@ int launch_recall2_s(const CUtensorMap& tmap_q, const CUtensorMap& tmap_rows_hal
   a.query_group = query_group;
   a.cand_keys = cand_keys;
   a.keys_per_query = (int64_t)n_tiles * (kTileRows / S) * 2;
-  auto kern = score_umma2_kernel<S>;
+  auto kern = score_umma2_kernel<false, S>;
   OMR_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes2));
   int64_t clusters = num_sms / 2;
   if (clusters > a.n_work) clusters = a.n_work;
@@ -571,6 +622,42 @@ int launch_score_umma2(const CUtensorMap& tmap_q, const CUtensorMap& tmap_rows_h
     case 256: return launch_recall2_s<256>(tmap_q, tmap_rows_half, nq, n_qtiles256, n_tiles, k_blocks, bitmaps, words_per_group, query_group, cand_keys, num_sms, st);
   }
   return fail_msg(-2, "sub-bucket size must be 32, 64, 128 or 256, got %d", S);
+}
+
+// Self-join on CTA pairs: tmap_half is the 128-row-box map of the member matrix (it serves both operands:
+// each CTA loads its half of the 256-row A tile and its half of the 256-row B tile).
+int launch_selfjoin_umma2(const CUtensorMap& tmap_half, int64_t n, int k_blocks, int part_index, int part_count,
+                          float threshold, const uint32_t* member_bitmap, PairCand* pairs, unsigned long long cap,
+                          unsigned long long* pair_count, int num_sms, cudaStream_t st) {
+  if (n <= 0) return 0;
+  const int64_t nb = (n + kTileRows - 1) / kTileRows;
+  KernelArgs<true, 256> a{};
+  a.n_a_tiles = (int)nb;
+  a.n_b_tiles = (int)nb;
+  int sb = 24;
+  if (k_blocks > 0) sb = std::max(8, std::min(96, 24 * 24 / k_blocks));
+  if (const char* e = getenv("OMR_SELFJOIN_SB")) sb = std::max(1, atoi(e));
+  a.sb = sb;
+  const int64_t NB = (nb + sb - 1) / sb;
+  const int64_t total = NB * (NB + 1) / 2 * ((int64_t)sb * sb);
+  if (part_count < 1) part_count = 1;
+  a.work_first = part_index;
+  a.work_step = part_count;
+  a.n_work = part_index < total ? (total - part_index + part_count - 1) / part_count : 0;
+  if (a.n_work == 0) return 0;
+  a.k_blocks = k_blocks;
+  a.pe.member = member_bitmap;
+  a.pe.pairs = pairs;
+  a.pe.cap = cap;
+  a.pe.count = pair_count;
+  a.pe.threshold = threshold;
+  auto kern = score_umma2_kernel<true, 256>;
+  OMR_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes2));
+  int64_t clusters = num_sms / 2;
+  if (clusters > a.n_work) clusters = a.n_work;
+  kern<<<(unsigned)(2 * clusters), kNumThreads, kSmemBytes2, st>>>(tmap_half, tmap_half, a);
+  OMR_CUDA_OK(cudaGetLastError());
+  return 0;
 }
 
 int launch_selfjoin_umma(const CUtensorMap& tmap_a, const CUtensorMap& tmap_b, int64_t n, int k_blocks,

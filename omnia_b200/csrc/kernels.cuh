@@ -134,6 +134,10 @@ struct PairCand {
 int launch_selfjoin_umma(const CUtensorMap& tmap_a, const CUtensorMap& tmap_b, int64_t n, int k_blocks,
                          int part_index, int part_count, float threshold, const uint32_t* member_bitmap, PairCand* pairs, unsigned long long cap,
                          unsigned long long* pair_count, int num_sms, cudaStream_t st);
+// the same join on CTA pairs (cta_group::2, A and B tiles of 256 rows); tmap_half has a 128-row box
+int launch_selfjoin_umma2(const CUtensorMap& tmap_half, int64_t n, int k_blocks, int part_index, int part_count,
+                          float threshold, const uint32_t* member_bitmap, PairCand* pairs, unsigned long long cap,
+                          unsigned long long* pair_count, int num_sms, cudaStream_t st);
 int launch_pair_rescore(const ShardView& sh, const PairCand* pairs, unsigned long long n_pairs, double* sim,
                         cudaStream_t st);
 int launch_gather_rows(const ShardView& sh, const int32_t* idx, int64_t m, __nv_bfloat16* dst, cudaStream_t st);

@@ -93,7 +93,7 @@ def c4():
     # C4: near-duplicate self-join 1M x 1536, cosine >= 0.92
     n, dim = int(os.environ.get("C4_ROWS", 1_000_000)), 1536
     corpus, planted = synth.planted_dups(n, dim, n_pairs=2000)
-    with GPUMemoryStore(dim, n) as s:
+    with GPUMemoryStore(dim, n, force_path=int(os.environ.get("C4_PATH", 0))) as s:
         s.bulk_load(corpus)
         from bench import ClockSampler
         for sbv in os.environ.get("C4_SB", "default").split(","):
@@ -112,7 +112,7 @@ def c4():
           got = {(min(p.canonical_row, p.dupe_row), max(p.canonical_row, p.dupe_row)) for p in pairs}
           flops = 2.0 * dim * n * (n + 256) / 2
           emit({"config": f"C4: self-join {n} x 1536, cosine >= 0.92", "seconds": dt, "pairs": len(pairs),
-                "kernel_ms": kernel_ms, "clocks": clocks, "sub_block": os.environ.get("OMR_SELFJOIN_SB", "default"), "planted_above_floor": len(want), "planted_found": len(want & got), "unplanted_pairs": len(got - want),
+                "kernel_ms": kernel_ms, "clocks": clocks, "sub_block": os.environ.get("OMR_SELFJOIN_SB", "default"), "kernel": "1 cta" if os.environ.get("C4_PATH") == "2" else "cta pair", "planted_above_floor": len(want), "planted_found": len(want & got), "unplanted_pairs": len(got - want),
                 "roofline": {"bound": "tensor", "achieved": flops / dt / 1e12, "peak": PEAKS["bf16_tflops_sustained"], "unit": "TFLOP/s",
                              "frac": flops / dt / 1e12 / PEAKS["bf16_tflops_sustained"], "note": "wall time of the whole omr_selfjoin call, host post-processing included"}})
 

@@ -15,15 +15,16 @@ def gpu_pairs(store, ws, floor, limit=0, **kw):
     return [(p.canonical_row, p.dupe_row, p.similarity) for p in out], out
 
 
-@pytest.mark.parametrize("n,dim", [(4096, 256), (3000, 1536), (700, 100)])
-def test_planted_duplicates_pair_set_is_identical(n, dim):
+@pytest.mark.parametrize("path", [0, 2])          # 0 = the CTA-pair (cta_group::2) join kernel, 2 = the 1-CTA kernel
+@pytest.mark.parametrize("n,dim", [(4096, 256), (3000, 1536), (700, 100), (13_000, 128)])
+def test_planted_duplicates_pair_set_is_identical(n, dim, path):
     corpus, planted = synth.planted_dups(n, dim, n_pairs=40)
     rng = np.random.default_rng(11)
     ids = rng.integers(0, 256, (n, 16)).astype(np.uint8)          # random uuids: order unrelated to rows
     kind = rng.integers(0, 2, n).astype(np.uint16)
     flags = np.full(n, ROW_HAS_EMBEDDING | ROW_MUTABLE, np.uint8)
     flags[rng.random(n) < 0.05] &= ~np.uint8(ROW_MUTABLE)
-    with GPUMemoryStore(dim, n) as s:
+    with GPUMemoryStore(dim, n, force_path=path) as s:
         s.bulk_load(corpus, observation_ids=ids, entity_ids=ids, kinds=["a", "b"], kind_idx=kind, flags=flags)
         for floor in (0.92, 0.85):
             got, _ = gpu_pairs(s, "default", floor)
