@@ -86,3 +86,19 @@ def test_block_partitions_of_the_pair_space_union_to_the_whole_join(parts):
         assert len(whole) >= 30
         top5 = sorted(union, key=lambda t: (-t[2], t[0], t[1]))[:5]
         assert top5 == whole[:5]
+
+
+@pytest.mark.parametrize("path", [0, 2])
+@pytest.mark.parametrize("sb", [1, 2, 5])
+def test_super_block_walk_covers_every_tile_pair_once(monkeypatch, sb, path):
+    # 2900 rows = 12 B tiles (the last one ragged); super-block edges of 1, 2 and 5 tiles give 12, 6 and 3
+    # block columns, with full, diagonal and ragged super-blocks.  Every planted pair must appear exactly once.
+    monkeypatch.setenv("OMR_SELFJOIN_SB", str(sb))
+    n, dim = 2900, 192
+    corpus, planted = synth.planted_dups(n, dim, n_pairs=120, sims=(0.93, 0.97, 0.999))
+    with GPUMemoryStore(dim, n, force_path=path) as s:
+        s.bulk_load(corpus)
+        pairs = s.run_entity_duplicate_candidates("default", 0.92, 0, require_same_kind=False)
+    got = [(min(p.canonical_row, p.dupe_row), max(p.canonical_row, p.dupe_row)) for p in pairs]
+    want = sorted((min(int(i), int(j)), max(int(i), int(j))) for i, j, _ in planted)
+    assert sorted(got) == want and len(set(got)) == len(got)
