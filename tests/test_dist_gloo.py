@@ -76,3 +76,58 @@ def test_shard_of_covers_every_row_once():
                 cnt, base, stride = shard_of(n, r, world)
                 rows += [base + i * stride for i in range(cnt)]
             assert sorted(rows) == list(range(n))
+
+
+class _StubJoinStore:
+    """Stands in for GPUMemoryStore in the self-join plumbing test: its pairs are the oracle's, cut into parts the
+    way the kernel's interleaved work items cut them (any disjoint cover will do for the host logic)."""
+
+    def __init__(self, pairs):
+        self.pairs = pairs
+
+    def run_entity_duplicate_candidates(self, workspace_id, similarity_floor, max_buckets_per_pass, part_index=0,
+                                        part_count=1, **kw):
+        mine = [p for i, p in enumerate(self.pairs) if i % part_count == part_index]
+        mine.sort(key=lambda p: (-p.similarity, p.canonical_row, p.dupe_row))
+        return mine[:max_buckets_per_pass] if max_buckets_per_pass > 0 else mine
+
+
+def _join_worker(rank, world, port, limit, out):
+    from omnia_b200.dist import sharded_selfjoin
+    from omnia_b200.store import DuplicatePair
+    from helpers import ids_from_rows
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        n, dim = 1500, 64
+        corpus, _ = synth.planted_dups(n, dim, n_pairs=60)
+        a, b, s = O.selfjoin(corpus, None, np.zeros(n, np.uint16), np.full(n, 12, np.uint8), ids_from_rows(n), 0.9,
+                             variant=O.VARIANT_F64)
+        pairs = [DuplicatePair(f"e{int(x)}", f"e{int(y)}", float(v), "", int(x), int(y)) for x, y, v in zip(a, b, s)]
+        rng = np.random.default_rng(5)
+        rng.shuffle(pairs)                                   # the parts must not rely on any input order
+        got = sharded_selfjoin(_StubJoinStore(pairs), "default", 0.9, limit)
+        want = sorted(pairs, key=lambda p: (-p.similarity, p.canonical_row, p.dupe_row))
+        want = want[:limit] if limit > 0 else want
+        assert [(p.canonical_row, p.dupe_row) for p in got] == [(p.canonical_row, p.dupe_row) for p in want]
+        if rank == 0:
+            out.put(len(got))
+        dist.barrier()
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,limit", [(2, 0), (3, 7)])
+def test_sharded_selfjoin_merges_the_parts_over_gloo(world, limit):
+    ctx = mp.get_context("spawn")
+    out = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_join_worker, args=(r, world, port, limit, out)) for r in range(world)]
+    for p in procs:
+        p.start()
+    n = out.get(timeout=120)
+    for p in procs:
+        p.join(timeout=120)
+        assert p.exitcode == 0
+    assert n == (7 if limit else n) and n > 0
