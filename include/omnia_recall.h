@@ -69,7 +69,9 @@ typedef struct omr_config {
   int64_t capacity;         /* rows this shard can hold */
   int64_t row_base;         /* global row id = row_base + local_row * row_stride */
   int64_t row_stride;       /* 0 is read as 1 */
-  float candidate_margin;   /* bf16 stage error allowance in cosine units; <= 0 -> 1e-3 (>= 14 sigma); 4.5e-3 = the deterministic bound */
+  float candidate_margin;   /* bf16 stage error allowance in cosine units; <= 0 -> 4.5e-3, the deterministic bound
+                               of the bf16 stage for any dim <= 2048; smaller values turn the
+                               exactness proof into a statistical statement and are for experiments only */
   int32_t sub_bucket;       /* 0 = choose from k; else 32 / 64 / 128 / 256 */
   int32_t rescore_width;    /* 0 = choose from k; candidates rescored exactly per query */
   int32_t force_path;       /* 0 auto, 1 streaming scorer, 2 tensor-core scorer (one CTA per tile),
@@ -336,7 +338,7 @@ typedef struct omr_stats {
   int64_t kernel_launches;   /* kernels this store has enqueued */
   int64_t searches;          /* query batches */
   int64_t queries;           /* queries */
-  int64_t rescued_rows;      /* rows rescored because their sub-bucket was suspect */
+  int64_t rescued_rows;      /* rows rescored beyond the first round (emission mode) / because their sub-bucket was suspect */
   int64_t fallback_queries;  /* queries answered by the exact scan */
   int32_t last_path;         /* 1 streaming, 2 tensor-core, 3 exact */
   int32_t last_sub_bucket;
@@ -346,6 +348,13 @@ typedef struct omr_stats {
   int64_t scorer_timed;      /* batches that sum covers */
   int64_t host_calls;        /* omr_search / omr_search_rows calls */
   int64_t host_batches;      /* searches they were coalesced into (concurrent calls share one pass) */
+  int64_t listed_entries;    /* candidate-list entries the tensor-core scorers emitted (emission mode) */
+  double phase_ms_sum[3];    /* profiling on, emission mode: seed pass | seed thresholds | post kernel, summed over
+                                the batches scorer_timed counts (stream time between the events around each) */
+  double scorer_kernel_ms_sum; /* profiling on, emission mode: the scorer kernel's own span (first CTA start to last
+                                  CTA end, %globaltimer), summed; unlike scorer_ms_sum it excludes the time the
+                                  kernel queued behind another batch in flight */
+  int64_t scorer_kernel_timed;
 } omr_stats;
 OMR_API int omr_get_stats(const omr_store* s, omr_stats* out);
 /* Brackets the approximate scorer (the dominant kernel) with CUDA events on the search stream

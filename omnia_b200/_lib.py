@@ -71,7 +71,9 @@ class Stats(C.Structure):
                 ("rescued_rows", C.c_int64), ("fallback_queries", C.c_int64), ("last_path", C.c_int32),
                 ("last_sub_bucket", C.c_int32), ("last_rescore_width", C.c_int32), ("num_sms", C.c_int32),
                 ("scorer_ms_sum", C.c_double), ("scorer_timed", C.c_int64), ("host_calls", C.c_int64),
-                ("host_batches", C.c_int64)]
+                ("host_batches", C.c_int64), ("listed_entries", C.c_int64),
+                ("phase_ms_sum", C.c_double * 3), ("scorer_kernel_ms_sum", C.c_double),
+                ("scorer_kernel_timed", C.c_int64)]
 
 
 # name -> (restype, argtypes).  tests/test_abi.py checks this table against the header.

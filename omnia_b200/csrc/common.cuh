@@ -51,6 +51,23 @@ __host__ __device__ __forceinline__ float key_score_upper(int32_t key) {
 #endif
 }
 
+// Inverse of score_to_ordered.
+__host__ __device__ __forceinline__ float ordered_to_score(int32_t k) {
+  int32_t b = k ^ ((k >> 31) & 0x7fffffff);
+#ifdef __CUDA_ARCH__
+  return __int_as_float(b);
+#else
+  float f;
+  memcpy(&f, &b, 4);
+  return f;
+#endif
+}
+// The same order on unsigned integers (what the emission lists store): 0 is below every score.
+__host__ __device__ __forceinline__ uint32_t score_to_biased(float s) { return (uint32_t)score_to_ordered(s) ^ 0x80000000u; }
+__host__ __device__ __forceinline__ float biased_to_score(uint32_t u) { return ordered_to_score((int32_t)(u ^ 0x80000000u)); }
+constexpr int32_t kOrderedNegInf = (int32_t)0x807FFFFF;  // score_to_ordered(-inf): every score clears it
+constexpr int32_t kOrderedPosInf = (int32_t)0x7F800000;  // score_to_ordered(+inf): no finite score clears it
+
 __device__ __forceinline__ void top2_insert(int32_t& m1, int32_t& m2, int32_t k) {
   m2 = max(m2, min(m1, k));
   m1 = max(m1, k);

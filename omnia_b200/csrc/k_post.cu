@@ -501,7 +501,256 @@ __global__ void __launch_bounds__(kPostThreads, 2) post_kernel(PostArgs a) {
   if (tid == 0 && sm.fail) a.fail_list[atomicAdd(a.fail_count, 1)] = q;
 }
 
+
+// =====================================================================================
+// Emission mode (tensor-core scorers, k <= 256): the scorer leaves a short per-query list of every
+// eligible row whose approximate score cleared the query's running threshold (k_score_umma.cu).
+// Nothing below T - band was ever skipped (T = the k-th best approximate score, band = 2 * margin),
+// so the exact top-k is inside the list and no certificate pass over the store is needed.
+
+constexpr int kEmitThreads = 256;
+constexpr int kEmitCand = 512;  // entries within the band of T that one block can rescore; more -> exact scan
+constexpr int kEmitRegs = 16;   // list entries per thread held in registers during the selection
+
+struct EmitSmem {
+  unsigned long long sk[kEmitCand];  // (biased score << 32 | ~row): descending = best score first, smaller row first
+  double sd[kEmitCand];
+  int32_t sr[kEmitCand];
+  int cnt[3];
+  int n_keep, n_b, fail;
+};
+
+// One warp per query: the k-th largest of the seed keys (top-2 per 32 rows over the first row tiles; distinct
+// rows, so k of them at or above a value bound the k-th best score of the whole store from below).
+__global__ void __launch_bounds__(256) emit_seed_kernel(const int32_t* __restrict__ seed_keys, int64_t kpq,
+                                                        const double* __restrict__ qnorm2, int nq, int qpad, EmitView ev) {
+  const int q = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  if (q >= qpad) return;
+  int32_t thr = kOrderedPosInf;  // padding rows of the last query tile and queries without a cosine emit nothing
+  if (q < nq) {
+    const double n2 = qnorm2[q];
+    if (n2 > 0.0 && n2 < INFINITY) {
+      const int32_t* keys = seed_keys + (int64_t)q * kpq;
+      uint32_t prefix = 0;
+      for (int bit = 31; bit >= 0; bit--) {
+        const uint32_t cand = prefix | (1u << bit);
+        int c = 0;
+        for (int64_t j = lane; j < kpq; j += 32) c += ((uint32_t)(__ldg(keys + j) & ~0xFF) ^ 0x80000000u) >= cand;
+        c = __reduce_add_sync(0xffffffffu, c);
+        if (c >= ev.k) prefix = cand;
+      }
+      // fewer than k keys (kKeyNone maps below every candidate value): no bound yet
+      thr = prefix == 0u ? kOrderedNegInf : score_to_ordered(biased_to_score(prefix) - ev.band);
+    }
+  }
+  if (lane == 0) {
+    ev.thr[q] = thr;
+    ev.count[q] = 0u;
+  }
+}
+
+__global__ void __launch_bounds__(kEmitThreads, 2) emit_post_kernel(EmitPostArgs a) {
+  extern __shared__ __align__(16) uint8_t raw[];
+  double* qd = reinterpret_cast<double*>(raw);  // [pitch]
+  EmitSmem& sm = *reinterpret_cast<EmitSmem*>(qd + a.sh.pitch);
+  const int q = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  constexpr int kWarps = kEmitThreads / 32;
+  const unsigned int n_raw = a.ev.count[q];
+  const int n = (int)min(n_raw, (unsigned)a.ev.cap);
+  unsigned long long* list = a.ev.list + (size_t)q * a.ev.cap;
+  const double qn2 = a.qnorm2[q];
+  const double maxd = a.max_dist ? a.max_dist[q] : INFINITY;
+
+  for (int i = tid; i < a.sh.pitch; i += kEmitThreads) qd[i] = i < a.sh.dim ? (double)a.q[(int64_t)q * a.sh.dim + i] : 0.0;
+  if (tid == 0) {
+    sm.cnt[0] = sm.cnt[1] = sm.cnt[2] = 0;
+    sm.n_keep = 0;
+    sm.n_b = 0;
+    sm.fail = n_raw > (unsigned)a.ev.cap;
+  }
+  // ---- the list: first 4096 entries in registers, the rest (large k only) re-read from L2
+  unsigned long long e[kEmitRegs];
+#pragma unroll
+  for (int j = 0; j < kEmitRegs; j++) {
+    const int i = tid + j * kEmitThreads;
+    e[j] = i < n ? __ldcg(list + i) : 0ull;
+  }
+  __syncthreads();
+  // ---- T = k-th largest approximate score in the list (bit by bit, largest prefix with >= k entries at or above it)
+  uint32_t prefix = 0;
+  for (int bit = 31; bit >= 0; bit--) {
+    const uint32_t cand = prefix | (1u << bit);
+    int c = 0;
+#pragma unroll
+    for (int j = 0; j < kEmitRegs; j++) c += (uint32_t)(e[j] >> 32) >= cand;
+    for (int i = kEmitRegs * kEmitThreads + tid; i < n; i += kEmitThreads) c += (uint32_t)(__ldcg(list + i) >> 32) >= cand;
+    c = __reduce_add_sync(0xffffffffu, c);
+    int* slot = &sm.cnt[bit % 3];
+    if (tid == 0) sm.cnt[(bit + 2) % 3] = 0;  // the counter of the NEXT round (bit - 1); last read two rounds ago
+    if (lane == 0 && c) atomicAdd(slot, c);
+    __syncthreads();
+    if (*slot >= a.k) prefix = cand;
+  }
+  // ---- keep what lies within the band of T (everything when the list holds fewer than k rows)
+  uint32_t cut = prefix == 0u ? 1u : score_to_biased(biased_to_score(prefix) - a.ev.band);
+  if (maxd < INFINITY) {  // `<= maxDistance`: a row that passes scores at least 1 - maxd - margin approximately
+    const uint32_t c2 = score_to_biased((float)(1.0 - maxd) - a.margin - 1e-6f);
+    cut = max(cut, c2);
+  }
+  auto keep = [&](unsigned long long v) {
+    if ((uint32_t)(v >> 32) >= cut && v != 0ull) {
+      const int pos = atomicAdd(&sm.n_keep, 1);
+      if (pos < kEmitCand) sm.sk[pos] = (v & 0xFFFFFFFF00000000ull) | (unsigned long long)(~(uint32_t)v);
+    }
+  };
+#pragma unroll
+  for (int j = 0; j < kEmitRegs; j++) keep(e[j]);
+  for (int i = kEmitRegs * kEmitThreads + tid; i < n; i += kEmitThreads) keep(__ldcg(list + i));
+  // the list is consumed: leave it zeroed for the next batch of this lane
+  for (int i = tid; i < n; i += kEmitThreads) __stcg(list + i, 0ull);
+  __syncthreads();
+  if (tid == 0 && a.listed_total) atomicAdd(a.listed_total, n);
+  const int nk = sm.n_keep;
+  if (nk > kEmitCand || sm.fail || !(qn2 > 0.0) || !(qn2 < INFINITY)) {
+    const bool no_cosine = !(qn2 > 0.0) || !(qn2 < INFINITY);  // pgvector: NaN distance, never returned
+    for (int i = tid; i < a.k; i += kEmitThreads) {
+      a.out_rows[(int64_t)q * a.k + i] = -1;
+      a.out_dist[(int64_t)q * a.k + i] = INFINITY;
+    }
+    if (tid == 0) {
+      a.out_count[q] = 0;
+      if (!no_cosine) a.fail_list[atomicAdd(a.fail_count, 1)] = q;
+    }
+    return;
+  }
+  // ---- best approximate score first
+  int P = 2;
+  while (P < nk) P <<= 1;
+  for (int i = nk + tid; i < P; i += kEmitThreads) sm.sk[i] = 0ull;
+  for (int size = 2; size <= P; size <<= 1) {
+    for (int stride = size >> 1; stride > 0; stride >>= 1) {
+      __syncthreads();
+      for (int i = tid; i < (P >> 1); i += kEmitThreads) {
+        const int lo = 2 * i - (i & (stride - 1)), hi = lo + stride;
+        const bool up = ((lo & size) == 0);
+        const unsigned long long x = sm.sk[lo], y = sm.sk[hi];
+        if ((y > x) == up) {
+          sm.sk[lo] = y;
+          sm.sk[hi] = x;
+        }
+      }
+    }
+  }
+  __syncthreads();
+  auto row_of = [&](int i) { return (int32_t)(~(uint32_t)sm.sk[i]); };
+  auto rescore = [&](int from, int to) {  // entries [from, to) of the score order -> sd / sr at the same index
+    for (int c = from + warp; c < to; c += 2 * kWarps) {
+      const int c1 = c + kWarps;
+      const bool two = c1 < to;
+      const int32_t r0 = row_of(c), r1 = two ? row_of(c1) : r0;
+      double d0, d1;
+      exact_distance2(a.sh, r0, r1, two, qd, qn2, lane, d0, d1);
+      if (lane == 0) {
+        sm.sd[c] = d0;
+        sm.sr[c] = r0;
+        if (two) {
+          sm.sd[c1] = d1;
+          sm.sr[c1] = r1;
+        }
+      }
+    }
+  };
+  auto sort_first = [&](int count) {  // ascending (distance, row) over [0, count), padded to a power of two
+    int Q = 2;
+    while (Q < count) Q <<= 1;
+    __syncthreads();
+    for (int i = count + tid; i < Q; i += kEmitThreads) {
+      sm.sd[i] = INFINITY;
+      sm.sr[i] = INT32_MAX;
+    }
+    if (Q <= 32) {
+      __syncthreads();
+      if (warp == 0) {
+        double d = lane < Q ? sm.sd[lane] : INFINITY;
+        int32_t r = lane < Q ? sm.sr[lane] : INT32_MAX;
+        warp_sort_items(d, r, lane);
+        if (lane < Q) {
+          sm.sd[lane] = d;
+          sm.sr[lane] = r;
+        }
+      }
+      __syncthreads();
+    } else {
+      sort_items(sm.sd, sm.sr, Q);
+    }
+  };
+  // ---- round one: the K2 best by approximate score
+  const int A = min(nk, a.K2);
+  rescore(0, A);
+  sort_first(A);
+  // tau0 = the k-th best exact similarity so far: the final k-th is no lower, and a row that can still reach it
+  // scores at least tau0 - margin approximately.  The sorted score order makes those rows a prefix of [A, nk).
+  double need = A >= a.k ? 1.0 - sm.sd[a.k - 1] : -INFINITY;
+  if (maxd < INFINITY) need = fmax(need, 1.0 - maxd);
+  const float thr_a = (float)(need - (double)a.margin) - 1e-6f;
+  {
+    int c = 0;
+    for (int i = A + tid; i < nk; i += kEmitThreads) c += biased_to_score((uint32_t)(sm.sk[i] >> 32)) >= thr_a;
+    c = __reduce_add_sync(0xffffffffu, c);
+    if (lane == 0 && c) atomicAdd(&sm.n_b, c);
+  }
+  __syncthreads();
+  const int B = sm.n_b;
+  if (B > 0) {
+    rescore(A, A + B);  // overwrites the padding sort_first left behind [A, ...)
+    sort_first(A + B);
+    if (tid == 0 && a.rescued_total) atomicAdd(a.rescued_total, B);
+  }
+  int found;
+  {
+    int lo = 0, hi = min(A + B, a.k);
+    while (lo < hi) {
+      const int mid = (lo + hi) >> 1;
+      if (sm.sd[mid] <= maxd && sm.sd[mid] < INFINITY) lo = mid + 1; else hi = mid;
+    }
+    found = lo;
+  }
+  for (int i = tid; i < a.k; i += kEmitThreads) {
+    const bool ok = i < found;
+    a.out_rows[(int64_t)q * a.k + i] = ok ? a.row_base + (int64_t)sm.sr[i] * a.row_stride : -1;
+    a.out_dist[(int64_t)q * a.k + i] = ok ? sm.sd[i] : INFINITY;
+  }
+  if (tid == 0) a.out_count[q] = found;
+}
+
 }  // namespace
+
+bool emit_supported(int k) { return k >= 1 && k <= 256; }
+
+int launch_emit_seed(const int32_t* seed_keys, int64_t keys_per_query, const double* qnorm2, int nq, int qpad,
+                     const EmitView& ev, cudaStream_t st) {
+  if (qpad <= 0) return 0;
+  emit_seed_kernel<<<(qpad + 7) / 8, 256, 0, st>>>(seed_keys, keys_per_query, qnorm2, nq, qpad, ev);
+  OMR_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+int launch_emit_post(const EmitPostArgs& a, cudaStream_t st) {
+  if (a.nq <= 0) return 0;
+  if (a.K2 < a.k || a.K2 > kEmitCand) return fail_msg(-1, "emission post kernel: first round of %d rows for k = %d", a.K2, a.k);
+  const size_t smem = (size_t)a.sh.pitch * sizeof(double) + sizeof(EmitSmem);
+  static bool attr_set = false;
+  if (!attr_set) {
+    OMR_CUDA_OK(cudaFuncSetAttribute(emit_post_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 48 * 1024));
+    // same carve-out as the scorer so a block fits beside a scorer CTA of the next batch (see launch_post)
+    OMR_CUDA_OK(cudaFuncSetAttribute(emit_post_kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                     cudaSharedmemCarveoutMaxShared));
+    attr_set = true;
+  }
+  emit_post_kernel<<<a.nq, kEmitThreads, smem, st>>>(a);
+  OMR_CUDA_OK(cudaGetLastError());
+  return 0;
+}
 
 bool post_fused_supported(int K2, int k) { return K2 <= 256 && k <= 256; }
 

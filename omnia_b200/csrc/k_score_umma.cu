@@ -16,6 +16,12 @@
 //   warps 4-7   epilogue: thread t owns query t of the tile (TMEM lane t), reads its
 //               256 scores 32 columns at a time with tcgen05.ld, applies the scope
 //               bitmap, and keeps the two best per S-row sub-bucket as packed keys.
+//               In the default recall mode (k <= 256) the epilogue keeps no keys at all: it
+//               compares every score with the query's running emission threshold and appends
+//               the few rows that clear it to the query's candidate list (EmitEpilogue).
+//   warp 3      (emission mode) raises the thresholds: every `trigger` appended entries of a
+//               query it takes the k-th best entry of that query's list as a new lower bound
+//               of the final k-th best score, so the epilogue warps never wait for it.
 // While the epilogue drains accumulator i, the tensor core fills accumulator i^1.
 //
 // Rows and queries are unit-normalised before they are rounded to bf16 (k_ingest.cu),
@@ -51,6 +57,8 @@ struct __align__(8) PipeBarriers {
   uint32_t tmem_base;
 };
 
+enum { kEpiTop2 = 0, kEpiPairs = 1, kEpiEmit = 2 };
+
 struct PairStage;
 constexpr int kPairStageBytes = 1024 * 8 + 32;
 constexpr int kSmemBytes = kStages * kStageBytes + (int)sizeof(PipeBarriers) + kPairStageBytes + 1024;  // +1024: manual alignment
@@ -85,6 +93,140 @@ struct Top2Epilogue {
     }
   }
 };
+
+
+// ---- threshold-filtered emission (recall, k <= 256) ------------------------------------
+// The slot of shared memory the self-join uses to stage pairs holds, in a recall launch, the
+// refresh warp's work: a ring of query numbers whose threshold is due for a refresh and the
+// scratch the refresh selects in.
+constexpr int kRefreshBuf = 1024;
+constexpr int kRefreshSlots = 64;
+struct RefreshQueue {
+  uint32_t buf[kRefreshBuf];
+  unsigned int slot[kRefreshSlots];  // query + 1; 0 = empty
+  unsigned int tail;
+  unsigned int epi_done;             // epilogue warps that have finished their tiles
+};
+static_assert(sizeof(RefreshQueue) <= kPairStageBytes, "RefreshQueue outgrew the pair-stage slot");
+
+__device__ __forceinline__ uint32_t pick32(const uint32_t (&v)[32], int j) {
+  uint32_t r = v[0];
+#pragma unroll
+  for (int i = 1; i < 32; i++) r = (j == i) ? v[i] : r;
+  return r;
+}
+
+// Appends (score, row) to query q's list; out of line so the scorer's hot loop stays small.  Every
+// `trigger`-th entry of a query (and its k-th) also files a refresh request with this CTA's warp 3.
+__device__ __noinline__ void emit_entry(int32_t* thr, unsigned int* count, unsigned long long* list, int cap, int k,
+                                        int trigger, RefreshQueue* rq, int q, int row, uint32_t bits) {
+  const unsigned int slot = atomicAdd(count + q, 1u);
+  if (slot < (unsigned)cap) {
+    const unsigned long long e =
+        ((unsigned long long)score_to_biased(__uint_as_float(bits)) << 32) | (unsigned long long)(uint32_t)row;
+    __stcg(list + (size_t)q * cap + slot, e);
+  } else if (slot == (unsigned)cap) {
+    atomicMax(thr + q, kOrderedPosInf);  // list full: the exact scan answers this query, stop feeding it
+  }
+  const unsigned int c1 = slot + 1;
+  if ((c1 & (unsigned)(trigger - 1)) == 0u || c1 == (unsigned)k) {
+    const unsigned int i = atomicAdd(&rq->tail, 1u);
+    atomicExch(&rq->slot[i & (kRefreshSlots - 1)], (unsigned)q + 1u);
+  }
+}
+
+struct EmitEpilogue {
+  EmitView ev;
+  const uint32_t* bitmap_row;
+  RefreshQueue* rq;
+  int q;
+  float t;  // this tile's emission threshold (the value of thr[q] when the tile began)
+
+  __device__ __forceinline__ void begin_tile(int q_) {
+    q = q_;
+    t = ordered_to_score(__ldcg(ev.thr + q));
+  }
+
+  __device__ __forceinline__ void chunk(int row_tile, int c, const uint32_t (&v)[32]) {
+    uint32_t pass = 0;
+#pragma unroll
+    for (int j = 0; j < 32; j++) pass |= (__uint_as_float(v[j]) >= t) ? (1u << j) : 0u;
+    if (pass == 0u) return;  // the common case: no bitmap word is even loaded
+    pass &= __ldg(bitmap_row + (int64_t)row_tile * 8 + c);
+    while (pass) {
+      const int j = __ffs(pass) - 1;
+      pass &= pass - 1;
+      emit_entry(ev.thr, ev.count, ev.list, ev.cap, ev.k, ev.trigger, rq, q, row_tile * kTileRows + c * 32 + j, pick32(v, j));
+    }
+  }
+};
+
+// One refresh, whole warp: the k-th largest entry of query q's list is a lower bound of the final k-th best
+// approximate score (k distinct eligible rows score at least that), so thr[q] may rise to it minus the band.
+// Entries below the current cut cannot be among the k best and are skipped while the list is read.
+__device__ void refresh_threshold(const EmitView& ev, int q, int lane, uint32_t* buf) {
+  const unsigned int n = min(__ldcg(ev.count + q), (unsigned)ev.cap);
+  if (n < (unsigned)ev.k) return;
+  const int32_t cur = __ldcg(ev.thr + q);
+  if (cur == kOrderedPosInf) return;
+  // three quarters of the band above the cut: at least k entries lie above it (fp32 rounding of cut + band aside)
+  const uint32_t filt = score_to_biased(ordered_to_score(cur) + 0.75f * ev.band);
+  const unsigned long long* L = ev.list + (size_t)q * ev.cap;
+  int m = 0;
+  for (unsigned int i0 = 0; i0 < n && m <= kRefreshBuf - 128; i0 += 128) {
+    unsigned long long e[4];
+#pragma unroll
+    for (int u = 0; u < 4; u++) {
+      const unsigned int i = i0 + u * 32 + lane;
+      e[u] = i < n ? __ldcg(L + i) : 0ull;
+    }
+#pragma unroll
+    for (int u = 0; u < 4; u++) {
+      const uint32_t key = (uint32_t)(e[u] >> 32);
+      const bool ok = e[u] != 0ull && key >= filt;
+      const unsigned int b = __ballot_sync(0xffffffffu, ok);
+      if (ok) buf[m + __popc(b & ((1u << lane) - 1u))] = key;
+      m += __popc(b);
+    }
+  }
+  __syncwarp();
+  if (m < ev.k) return;
+  uint32_t prefix = 0;
+  for (int bit = 31; bit >= 0; bit--) {
+    const uint32_t cand = prefix | (1u << bit);
+    int c = 0;
+    for (int j = lane; j < m; j += 32) c += buf[j] >= cand;
+    c = __reduce_add_sync(0xffffffffu, c);
+    if (c >= ev.k) prefix = cand;
+  }
+  if (lane == 0) atomicMax(ev.thr + q, score_to_ordered(biased_to_score(prefix) - ev.band));
+  __syncwarp();
+}
+
+// Body of warp 3 in an emission launch: serve refresh requests until the four epilogue warps are done.
+__device__ void refresh_loop(const EmitView& ev, RefreshQueue* rq, int lane) {
+  while (true) {
+    const unsigned int done = *reinterpret_cast<volatile unsigned int*>(&rq->epi_done);
+    const unsigned int v0 = atomicExch(&rq->slot[lane], 0u);
+    const unsigned int v1 = atomicExch(&rq->slot[lane + 32], 0u);
+    unsigned int b0 = __ballot_sync(0xffffffffu, v0 != 0u), b1 = __ballot_sync(0xffffffffu, v1 != 0u);
+    if (!(b0 | b1)) {
+      if (__shfl_sync(0xffffffffu, done, 0) >= 4u) break;
+      __nanosleep(400);
+      continue;
+    }
+    while (b0) {
+      const int src = __ffs(b0) - 1;
+      b0 &= b0 - 1;
+      refresh_threshold(ev, (int)__shfl_sync(0xffffffffu, v0, src) - 1, lane, rq->buf);
+    }
+    while (b1) {
+      const int src = __ffs(b1) - 1;
+      b1 &= b1 - 1;
+      refresh_threshold(ev, (int)__shfl_sync(0xffffffffu, v1, src) - 1, lane, rq->buf);
+    }
+  }
+}
 
 // Epilogue of the self-join: emit (a, b) for a < b when the approximate cosine clears the
 // (margin-lowered) floor and both rows are members of the join.  Pairs are staged in shared
@@ -147,7 +289,7 @@ struct PairEpilogue {
   }
 };
 
-template <bool kSelfJoin, int S>
+template <int kEpi, int S>
 struct KernelArgs {
   int n_a_tiles;   // recall: query tiles; self-join: unused
   int n_b_tiles;   // 256-row tiles of the store
@@ -156,17 +298,31 @@ struct KernelArgs {
   int sb;                         // self-join: B tiles per super-block edge (see decode_work)
   int k_blocks;
   int nq;          // real queries; tiles are padded with zero queries beyond it
-  int n_stages;    // TMA ring depth in use (<= kStages); experiments only, normally kStages
+#ifdef OMR_UMMA_EXPERIMENTS
+  int n_stages;    // TMA ring depth in use (<= kStages)
   int exp;         // experiment bits (OMR_UMMA_EXP): 1 = epilogue only waits/arrives, 2 = MMA issue without TMA
+#endif
   // recall
   const uint32_t* bitmaps;
   int words_per_group;
   const int32_t* query_group;
   int32_t* cand_keys;
   int64_t keys_per_query;
+  EmitView ev;     // emission mode
+  unsigned long long* timer;  // nullable: [0] = earliest CTA start, [1] = latest CTA end (%globaltimer, ns)
   // self-join
   PairEpilogue pe;
 };
+
+// Debug builds (-DOMR_UMMA_EXPERIMENTS) can switch parts of the kernel off and shorten the TMA ring from
+// the environment; the shipped build has neither the knobs nor the branches.
+#ifdef OMR_UMMA_EXPERIMENTS
+#define OMR_EXP(args, bit) ((args).exp & (bit))
+#define OMR_NSTAGES(args) ((args).n_stages)
+#else
+#define OMR_EXP(args, bit) 0
+#define OMR_NSTAGES(args) kStages
+#endif
 
 // Work item -> (A tile of 128, B tile of 256); false = nothing to do for this item.
 // Recall: a-tile fastest, so the CTAs that run concurrently share B tiles through L2.
@@ -195,10 +351,11 @@ __device__ __forceinline__ bool decode_work(int64_t w, int n_a_tiles, int n_b_ti
   }
 }
 
-template <bool kSelfJoin, int S>
+template <int kEpi, int S>
 __global__ void __launch_bounds__(kNumThreads, 1)
     score_umma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
-                      const KernelArgs<kSelfJoin, S> args) {
+                      const KernelArgs<kEpi, S> args) {
+  constexpr bool kSelfJoin = kEpi == kEpiPairs;
   extern __shared__ uint8_t smem_raw[];
   // SWIZZLE_128B tiles must start on a 1024-byte boundary.
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -206,9 +363,18 @@ __global__ void __launch_bounds__(kNumThreads, 1)
   uint8_t* smem_b = smem + kStages * kABytes;
   PipeBarriers* bars = reinterpret_cast<PipeBarriers*>(smem + kStages * kStageBytes);
   PairStage* pstage = reinterpret_cast<PairStage*>(reinterpret_cast<uint8_t*>(bars) + ((sizeof(PipeBarriers) + 15) & ~size_t(15)));
+  RefreshQueue* rq = reinterpret_cast<RefreshQueue*>(pstage);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   if (kSelfJoin && threadIdx.x == 0) pstage->count = 0;
+  if (args.timer && threadIdx.x == 0) atomicMin(args.timer, ptx::globaltimer());
+  if (kEpi == kEpiEmit) {
+    if (threadIdx.x < kRefreshSlots) rq->slot[threadIdx.x] = 0u;
+    if (threadIdx.x == 0) {
+      rq->tail = 0u;
+      rq->epi_done = 0u;
+    }
+  }
 
   if (warp == 0 && lane == 0) {
     ptx::tma_prefetch_desc(&tmap_a);
@@ -233,7 +399,7 @@ __global__ void __launch_bounds__(kNumThreads, 1)
 
   if (warp == 0) {
     // ---------------- TMA producer ----------------
-    if (lane == 0 && !(args.exp & 2)) {
+    if (lane == 0 && !OMR_EXP(args, 2)) {
       int stage = 0;
       uint32_t phase = 0;
       for (int64_t w = blockIdx.x; w < args.n_work; w += gridDim.x) {
@@ -248,7 +414,7 @@ __global__ void __launch_bounds__(kNumThreads, 1)
                            a_tile * kQueryTile, ptx::kEvictLast);
           ptx::tma_load_2d(smem_b + stage * kBBytes, &tmap_b, &bars->full[stage], kb * kBlockK,
                            b_tile * kTileRows, kSelfJoin ? ptx::kEvictLast : ptx::kEvictNormal);
-          if (++stage == args.n_stages) {
+          if (++stage == OMR_NSTAGES(args)) {
             stage = 0;
             phase ^= 1;
           }
@@ -272,7 +438,7 @@ __global__ void __launch_bounds__(kNumThreads, 1)
       ptx::mbar_wait(&bars->tmem_empty[as], aphase ^ 1);
       ptx::tc_fence_after_sync();
       for (int kb = 0; kb < args.k_blocks; kb++) {
-        if (!(args.exp & 2)) ptx::mbar_wait(&bars->full[stage], phase);
+        if (!OMR_EXP(args, 2)) ptx::mbar_wait(&bars->full[stage], phase);
         ptx::tc_fence_after_sync();
         if (lane == 0) {
           const uint64_t da = ptx::make_smem_desc_sw128(ptx::smem_u32(smem_a + stage * kABytes));
@@ -280,16 +446,19 @@ __global__ void __launch_bounds__(kNumThreads, 1)
 #pragma unroll
           for (int k = 0; k < kBlockK / 16; k++)
             ptx::umma_bf16(tmem_base + as * kTileRows, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
-          if (!(args.exp & 2)) ptx::umma_commit(&bars->empty[stage]);  // frees the smem stage when these MMAs retire
+          if (!OMR_EXP(args, 2)) ptx::umma_commit(&bars->empty[stage]);  // frees the smem stage when these MMAs retire
           if (kb == args.k_blocks - 1) ptx::umma_commit(&bars->tmem_full[as]);
         }
         __syncwarp();
-        if (++stage == args.n_stages) {
+        if (++stage == OMR_NSTAGES(args)) {
           stage = 0;
           phase ^= 1;
         }
       }
     }
+  } else if (kEpi == kEpiEmit && warp == 3) {
+    // ---------------- threshold refresh ----------------
+    refresh_loop(args.ev, rq, lane);
   } else if (warp >= kEpilogueWarp0) {
     // ---------------- epilogue ----------------
     const int quarter = warp & 3;  // TMEM lanes [32*quarter, 32*quarter+32) are this warp's
@@ -297,6 +466,9 @@ __global__ void __launch_bounds__(kNumThreads, 1)
     const uint32_t lane_addr = tmem_base + ((uint32_t)(quarter * 32) << 16);
     uint32_t it = 0;
     Top2Epilogue<S> te;
+    EmitEpilogue ee;
+    ee.ev = args.ev;
+    ee.rq = rq;
     PairEpilogue pe = args.pe;
     pe.stage = pstage;
     for (int64_t w = blockIdx.x; w < args.n_work; w += gridDim.x) {
@@ -309,9 +481,14 @@ __global__ void __launch_bounds__(kNumThreads, 1)
       if (!kSelfJoin) {
         const int q = a_tile * kQueryTile + t_local;
         const int g = (args.query_group && q < args.nq) ? __ldg(args.query_group + q) : 0;
-        te.bitmap_row = args.bitmaps + (int64_t)g * args.words_per_group;
-        te.out = args.cand_keys + (int64_t)q * args.keys_per_query;
-        te.begin_tile();
+        if (kEpi == kEpiEmit) {
+          ee.bitmap_row = args.bitmaps + (int64_t)g * args.words_per_group;
+          ee.begin_tile(q);
+        } else {
+          te.bitmap_row = args.bitmaps + (int64_t)g * args.words_per_group;
+          te.out = args.cand_keys + (int64_t)q * args.keys_per_query;
+          te.begin_tile();
+        }
       } else {
         pe.row_a = a_tile * kQueryTile + t_local;
         pe.a_member = (__ldg(pe.member + (pe.row_a >> 5)) >> (pe.row_a & 31)) & 1u;
@@ -319,13 +496,16 @@ __global__ void __launch_bounds__(kNumThreads, 1)
       ptx::mbar_wait(&bars->tmem_full[as], aphase);
       ptx::tc_fence_after_sync();
 #pragma unroll 1
-      for (int c = 0; c < ((args.exp & 1) ? 0 : kTileRows / 32); c += 2) {
+      for (int c = 0; c < (OMR_EXP(args, 1) ? 0 : kTileRows / 32); c += 2) {
         uint32_t v0[32], v1[32];
         __syncwarp();  // the epilogue's data-dependent branches must reconverge before a .sync.aligned load
         ptx::tmem_ld_32x32(lane_addr + as * kTileRows + c * 32, v0);
         ptx::tmem_ld_32x32(lane_addr + as * kTileRows + (c + 1) * 32, v1);
         ptx::tmem_ld_wait();
-        if (!kSelfJoin) {
+        if (kEpi == kEpiEmit) {
+          ee.chunk(b_tile, c, v0);
+          ee.chunk(b_tile, c + 1, v1);
+        } else if (!kSelfJoin) {
           te.chunk(b_tile, c, v0);
           te.chunk(b_tile, c + 1, v1);
         } else {
@@ -337,11 +517,16 @@ __global__ void __launch_bounds__(kNumThreads, 1)
       ptx::mbar_arrive(&bars->tmem_empty[as]);
       if (kSelfJoin) pe.flush(t_local);
     }
+    if (kEpi == kEpiEmit) {
+      __syncwarp();
+      if (lane == 0) atomicAdd(&rq->epi_done, 1u);
+    }
   }
 
   ptx::tc_fence_before_sync();
   __syncthreads();
   if (warp == 2) ptx::tmem_dealloc(tmem_base, kTmemCols);
+  if (args.timer && threadIdx.x == 0) atomicMax(args.timer + 1, ptx::globaltimer());
 }
 
 // ---------------------------------------------------------------------------------------
@@ -365,8 +550,28 @@ constexpr int kSmemBytes2 = kStages2 * kStageBytes2 + (int)sizeof(PipeBarriers2)
 // Work item of the pair kernel -> (A tile of 256 rows, B tile of 256 rows).  Self-join: super-blocks of
 // sb x sb tiles over the upper triangle, as decode_work, at 256-row granularity on both sides.
 template <bool kSelfJoin>
-__device__ __forceinline__ bool decode_work2(int64_t w, int n_a_tiles, int n_b_tiles, int sb, int& a_tile, int& b_tile) {
+__device__ __forceinline__ bool decode_work2(int64_t w, int n_a_tiles, int n_b_tiles, int sb, int64_t n_clusters,
+                                             int& a_tile, int& b_tile) {
   if (!kSelfJoin) {
+    if (sb & 1) {
+      // Row-tile-major: round r of cluster c takes row tile c + r * n_clusters and walks every query tile on it,
+      // so a row tile is fetched from HBM once and re-read from L2 by the SAME cluster a few microseconds later
+      // (ncu, 1M x 1536, 1024 queries: DRAM read 3.22 GB = 1.05 x the matrix, against 3.7-4.5 GB when the four
+      // clusters that share a row tile are different ones; the kernel's time is the same, it is power-bound).
+      // The last, partial round of row tiles is dealt out item by item so that no cluster idles.
+      const int64_t i = w / n_clusters, c = w % n_clusters;
+      const int64_t full = n_b_tiles / n_clusters;
+      if (i < full * n_a_tiles) {
+        b_tile = (int)(c + n_clusters * (i / n_a_tiles));
+        a_tile = (int)(i % n_a_tiles);
+        return true;
+      }
+      const int64_t ww = full * n_clusters * n_a_tiles + c + (i - full * n_a_tiles) * n_clusters;
+      if (ww >= (int64_t)n_a_tiles * n_b_tiles) return false;
+      b_tile = (int)(ww / n_a_tiles);
+      a_tile = (int)(ww % n_a_tiles);
+      return true;
+    }
     b_tile = (int)(w / n_a_tiles);
     a_tile = (int)(w % n_a_tiles);
     return true;
@@ -384,19 +589,29 @@ __device__ __forceinline__ bool decode_work2(int64_t w, int n_a_tiles, int n_b_t
   }
 }
 
-template <bool kSelfJoin, int S>
+template <int kEpi, int S>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kNumThreads, 1)
     score_umma2_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_rows,
-                       const KernelArgs<kSelfJoin, S> args) {
+                       const KernelArgs<kEpi, S> args) {
+  constexpr bool kSelfJoin = kEpi == kEpiPairs;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* smem_a = smem;
   uint8_t* smem_b = smem + kStages2 * kABytes;
   PipeBarriers2* bars = reinterpret_cast<PipeBarriers2*>(smem + kStages2 * kStageBytes2);
   PairStage* pstage = reinterpret_cast<PairStage*>(reinterpret_cast<uint8_t*>(bars) + ((sizeof(PipeBarriers2) + 15) & ~size_t(15)));
+  RefreshQueue* rq = reinterpret_cast<RefreshQueue*>(pstage);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   if (kSelfJoin && threadIdx.x == 0) pstage->count = 0;
+  if (args.timer && threadIdx.x == 0) atomicMin(args.timer, ptx::globaltimer());
+  if (kEpi == kEpiEmit) {
+    if (threadIdx.x < kRefreshSlots) rq->slot[threadIdx.x] = 0u;
+    if (threadIdx.x == 0) {
+      rq->tail = 0u;
+      rq->epi_done = 0u;
+    }
+  }
   const uint32_t rank = ptx::cluster_ctarank();
   const bool leader = rank == 0;
   const int64_t cluster = ptx::cluster_id_x(), n_clusters = ptx::cluster_nctaid_x();
@@ -430,8 +645,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kNumThreads, 1)
       uint32_t phase = 0;
       for (int64_t w = cluster; w < args.n_work; w += n_clusters) {
         int a_tile, b_tile;
-        if (!decode_work2<kSelfJoin>(args.work_first + w * args.work_step, args.n_a_tiles, args.n_b_tiles, args.sb, a_tile,
-                                     b_tile))
+        if (!decode_work2<kSelfJoin>(args.work_first + w * args.work_step, args.n_a_tiles, args.n_b_tiles, args.sb, n_clusters,
+                                     a_tile, b_tile))
           continue;
         for (int kb = 0; kb < args.k_blocks; kb++) {
           ptx::mbar_wait(&bars->empty[stage], phase ^ 1);
@@ -455,9 +670,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kNumThreads, 1)
     int stage = 0;
     uint32_t phase = 0, it = 0;
     for (int64_t w = cluster; w < args.n_work; w += n_clusters) {
-      if (kSelfJoin) {
+      if (kSelfJoin || (args.sb & 1)) {
         int ta, tb;
-        if (!decode_work2<kSelfJoin>(args.work_first + w * args.work_step, args.n_a_tiles, args.n_b_tiles, args.sb, ta, tb))
+        if (!decode_work2<kSelfJoin>(args.work_first + w * args.work_step, args.n_a_tiles, args.n_b_tiles, args.sb, n_clusters, ta, tb))
           continue;
       }
       const uint32_t as = it & 1, aphase = (it >> 1) & 1;
@@ -483,6 +698,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kNumThreads, 1)
         }
       }
     }
+  } else if (kEpi == kEpiEmit && warp == 3) {
+    // ---------------- threshold refresh (one warp per CTA) ----------------
+    refresh_loop(args.ev, rq, lane);
   } else if (warp >= kEpilogueWarp0) {
     // ---------------- epilogue (both CTAs, own TMEM lanes) ----------------
     const int quarter = warp & 3;
@@ -490,21 +708,29 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kNumThreads, 1)
     const uint32_t lane_addr = tmem_base + ((uint32_t)(quarter * 32) << 16);
     uint32_t it = 0;
     Top2Epilogue<S> te;
+    EmitEpilogue ee;
+    ee.ev = args.ev;
+    ee.rq = rq;
     PairEpilogue pe = args.pe;
     pe.stage = pstage;
     for (int64_t w = cluster; w < args.n_work; w += n_clusters) {
       int a_tile, b_tile;
-      if (!decode_work2<kSelfJoin>(args.work_first + w * args.work_step, args.n_a_tiles, args.n_b_tiles, args.sb, a_tile,
-                                   b_tile))
+      if (!decode_work2<kSelfJoin>(args.work_first + w * args.work_step, args.n_a_tiles, args.n_b_tiles, args.sb, n_clusters,
+                                   a_tile, b_tile))
         continue;
       const uint32_t as = it & 1, aphase = (it >> 1) & 1;
       it++;
       const int q = a_tile * 2 * kQueryTile + (int)rank * kQueryTile + t_local;
       if (!kSelfJoin) {
         const int g = (args.query_group && q < args.nq) ? __ldg(args.query_group + q) : 0;
-        te.bitmap_row = args.bitmaps + (int64_t)g * args.words_per_group;
-        te.out = args.cand_keys + (int64_t)q * args.keys_per_query;
-        te.begin_tile();
+        if (kEpi == kEpiEmit) {
+          ee.bitmap_row = args.bitmaps + (int64_t)g * args.words_per_group;
+          ee.begin_tile(q);
+        } else {
+          te.bitmap_row = args.bitmaps + (int64_t)g * args.words_per_group;
+          te.out = args.cand_keys + (int64_t)q * args.keys_per_query;
+          te.begin_tile();
+        }
       } else {
         pe.row_a = q;
         pe.a_member = (__ldg(pe.member + (pe.row_a >> 5)) >> (pe.row_a & 31)) & 1u;
@@ -518,7 +744,10 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kNumThreads, 1)
         ptx::tmem_ld_32x32(lane_addr + as * kTileRows + c * 32, v0);
         ptx::tmem_ld_32x32(lane_addr + as * kTileRows + (c + 1) * 32, v1);
         ptx::tmem_ld_wait();
-        if (!kSelfJoin) {
+        if (kEpi == kEpiEmit) {
+          ee.chunk(b_tile, c, v0);
+          ee.chunk(b_tile, c + 1, v1);
+        } else if (!kSelfJoin) {
           te.chunk(b_tile, c, v0);
           te.chunk(b_tile, c + 1, v1);
         } else {
@@ -530,18 +759,23 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kNumThreads, 1)
       ptx::mbar_arrive_cluster(&bars->tmem_empty[as], 0);
       if (kSelfJoin) pe.flush(t_local);
     }
+    if (kEpi == kEpiEmit) {
+      __syncwarp();
+      if (lane == 0) atomicAdd(&rq->epi_done, 1u);
+    }
   }
 
   ptx::tc_fence_before_sync();
   ptx::cluster_sync_all();
   if (warp == 2) ptx::tmem_dealloc_2sm(tmem_base, kTmemCols);
+  if (args.timer && threadIdx.x == 0) atomicMax(args.timer + 1, ptx::globaltimer());
 }
 
 template <int S>
 int launch_recall2_s(const CUtensorMap& tmap_q, const CUtensorMap& tmap_rows_half, int nq, int n_qtiles256, int n_tiles,
                      int k_blocks, const uint32_t* bitmaps, int words_per_group, const int32_t* query_group,
                      int32_t* cand_keys, int num_sms, cudaStream_t st) {
-  KernelArgs<false, S> a{};
+  KernelArgs<kEpiTop2, S> a{};
   a.n_a_tiles = n_qtiles256;
   a.n_b_tiles = n_tiles;
   a.n_work = (int64_t)n_qtiles256 * n_tiles;
@@ -554,7 +788,8 @@ int launch_recall2_s(const CUtensorMap& tmap_q, const CUtensorMap& tmap_rows_hal
   a.query_group = query_group;
   a.cand_keys = cand_keys;
   a.keys_per_query = (int64_t)n_tiles * (kTileRows / S) * 2;
-  auto kern = score_umma2_kernel<false, S>;
+  a.sb = 1;      // row-tile-major order (decode_work2)
+  auto kern = score_umma2_kernel<kEpiTop2, S>;
   OMR_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes2));
   int64_t clusters = num_sms / 2;
   if (clusters > a.n_work) clusters = a.n_work;
@@ -567,7 +802,7 @@ template <int S>
 int launch_recall_s(const CUtensorMap& tmap_q, const CUtensorMap& tmap_rows, int nq, int n_qtiles, int n_tiles, int k_blocks,
                     const uint32_t* bitmaps, int words_per_group, const int32_t* query_group, int32_t* cand_keys,
                     int num_sms, cudaStream_t st) {
-  KernelArgs<false, S> a{};
+  KernelArgs<kEpiTop2, S> a{};
   a.n_a_tiles = n_qtiles;
   a.n_b_tiles = n_tiles;
   a.n_work = (int64_t)n_qtiles * n_tiles;
@@ -580,11 +815,13 @@ int launch_recall_s(const CUtensorMap& tmap_q, const CUtensorMap& tmap_rows, int
   a.query_group = query_group;
   a.cand_keys = cand_keys;
   a.keys_per_query = (int64_t)n_tiles * (kTileRows / S) * 2;
+#ifdef OMR_UMMA_EXPERIMENTS
   a.n_stages = kStages;
   a.exp = 0;
   if (const char* e = getenv("OMR_UMMA_EXP")) a.exp = atoi(e);
   if (const char* e = getenv("OMR_UMMA_STAGES")) a.n_stages = std::max(2, std::min(kStages, atoi(e)));
-  auto kern = score_umma_kernel<false, S>;
+#endif
+  auto kern = score_umma_kernel<kEpiTop2, S>;
   OMR_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
   int grid = num_sms;
   if ((int64_t)grid > a.n_work) grid = (int)a.n_work;
@@ -594,6 +831,65 @@ int launch_recall_s(const CUtensorMap& tmap_q, const CUtensorMap& tmap_rows, int
 }
 
 }  // namespace
+
+int launch_score_umma_emit(const CUtensorMap& tmap_q, const CUtensorMap& tmap_rows, int nq, int n_qtiles, int n_tiles,
+                           int k_blocks, const uint32_t* bitmaps, int words_per_group, const int32_t* query_group,
+                           const EmitView& ev, unsigned long long* timer, int num_sms, cudaStream_t st) {
+  if (n_qtiles <= 0 || n_tiles <= 0) return 0;
+  KernelArgs<kEpiEmit, 256> a{};
+  a.n_a_tiles = n_qtiles;
+  a.n_b_tiles = n_tiles;
+  a.n_work = (int64_t)n_qtiles * n_tiles;
+  a.work_first = 0;
+  a.work_step = 1;
+  a.k_blocks = k_blocks;
+  a.nq = nq;
+  a.bitmaps = bitmaps;
+  a.words_per_group = words_per_group;
+  a.query_group = query_group;
+  a.ev = ev;
+  a.timer = timer;
+#ifdef OMR_UMMA_EXPERIMENTS
+  a.n_stages = kStages;
+  a.exp = 0;
+  if (const char* e = getenv("OMR_UMMA_EXP")) a.exp = atoi(e);
+#endif
+  auto kern = score_umma_kernel<kEpiEmit, 256>;
+  OMR_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+  int grid = num_sms;
+  if ((int64_t)grid > a.n_work) grid = (int)a.n_work;
+  kern<<<grid, kNumThreads, kSmemBytes, st>>>(tmap_q, tmap_rows, a);
+  OMR_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+int launch_score_umma2_emit(const CUtensorMap& tmap_q, const CUtensorMap& tmap_rows_half, int nq, int n_qtiles256,
+                            int n_tiles, int k_blocks, const uint32_t* bitmaps, int words_per_group,
+                            const int32_t* query_group, const EmitView& ev, unsigned long long* timer, int num_sms,
+                            cudaStream_t st) {
+  if (n_qtiles256 <= 0 || n_tiles <= 0) return 0;
+  KernelArgs<kEpiEmit, 256> a{};
+  a.n_a_tiles = n_qtiles256;
+  a.n_b_tiles = n_tiles;
+  a.n_work = (int64_t)n_qtiles256 * n_tiles;
+  a.work_first = 0;
+  a.work_step = 1;
+  a.k_blocks = k_blocks;
+  a.nq = nq;
+  a.bitmaps = bitmaps;
+  a.words_per_group = words_per_group;
+  a.query_group = query_group;
+  a.ev = ev;
+  a.sb = 1;      // row-tile-major order (decode_work2)
+  a.timer = timer;
+  auto kern = score_umma2_kernel<kEpiEmit, 256>;
+  OMR_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes2));
+  int64_t clusters = num_sms / 2;
+  if (clusters > a.n_work) clusters = a.n_work;
+  kern<<<(unsigned)(2 * clusters), kNumThreads, kSmemBytes2, st>>>(tmap_q, tmap_rows_half, a);
+  OMR_CUDA_OK(cudaGetLastError());
+  return 0;
+}
 
 int score_umma_smem_bytes() { return kSmemBytes; }
 
@@ -631,7 +927,7 @@ int launch_selfjoin_umma2(const CUtensorMap& tmap_half, int64_t n, int k_blocks,
                           unsigned long long* pair_count, int num_sms, cudaStream_t st) {
   if (n <= 0) return 0;
   const int64_t nb = (n + kTileRows - 1) / kTileRows;
-  KernelArgs<true, 256> a{};
+  KernelArgs<kEpiPairs, 256> a{};
   a.n_a_tiles = (int)nb;
   a.n_b_tiles = (int)nb;
   int sb = 24;
@@ -651,7 +947,7 @@ int launch_selfjoin_umma2(const CUtensorMap& tmap_half, int64_t n, int k_blocks,
   a.pe.cap = cap;
   a.pe.count = pair_count;
   a.pe.threshold = threshold;
-  auto kern = score_umma2_kernel<true, 256>;
+  auto kern = score_umma2_kernel<kEpiPairs, 256>;
   OMR_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes2));
   int64_t clusters = num_sms / 2;
   if (clusters > a.n_work) clusters = a.n_work;
@@ -665,7 +961,7 @@ int launch_selfjoin_umma(const CUtensorMap& tmap_a, const CUtensorMap& tmap_b, i
                          unsigned long long* pair_count, int num_sms, cudaStream_t st) {
   if (n <= 0) return 0;
   const int64_t nb = (n + kTileRows - 1) / kTileRows;
-  KernelArgs<true, 256> a{};
+  KernelArgs<kEpiPairs, 256> a{};
   a.n_a_tiles = (int)(2 * nb);
   a.n_b_tiles = (int)nb;
   // super-block edge: two row blocks of sb * 256 rows must sit in L2 together (126 MB, two dies); 24 tiles =
@@ -687,9 +983,11 @@ int launch_selfjoin_umma(const CUtensorMap& tmap_a, const CUtensorMap& tmap_b, i
   a.pe.cap = cap;
   a.pe.count = pair_count;
   a.pe.threshold = threshold;
+#ifdef OMR_UMMA_EXPERIMENTS
   a.n_stages = kStages;
   a.exp = 0;
-  auto kern = score_umma_kernel<true, 256>;
+#endif
+  auto kern = score_umma_kernel<kEpiPairs, 256>;
   OMR_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
   int grid = num_sms;
   if ((int64_t)grid > a.n_work) grid = (int)a.n_work;

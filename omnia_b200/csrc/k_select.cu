@@ -345,9 +345,18 @@ __global__ void __launch_bounds__(256) exact_scan_kernel(ShardView sh, const flo
     const int b = __ffs(bits) - 1;
     bits &= bits - 1;
     const int64_t row = row0 + b;
-    const float* m = sh.rows_f32 + row * sh.pitch;
+    // same summation order as the rescore of the candidate paths (k_post.cu exact_distance2: lane-strided
+    // float4, x y z w in turn, xor-shuffle reduction), so a query gets the same bits whichever path answers it
+    const float4* m4 = reinterpret_cast<const float4*>(sh.rows_f32 + row * sh.pitch);
     double dot = 0.0;
-    for (int i = lane; i < sh.dim; i += 32) dot += (double)qv[i] * (double)m[i];
+    for (int i = lane; i < (sh.pitch >> 2); i += 32) {
+      const float4 a = __ldg(m4 + i);
+      const int e = 4 * i;
+      dot = fma((double)a.x, e < sh.dim ? (double)qv[e] : 0.0, dot);
+      dot = fma((double)a.y, e + 1 < sh.dim ? (double)qv[e + 1] : 0.0, dot);
+      dot = fma((double)a.z, e + 2 < sh.dim ? (double)qv[e + 2] : 0.0, dot);
+      dot = fma((double)a.w, e + 3 < sh.dim ? (double)qv[e + 3] : 0.0, dot);
+    }
     dot = warp_sum_d(dot);
     if (lane == 0) {
       const double d = 1.0 - clamp_sim(dot / sqrt(qn * sh.norm2[row]));

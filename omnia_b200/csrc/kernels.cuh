@@ -30,6 +30,61 @@ int launch_score_umma2(const CUtensorMap& tmap_q, const CUtensorMap& tmap_rows_h
                        const int32_t* query_group, int32_t* cand_keys, int num_sms, cudaStream_t st);
 int score_umma_smem_bytes();
 
+// ---- threshold-filtered candidate emission (tensor-core scorers, k <= 256) ----------
+// Instead of two keys per (query, sub-bucket) the scorer appends to a short per-query list every
+// eligible row whose approximate score clears a per-query threshold that only ever rises:
+//   thr[q]   = (a lower bound of the k-th best approximate score of query q) - band, stored as its
+//              order-preserving int32 image and raised with atomicMax;
+//   list[q]  = (biased score << 32 | row) entries, 0 = slot reserved but not written yet;
+//   count[q] = entries appended (beyond `cap` the query is answered by the exact scan).
+// band = 2 * margin: a row of the exact top-k scores at least T - 2*margin approximately (T = the k-th best
+// approximate score), so a threshold that never exceeds T - band never drops an answer row.
+struct EmitView {
+  int32_t* thr = nullptr;
+  unsigned int* count = nullptr;
+  unsigned long long* list = nullptr;
+  int cap = 0;      // entries per query
+  int k = 0;
+  int trigger = 32; // power of two: a threshold refresh is requested every `trigger` appended entries
+  float band = 0.0f;
+};
+// Seeds thr[] from the top-2-per-32-row keys of the first `seed_tiles` row tiles and zeroes count[].
+// Queries q >= nq (tile padding) and zero-norm queries get a threshold nothing clears.
+int launch_emit_seed(const int32_t* seed_keys, int64_t keys_per_query, const double* qnorm2, int nq, int qpad,
+                     const EmitView& ev, cudaStream_t st);
+int launch_score_umma_emit(const CUtensorMap& tmap_q, const CUtensorMap& tmap_rows, int nq, int n_qtiles, int n_tiles,
+                           int k_blocks, const uint32_t* bitmaps, int words_per_group, const int32_t* query_group,
+                           const EmitView& ev, unsigned long long* timer, int num_sms, cudaStream_t st);
+int launch_score_umma2_emit(const CUtensorMap& tmap_q, const CUtensorMap& tmap_rows_half, int nq, int n_qtiles256,
+                            int n_tiles, int k_blocks, const uint32_t* bitmaps, int words_per_group,
+                            const int32_t* query_group, const EmitView& ev, unsigned long long* timer, int num_sms,
+                            cudaStream_t st);
+// `timer` (nullable, device): [0] receives the earliest CTA start and [1] the latest CTA end of the launch in
+// %globaltimer nanoseconds ([0] must start at ~0ull, [1] at 0): the kernel's own duration even when it queued
+// behind another batch's kernels, which stream events around it cannot tell apart.
+// Per query: keep the list entries within `band` of the k-th best approximate score, rescore them exactly
+// from the fp32 master (best K2 first, then whatever the exact k-th distance found so far still allows),
+// ORDER BY distance LIMIT k with the cutoff, and clear the list for the lane's next batch (k_emit.cu).
+struct EmitPostArgs {
+  ShardView sh;
+  const float* q = nullptr;
+  const double* qnorm2 = nullptr;
+  EmitView ev;
+  int nq = 0, k = 10, K2 = 16;
+  const double* max_dist = nullptr;
+  float margin = 0.0f;
+  int64_t row_base = 0, row_stride = 1;
+  int64_t* out_rows = nullptr;
+  double* out_dist = nullptr;
+  int32_t* out_count = nullptr;
+  int32_t* fail_list = nullptr;
+  int32_t* fail_count = nullptr;
+  int32_t* rescued_total = nullptr;  // rows rescored in the second round
+  int32_t* listed_total = nullptr;   // list entries consumed (diagnostics)
+};
+bool emit_supported(int k);
+int launch_emit_post(const EmitPostArgs& a, cudaStream_t st);
+
 // ---- select / exact rescore / finalize (k_select.cu) -------------------------
 // Candidate slots of a query are sel_rows/sel_dist[q][K2x]: the first K2 hold the keys
 // select_keys picked, the remaining K2x - K2 are "extra" slots that finalize pass 1 fills

@@ -154,7 +154,7 @@ struct omr_store {
   omr_config cfg{};
   int dim = 0, pitch = 0, num_sms = 148;
   int64_t cap = 0, n = 0;
-  float margin = 1e-3f;
+  float margin = 4.5e-3f;
   std::mutex mu;
   cudaStream_t stream = nullptr;
   EncodeTiledFn encode = nullptr;
@@ -190,14 +190,21 @@ struct omr_store {
     DevBuf<__nv_bfloat16> qn;
     DevBuf<double> qnorm2;
     DevBuf<int32_t> cand, fail_list, counters, extra_cnt;
+    // emission mode (tensor-core scorers, k <= 256): per-query thresholds, counts and candidate lists
+    DevBuf<int32_t> ethr, seed_keys;
+    DevBuf<unsigned int> ecount;
+    DevBuf<unsigned long long> elist;
+    bool elist_dirty = true;   // a batch was enqueued past the scorer without its post kernel: lists may hold entries
     DevBuf<long long> timing;
+    DevBuf<unsigned long long> ktimer;
     PinBuf<int32_t> pin;
     CUtensorMap tmap_q{};
     size_t tmap_q_rows = 0;
     const void* tmap_q_ptr = nullptr;
     cudaStream_t stream = nullptr;
     cudaEvent_t ev_in = nullptr, ev_done = nullptr, ev0 = nullptr, ev1 = nullptr;
-    bool busy = false, immediate = false, timed = false;
+    cudaEvent_t ph[3] = {nullptr, nullptr, nullptr};   // profiling: before the seed pass, after it, after the post kernel
+    bool busy = false, immediate = false, timed = false, phased = false;
     // the batch in flight
     const float* d_q = nullptr;
     const uint32_t* d_bitmaps = nullptr;
@@ -237,7 +244,7 @@ struct omr_store {
   bool post_timing = false;  // OMR_POST_TIMING=1: per-phase clock stamps of the fused post kernel
   bool legacy_post = false;  // OMR_LEGACY_POST=1: use the unfused select/rescore/finalize chain
 
-  std::atomic<int64_t> st_launches{0}, st_searches{0}, st_queries{0}, st_rescued{0}, st_fallback{0};
+  std::atomic<int64_t> st_launches{0}, st_searches{0}, st_queries{0}, st_rescued{0}, st_fallback{0}, st_listed{0};
   // Coalescing of concurrent host calls (dedup-on-write micro-batching): while one
   // search runs, the calls that arrive queue up and the next leader takes them all as ONE batch.
   struct HostReq {
@@ -262,8 +269,8 @@ struct omr_store {
   void run_batch(std::vector<HostReq*>& batch);
   // optional device timing of the dominant kernel (the approximate scorer), for bench.py's roofline
   bool profiling = false;
-  double scorer_ms_sum = 0.0;
-  int64_t scorer_timed = 0;
+  double scorer_ms_sum = 0.0, phase_ms_sum[3] = {0.0, 0.0, 0.0}, kernel_ns_sum = 0.0;
+  int64_t scorer_timed = 0, kernel_ns_n = 0;
   int last_path = 0, last_S = 0, last_K2 = 0;
 
   int64_t words() const { return (cap / kTileRows) * 8; }
@@ -295,6 +302,7 @@ struct omr_store {
               const double* d_maxdist, int k, int64_t* d_rows, double* d_dist, int32_t* d_count, cudaStream_t st,
               bool* fused_out);
   int complete(Lane& L, cudaStream_t st);
+  int prepare_emit(Lane& L, int qpad, int k, int n_tiles, cudaStream_t st, EmitView* ev, int* seed_n, int64_t* seed_kpq);
   int drain();
   int host_search(const float* queries, int nq, const omr_filter* filters, int n_filters, const int32_t* query_filter,
                   int k, omr_hit* hits, int32_t* counts, int64_t* soa_rows = nullptr, double* soa_dist = nullptr);
@@ -343,8 +351,9 @@ int omr_store::open() {
     OMR_CUDA_OK(cudaEventCreateWithFlags(&L.ev_done, cudaEventDisableTiming));
     OMR_CUDA_OK(cudaEventCreate(&L.ev0));
     OMR_CUDA_OK(cudaEventCreate(&L.ev1));
-    if ((rc = L.pin.reserve(4))) return rc;
-    if ((rc = L.counters.reserve(4))) return rc;
+    for (cudaEvent_t& e : L.ph) OMR_CUDA_OK(cudaEventCreate(&e));
+    if ((rc = L.pin.reserve(8))) return rc;
+    if ((rc = L.counters.reserve(8))) return rc;
   }
   return 0;
 }
@@ -360,9 +369,10 @@ void omr_store::destroy() {
     L.xlocal.release(); L.xcount.release();
     L.hq.release(); L.hgroup.release(); L.hcount.release(); L.hmaxd.release(); L.hdist.release(); L.hrows.release();
     L.hbitmaps.release(); L.hfilters.release(); L.hin.release(); L.hout.release();
+    L.ethr.release(); L.seed_keys.release(); L.ecount.release(); L.elist.release(); L.ktimer.release();
     L.qn.release(); L.qnorm2.release(); L.cand.release(); L.fail_list.release(); L.counters.release();
     L.extra_cnt.release(); L.timing.release(); L.pin.release();
-    for (cudaEvent_t e : {L.ev_in, L.ev_done, L.ev0, L.ev1})
+    for (cudaEvent_t e : {L.ev_in, L.ev_done, L.ev0, L.ev1, L.ph[0], L.ph[1], L.ph[2]})
       if (e) cudaEventDestroy(e);
     if (L.stream) cudaStreamDestroy(L.stream);
   }
@@ -495,6 +505,35 @@ int omr_store::drain() {
   return 0;
 }
 
+// Emission-mode scratch of a lane: thresholds, counts, candidate lists and the seed keys.
+// Seed = top-2-per-32-row keys of the first row tiles (one wave of the scorer at most, at least enough tiles
+// for k keys, a sixteenth of a small store); they give every query its first threshold.
+int omr_store::prepare_emit(Lane& L, int qpad, int k, int n_tiles, cudaStream_t st, EmitView* out, int* seed_n,
+                            int64_t* seed_kpq) {
+  int rc;
+  EmitView ev;
+  ev.k = k;
+  ev.band = 2.0f * margin;
+  ev.cap = std::min(16384, std::max(2048, pow2ceil_i(48 * k)));
+  ev.trigger = std::max(32, pow2ceil_i(2 * k));
+  const int wave = std::max(1, num_sms / std::max(1, qpad / kQueryTile));
+  *seed_n = std::min(n_tiles, std::max((k + 7) / 8 + 1, std::min(std::min(20, wave), std::max(1, n_tiles / 16))));
+  *seed_kpq = (int64_t)*seed_n * (kTileRows / 32) * 2;
+  if ((rc = L.ethr.reserve((size_t)qpad))) return rc;
+  if ((rc = L.ecount.reserve((size_t)qpad))) return rc;
+  const size_t had = L.elist.n;
+  if ((rc = L.elist.reserve((size_t)qpad * ev.cap))) return rc;
+  if ((rc = L.seed_keys.reserve((size_t)qpad * *seed_kpq))) return rc;
+  if (L.elist.n != had || L.elist_dirty)   // fresh memory, or a batch that never reached its post kernel
+    OMR_CUDA_OK(cudaMemsetAsync(L.elist.p, 0, L.elist.n * sizeof(unsigned long long), st));
+  L.elist_dirty = true;
+  ev.thr = L.ethr.p;
+  ev.count = L.ecount.p;
+  ev.list = L.elist.p;
+  *out = ev;
+  return 0;
+}
+
 // Enqueues one batch on `st` up to (and including) the read-back of its counters; no host wait.
 int omr_store::enqueue(Lane& L, const float* d_q, int nq, const uint32_t* d_bitmaps, const int32_t* d_qgroup,
                        const double* d_maxdist, int k, int64_t* d_rows, double* d_dist, int32_t* d_count,
@@ -502,6 +541,7 @@ int omr_store::enqueue(Lane& L, const float* d_q, int nq, const uint32_t* d_bitm
   L.nq = 0;
   L.nfail_known = 0;
   L.timed = false;
+  L.phased = false;
   if (fused_out) *fused_out = true;
   if (nq <= 0) return 0;
   if (k <= 0 || k > 4096) return fail_msg(OMR_E_INVALID, "memory: k must be in 1..4096, got %d", k);
@@ -528,7 +568,10 @@ int omr_store::enqueue(Lane& L, const float* d_q, int nq, const uint32_t* d_bitm
   // Measured on B200 (profiles/r01_configs_single_gpu.jsonl): the TMA-fed tensor-core scorer streams the
   // matrix at ~6.7 TB/s for any batch up to ~128 queries, above the LDG-based streaming scorer for
   // every batch but a single query.
-  int path = cfg.force_path > 0 ? cfg.force_path : (nq <= 1 ? 1 : 2);
+  // One query: the bulk-copy streaming scorer.  Up to one query tile: the 1-CTA tensor-core scorer (HBM-bound
+  // there).  More: CTA pairs, whose lower L2->SM traffic per flop holds higher clocks under the power cap
+  // (profiles/r02_*: 466 k vs 439 k queries/s at 1M x 1536, 400 k vs 381 k sustained).
+  int path = cfg.force_path > 0 ? cfg.force_path : (nq <= 1 ? 1 : (nq <= kQueryTile ? 2 : 4));
   // Expected rescued rows per query ~ m^2 S^2 / (2n), m = rows whose approximate score clears the
   // certificate's threshold (the k answers plus those inside the margin; 2k allows for as many again).
   // When even the smallest sub-bucket cannot keep that small (large k on a small store), the two-stage
@@ -543,8 +586,15 @@ int omr_store::enqueue(Lane& L, const float* d_q, int nq, const uint32_t* d_bitm
   const int64_t kpq = (int64_t)n_tiles * (kTileRows / S) * 2;
   last_path = path; last_S = S; last_K2 = K2;
 
-  const bool fused = path != 3 && !legacy_post && post_fused_supported(K2, k);
+  // Tensor-core paths with k <= 256 run in emission mode: no key array at all, the scorer appends the rows that
+  // clear a per-query running threshold to a short list (k_score_umma.cu) and one kernel finishes from it.
+  const bool emit = (path == 2 || path == 4) && !legacy_post && emit_supported(k);
+  const bool fused = path != 3 && !legacy_post && (emit || post_fused_supported(K2, k));
   if (fused_out) *fused_out = fused;
+  EmitView ev;
+  int seed_n = 0;
+  int64_t seed_kpq = 0;
+  if (emit && (rc = prepare_emit(L, qpad, k, n_tiles, st, &ev, &seed_n, &seed_kpq))) return rc;
   if ((rc = L.qn.reserve((size_t)qpad * pitch))) return rc;
   if ((rc = L.qnorm2.reserve((size_t)qpad))) return rc;
   if ((rc = L.fail_list.reserve((size_t)qpad))) return rc;
@@ -555,7 +605,7 @@ int omr_store::enqueue(Lane& L, const float* d_q, int nq, const uint32_t* d_bitm
     if ((rc = w_sel_bound.reserve((size_t)qpad))) return rc;
     if ((rc = w_extra_items.reserve((size_t)qpad * kExtraSlots))) return rc;
   }
-  if (path != 3 && (rc = L.cand.reserve((size_t)qpad * kpq))) return rc;
+  if (path != 3 && !emit && (rc = L.cand.reserve((size_t)qpad * kpq))) return rc;
 
   OMR_CUDA_OK(cudaMemsetAsync(L.counters.p, 0, 4 * sizeof(int32_t), st));
   OMR_CUDA_OK(cudaMemsetAsync(L.extra_cnt.p, 0, (size_t)qpad * sizeof(int32_t), st));
@@ -606,7 +656,32 @@ int omr_store::enqueue(Lane& L, const float* d_q, int nq, const uint32_t* d_bitm
         L.tmap_q_ptr = L.qn.p;
         L.tmap_q_rows = L.qn.n / pitch;
       }
-      if (path == 4)
+      if (emit) {
+        if (profiling) OMR_CUDA_OK(cudaEventRecord(L.ph[0], st));
+        rc = launch_score_umma(L.tmap_q, tmap_rows_b, nq, qpad / kQueryTile, seed_n, pitch / kBlockK, 32, d_bitmaps, wpg,
+                               d_qgroup, L.seed_keys.p, num_sms, st);
+        if (rc) return rc;
+        if (profiling) OMR_CUDA_OK(cudaEventRecord(L.ph[1], st));
+        if ((rc = launch_emit_seed(L.seed_keys.p, seed_kpq, L.qnorm2.p, nq, qpad, ev, st))) return rc;
+        st_launches += 2;
+        unsigned long long* timer = nullptr;
+        if (profiling) {   // time the full-store scorer, not its seed: events on the stream and, since those also
+                           // count the time the kernel queued behind another batch, the kernel's own %globaltimer span
+          OMR_CUDA_OK(cudaEventRecord(L.ev0, st));
+          if ((rc = L.ktimer.reserve(2))) return rc;
+          OMR_CUDA_OK(cudaMemsetAsync(L.ktimer.p, 0xFF, 8, st));
+          OMR_CUDA_OK(cudaMemsetAsync(L.ktimer.p + 1, 0, 8, st));
+          timer = L.ktimer.p;
+        }
+        if (path == 4)
+          rc = launch_score_umma2_emit(L.tmap_q, tmap_rows_a, nq, qpad / (2 * kQueryTile), n_tiles, pitch / kBlockK,
+                                       d_bitmaps, wpg, d_qgroup, ev, timer, num_sms, st);
+        else
+          rc = launch_score_umma_emit(L.tmap_q, tmap_rows_b, nq, qpad / kQueryTile, n_tiles, pitch / kBlockK, d_bitmaps,
+                                      wpg, d_qgroup, ev, timer, num_sms, st);
+        if (!rc && timer)
+          OMR_CUDA_OK(cudaMemcpyAsync(L.pin.p + 4, L.ktimer.p, 16, cudaMemcpyDeviceToHost, st));
+      } else if (path == 4)
         rc = launch_score_umma2(L.tmap_q, tmap_rows_a, nq, qpad / (2 * kQueryTile), n_tiles, pitch / kBlockK, S, d_bitmaps, wpg,
                                 d_qgroup, L.cand.p, num_sms, st);
       else
@@ -616,7 +691,21 @@ int omr_store::enqueue(Lane& L, const float* d_q, int nq, const uint32_t* d_bitm
       st_launches++;
     }
     if (profiling) OMR_CUDA_OK(cudaEventRecord(L.ev1, st));
-    if (fused) {
+    if (emit) {
+      EmitPostArgs pa;
+      pa.sh = sh; pa.q = d_q; pa.qnorm2 = L.qnorm2.p; pa.ev = ev;
+      pa.nq = nq; pa.k = k; pa.K2 = cfg.rescore_width > 0 ? std::min(std::max(K2, k), 512) : std::max(16, k + 6);
+      pa.max_dist = d_maxdist; pa.margin = margin;
+      pa.row_base = cfg.row_base; pa.row_stride = cfg.row_stride;
+      pa.out_rows = d_rows; pa.out_dist = d_dist; pa.out_count = d_count;
+      pa.fail_list = L.fail_list.p; pa.fail_count = fail_count; pa.rescued_total = extra_total;
+      pa.listed_total = L.counters.p + 3;
+      if ((rc = launch_emit_post(pa, st))) return rc;
+      if (profiling) OMR_CUDA_OK(cudaEventRecord(L.ph[2], st));
+      L.phased = profiling;
+      st_launches += 1;
+      L.elist_dirty = false;
+    } else if (fused) {
       PostArgs pa;
       pa.sh = sh; pa.q = d_q; pa.qnorm2 = L.qnorm2.p; pa.cand_keys = L.cand.p; pa.keys_per_query = kpq;
       // the fused kernel tops its candidate list up adaptively, so its first pass can be narrow
@@ -644,7 +733,7 @@ int omr_store::enqueue(Lane& L, const float* d_q, int nq, const uint32_t* d_bitm
       if ((rc = launch_finalize_extra(fa, st))) return rc;
       st_launches += 5;
     }
-    OMR_CUDA_OK(cudaMemcpyAsync(L.pin.p, L.counters.p, 3 * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+    OMR_CUDA_OK(cudaMemcpyAsync(L.pin.p, L.counters.p, 4 * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
     L.timed = profiling;
   }
   return 0;
@@ -665,12 +754,26 @@ int omr_store::complete(Lane& L, cudaStream_t st) {
   if (L.pin.p[2] & 2) return fail_msg(OMR_E_INVALID, "memory: infinite value not allowed in vector");
   if (nfail < 0) {
     st_rescued += L.pin.p[0];
+    st_listed += L.pin.p[3];
     nfail = L.pin.p[1];
     if (L.timed) {
       float ms = 0.0f;
       OMR_CUDA_OK(cudaEventElapsedTime(&ms, L.ev0, L.ev1));
       scorer_ms_sum += ms;
       scorer_timed++;
+      if (L.phased) {   // seed pass | seed thresholds | (scorer, above) | post kernel
+        unsigned long long t01[2];
+        memcpy(t01, L.pin.p + 4, 16);
+        if (t01[1] > t01[0]) {
+          kernel_ns_sum += (double)(t01[1] - t01[0]);
+          kernel_ns_n++;
+        }
+        float a = 0, b = 0, c = 0;
+        OMR_CUDA_OK(cudaEventElapsedTime(&a, L.ph[0], L.ph[1]));
+        OMR_CUDA_OK(cudaEventElapsedTime(&b, L.ph[1], L.ev0));
+        OMR_CUDA_OK(cudaEventElapsedTime(&c, L.ev1, L.ph[2]));
+        phase_ms_sum[0] += a; phase_ms_sum[1] += b; phase_ms_sum[2] += c;
+      }
     }
   }
   L.nfail_seen = nfail;
@@ -951,7 +1054,8 @@ int omr_open(const omr_config* cfg, omr_store** out) {
     delete s;
     return fail_msg(OMR_E_CAPACITY, "memory: a shard holds at most 2^31 rows");
   }
-  s->margin = cfg->candidate_margin > 0 ? cfg->candidate_margin : 1e-3f;  // 4.5e-3 = deterministic bound, DESIGN.md section 3
+  // default: the deterministic error bound of the bf16 stage, valid for every dim <= 2048
+  s->margin = cfg->candidate_margin > 0 ? cfg->candidate_margin : 4.5e-3f;
   if (const char* e = getenv("OMR_LEGACY_POST")) s->legacy_post = e[0] == '1';
   if (const char* e = getenv("OMR_POST_TIMING")) s->post_timing = e[0] == '1';
   if (const char* e = getenv("OMR_STREAM_LDG")) g_force_ldg_stream = e[0] == '1';
@@ -2021,6 +2125,10 @@ int omr_get_stats(const omr_store* s, omr_stats* out) {
   out->host_batches = s->st_host_batches.load();
   out->scorer_ms_sum = s->scorer_ms_sum;
   out->scorer_timed = s->scorer_timed;
+  out->listed_entries = s->st_listed.load();
+  for (int i = 0; i < 3; i++) out->phase_ms_sum[i] = s->phase_ms_sum[i];
+  out->scorer_kernel_ms_sum = s->kernel_ns_sum * 1e-6;
+  out->scorer_kernel_timed = s->kernel_ns_n;
   return OMR_OK;
 }
 
@@ -2034,14 +2142,20 @@ int omr_debug_time_scorer(omr_store* s, int32_t nq, int32_t path, int32_t S, int
   omr_store::Lane& L = s->lanes[0];
   int rc;
   const int n_tiles = (int)((s->n + kTileRows - 1) / kTileRows);
-  const int64_t kpq = (int64_t)n_tiles * (kTileRows / S) * 2;
+  const bool emit = S == 0;   // emission mode (top-10 thresholds): seed pass + seed kernel + scorer per iteration
+  if (emit && path != 2 && path != 4) return fail_msg(OMR_E_INVALID, "memory: emission mode is a tensor-core path");
+  const int64_t kpq = emit ? 0 : (int64_t)n_tiles * (kTileRows / S) * 2;
   const int qtile = path == 4 ? 2 * kQueryTile : kQueryTile;
   const int qpad = path != 1 ? ((nq + qtile - 1) / qtile) * qtile : std::max(nq, 8);
   if ((rc = s->w_queries.reserve((size_t)nq * s->dim))) return rc;
   if ((rc = L.qn.reserve((size_t)qpad * s->pitch))) return rc;
   if ((rc = L.qnorm2.reserve((size_t)qpad))) return rc;
-  if ((rc = L.cand.reserve((size_t)qpad * kpq))) return rc;
+  if (!emit && (rc = L.cand.reserve((size_t)qpad * kpq))) return rc;
   if ((rc = s->ensure_live(st))) return rc;
+  EmitView ev;
+  int seed_n = 0;
+  int64_t seed_kpq = 0;
+  if (emit && (rc = s->prepare_emit(L, qpad, 10, n_tiles, st, &ev, &seed_n, &seed_kpq))) return rc;
   // queries = the store's own first rows (real data: all-zero operands would flatter the power-limited clocks)
   if (nq > s->n) return fail_msg(OMR_E_INVALID, "memory: omr_debug_time_scorer needs nq <= rows");
   OMR_CUDA_OK(cudaMemcpy2DAsync(s->w_queries.p, (size_t)s->dim * 4, s->d_f32, (size_t)s->pitch * 4, (size_t)s->dim * 4, nq,
@@ -2054,7 +2168,16 @@ int omr_debug_time_scorer(omr_store* s, int32_t nq, int32_t path, int32_t S, int
   }
   for (int it = -1; it < iters; it++) {
     if (it == 0) OMR_CUDA_OK(cudaEventRecord(L.ev0, st));
-    if (path == 4)
+    if (emit) {
+      rc = launch_score_umma(L.tmap_q, s->tmap_rows_b, nq, qpad / kQueryTile, seed_n, s->pitch / kBlockK, 32, s->w_live.p,
+                             (int)s->words(), nullptr, L.seed_keys.p, s->num_sms, st);
+      if (!rc) rc = launch_emit_seed(L.seed_keys.p, seed_kpq, L.qnorm2.p, nq, qpad, ev, st);
+      if (!rc)
+        rc = path == 4 ? launch_score_umma2_emit(L.tmap_q, s->tmap_rows_a, nq, qpad / (2 * kQueryTile), n_tiles,
+                                                 s->pitch / kBlockK, s->w_live.p, (int)s->words(), nullptr, ev, nullptr, s->num_sms, st)
+                       : launch_score_umma_emit(L.tmap_q, s->tmap_rows_b, nq, qpad / kQueryTile, n_tiles, s->pitch / kBlockK,
+                                                s->w_live.p, (int)s->words(), nullptr, ev, nullptr, s->num_sms, st);
+    } else if (path == 4)
       rc = launch_score_umma2(L.tmap_q, s->tmap_rows_a, nq, qpad / (2 * kQueryTile), n_tiles, s->pitch / kBlockK, S,
                               s->w_live.p, (int)s->words(), nullptr, L.cand.p, s->num_sms, st);
     else if (path == 2)
@@ -2088,6 +2211,9 @@ int omr_set_profiling(omr_store* s, int32_t on) {
   s->profiling = on != 0;
   s->scorer_ms_sum = 0.0;
   s->scorer_timed = 0;
+  for (double& v : s->phase_ms_sum) v = 0.0;
+  s->kernel_ns_sum = 0.0;
+  s->kernel_ns_n = 0;
   return OMR_OK;
 }
 

@@ -93,6 +93,37 @@ def clustered(n: int, dim: int, seed: int = CORPUS_SEED, topics: int = 6, varian
     return out
 
 
+def low_entropy(n: int, dim: int, seed: int = CORPUS_SEED, clusters: int = 16, per_cluster: int = 300
+                ) -> Tuple[np.ndarray, np.ndarray]:
+    """(v) vectors whose bf16 rounding errors are COHERENT: few-valued and constant rows in the style of the
+    reference's own test vectors (`repeatFloat(0.1, 1536)` and one-hot mixtures,
+    internal/memory/store_test.go:912-933).  Every element of a constant row rounds the same way, so the
+    approximate score of two such rows is off by up to ~2 * 2^-9 near cosine 1 instead of averaging out.
+    Layout: `clusters` centres (centre 0 is the constant 0.1 vector, the others are +-0.1 / +-0.2 sign
+    patterns); around each, `per_cluster` near-parallel members = centre * scale + a one-hot twist whose size
+    puts the member's cosine to the centre in [0.995, 0.9999]; the rest are few-valued background rows.
+    Members of one cluster are spread over consecutive rows AND far apart, so some share a sub-bucket.
+    Returns (corpus, queries): one query per centre (the centre itself with a small one-hot twist)."""
+    rng = np.random.default_rng([seed, 77])
+    cent = rng.choice(np.array([0.1, -0.1, 0.2, -0.2], np.float32), (clusters, dim))
+    cent[0] = 0.1
+    out = rng.choice(np.array([0.1, -0.1, 0.3], np.float32), (n, dim))     # background: three values only
+    per = min(per_cluster, max(1, n // (2 * clusters)))
+    for c in range(clusters):
+        norm = float(np.sqrt((cent[c].astype(np.float64) ** 2).sum()))
+        start = int(rng.integers(0, max(1, n - per)))
+        rows = np.concatenate([np.arange(start, start + per // 2),                       # neighbours in one sub-bucket
+                               rng.choice(n, per - per // 2, replace=False)]) % n       # and scattered ones
+        scale = rng.choice(np.array([0.5, 1.0, 2.0, 3.0], np.float32), rows.size)
+        a = rng.uniform(0.015, 0.1, rows.size).astype(np.float32) * norm     # twist size relative to |centre|
+        m = cent[c][None, :] * scale[:, None]
+        m[np.arange(rows.size), rng.integers(0, dim, rows.size)] += a * scale
+        out[rows] = m
+    q = cent.copy()
+    q[np.arange(clusters), rng.integers(0, dim, clusters)] *= 1.02
+    return np.ascontiguousarray(out, np.float32), np.ascontiguousarray(q, np.float32)
+
+
 def planted_dups(n: int, dim: int, seed: int = CORPUS_SEED, n_pairs: int = 64,
                  sims: Tuple[float, ...] = (0.90, 0.918, 0.922, 0.95, 0.999)) -> Tuple[np.ndarray, np.ndarray]:
     """(iii) gauss-unit corpus with pairs planted at chosen cosines (none within 1e-6 of
