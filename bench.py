@@ -494,6 +494,8 @@ def main():
         if rank == 0:
             sustained = {"value": NQ / (sus_ms / 1e3), "unit": UNIT, "ms_per_step": sus_ms, "steps": n_half,
                          "after_s_of_load": round(n_half * sus_ms / 1e3, 2), "scorer_kernel_ms": scorer_ms_sustained,
+                         "scorer_start_skew_ms": sts.scorer_start_skew_ms_sum / max(1, sts.scorer_kernel_timed),
+                         "scorer_end_skew_ms": sts.scorer_end_skew_ms_sum / max(1, sts.scorer_kernel_timed),
                          "clocks": sampler2.stop()}
 
     # ---- a wrong-but-fast configuration must not produce a headline: one batch of the timed workload is held

@@ -41,6 +41,7 @@ extern "C" {
 #define OMR_E_CAPACITY (-4)  /* store or output buffer full */
 #define OMR_E_NOT_FOUND (-5) /* memory.ErrNotFound, internal/memory/store.go:69 */
 #define OMR_E_WORKSPACE (-6) /* errWorkspaceRequired, internal/memory/store.go:60 */
+#define OMR_E_CANCELLED (-7) /* the caller's cancel flag was raised (Go: ctx.Err()) */
 
 /* Row flag bits (the boolean columns the recall WHERE clause reads, store.go:250-258). */
 #define OMR_ROW_FORGOTTEN 1u     /* memory_entities.forgotten */
@@ -121,6 +122,19 @@ typedef struct omr_row {
   int64_t valid_until_us;
 } omr_row;
 OMR_API int omr_upsert(omr_store* s, const omr_row* row, const float* vec, int32_t dim);
+/* n upserts in one call: one staged copy of the vectors and one ingest launch instead of n of each (the re-embed
+ * worker writes a page of rows at a time, internal/memory/reembed_worker.go:181-218).  rows[i] goes with
+ * vecs[i*dim .. (i+1)*dim); an observation id given twice keeps its last vector.  A row that fails validation
+ * stops the call; the rows before it stay upserted, as with n single calls. */
+OMR_API int omr_upsert_batch(omr_store* s, const omr_row* rows, const float* vecs, int32_t n, int32_t dim);
+/* Reclamation of hard-deleted rows (tombstone GC, internal/memory/tombstone.go:124; DeleteAll / BatchDelete;
+ * re-embedding churn).  A hard-deleted row's slot goes on a free list and omr_upsert / omr_upsert_batch hand it
+ * to the next NEW observation, so a store under steady churn never fills up with tombstones.  omr_compact
+ * additionally squeezes every hard-deleted row out (rows behind it move down, order kept, matrices rewritten
+ * in place on the device) and lowers omr_count; global row ids handed out earlier are stale afterwards.
+ * *reclaimed (may be NULL) receives the number of rows removed.  omr_free_slots: slots waiting for reuse. */
+OMR_API int omr_compact(omr_store* s, int64_t* reclaimed);
+OMR_API int64_t omr_free_slots(const omr_store* s);
 /* UpdateEmbedding (store_write.go:557-578): new vector for the entity's latest observation. */
 OMR_API int omr_update_embedding(omr_store* s, const uint8_t entity_id[16], const float* vec, int32_t dim);
 
@@ -228,6 +242,9 @@ typedef struct omr_selfjoin_opts {
   int32_t part_count;        /* ... of part_count (0 or 1 = the whole join).  With the matrix replicated on G
                                 GPUs, rank r runs part r of G and the G pair lists are concatenated
                                 (SURVEY.md section 8e); each part applies `limit` to its own pairs. */
+  const volatile int32_t* cancel; /* NULL, or a flag the caller may raise from another thread while the call runs (the
+                                Go binding's ctx.Done watcher): the join is launched in chunks of ~50 ms and returns
+                                OMR_E_CANCELLED at the next chunk boundary.  Must stay valid until the call returns. */
 } omr_selfjoin_opts;
 
 typedef struct omr_pair {
@@ -237,8 +254,22 @@ typedef struct omr_pair {
   int64_t canonical_row, dupe_row;
   uint32_t kind;
 } omr_pair;
-/* Writes min(found, cap) pairs ordered by similarity DESC; *found is the total. */
+/* Writes min(found, cap) pairs ordered by similarity DESC (ties: by canonical row, then dupe row); *found is the
+ * total.  `ORDER BY similarity DESC LIMIT n` runs on the device (running cut in the candidate pass, exact rescore,
+ * radix selection of the n best), so with a limit only n pairs ever reach the host.  The store's rows cannot
+ * change while a join runs (calls that would change them wait); recall calls proceed beside it. */
 OMR_API int omr_selfjoin(omr_store* s, const omr_selfjoin_opts* opts, omr_pair* out, int64_t cap, int64_t* found);
+/* The same join with struct-of-arrays results and no uuid lookup: global row ids of the canonical and the dupe
+ * observation and their similarity.  What the multi-GPU host code gathers from the ranks (SURVEY.md section 8e:
+ * counts, then payload) before the owner of the identity maps turns rows into uuids. */
+OMR_API int omr_selfjoin_rows(omr_store* s, const omr_selfjoin_opts* opts, int64_t* canonical_rows, int64_t* dupe_rows,
+                              double* similarities, int64_t cap, int64_t* found);
+
+/* Identity of a resident row: the uuid of the entity that owns global row `row` and (kind may be NULL) its interned
+ * kind (omr_kind_name turns it into the string).  For callers that hold rows from omr_search_rows /
+ * omr_selfjoin_rows and need the uuids the reference's records carry (Bucket.Entries,
+ * internal/memory/postgres/consolidation_prefilter.go:176-203). */
+OMR_API int omr_row_entity(omr_store* s, int64_t row, uint8_t entity_id[16], uint32_t* kind);
 
 /* ---- Memory Galaxy projection input: PCA over resident rows ----------
  * The reference loads one row per live entity (LoadProjectionInputs,
@@ -355,6 +386,9 @@ typedef struct omr_stats {
                                   CTA end, %globaltimer), summed; unlike scorer_ms_sum it excludes the time the
                                   kernel queued behind another batch in flight */
   int64_t scorer_kernel_timed;
+  int64_t join_candidates;   /* candidate pairs the self-join's tensor-core pass emitted (before the exact rescore) */
+  double scorer_start_skew_ms_sum; /* latest minus earliest CTA start of those launches, summed */
+  double scorer_end_skew_ms_sum;   /* latest minus earliest CTA end, summed */
 } omr_stats;
 OMR_API int omr_get_stats(const omr_store* s, omr_stats* out);
 /* Brackets the approximate scorer (the dominant kernel) with CUDA events on the search stream

@@ -10,7 +10,7 @@ from pathlib import Path
 PKG = Path(__file__).resolve().parent
 LIB_PATH = PKG / "lib" / "libomnia_recall.so"
 
-OK, E_INVALID, E_CUDA, E_DIM, E_CAPACITY, E_NOT_FOUND, E_WORKSPACE = 0, -1, -2, -3, -4, -5, -6
+OK, E_INVALID, E_CUDA, E_DIM, E_CAPACITY, E_NOT_FOUND, E_WORKSPACE, E_CANCELLED = 0, -1, -2, -3, -4, -5, -6, -7
 ROW_FORGOTTEN, ROW_SUPERSEDED, ROW_HAS_EMBEDDING, ROW_MUTABLE = 1, 2, 4, 8
 MATCH_ANY, MATCH_NULL_ONLY, MATCH_EQ, MATCH_NULL_OR_EQ = 0, 1, 2, 3
 NO_EXPIRY = 2**63 - 1
@@ -58,7 +58,7 @@ class Hit(C.Structure):
 class SelfJoinOpts(C.Structure):
     _fields_ = [("workspace_id", C.c_char_p), ("similarity_floor", C.c_float), ("limit", C.c_int32),
                 ("require_same_kind", C.c_int32), ("require_mutable", C.c_int32), ("part_index", C.c_int32),
-                ("part_count", C.c_int32)]
+                ("part_count", C.c_int32), ("cancel", C.POINTER(C.c_int32))]
 
 
 class Pair(C.Structure):
@@ -73,7 +73,9 @@ class Stats(C.Structure):
                 ("scorer_ms_sum", C.c_double), ("scorer_timed", C.c_int64), ("host_calls", C.c_int64),
                 ("host_batches", C.c_int64), ("listed_entries", C.c_int64),
                 ("phase_ms_sum", C.c_double * 3), ("scorer_kernel_ms_sum", C.c_double),
-                ("scorer_kernel_timed", C.c_int64)]
+                ("scorer_kernel_timed", C.c_int64), ("join_candidates", C.c_int64),
+                ("scorer_start_skew_ms_sum", C.c_double),
+                ("scorer_end_skew_ms_sum", C.c_double)]
 
 
 # name -> (restype, argtypes).  tests/test_abi.py checks this table against the header.
@@ -108,6 +110,12 @@ SIGNATURES = {
     "omr_cosine_ranked": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.POINTER(Filter), C.c_int32, C.c_void_p,
                                     C.POINTER(C.c_int32)]),
     "omr_selfjoin": (C.c_int, [C.c_void_p, C.POINTER(SelfJoinOpts), C.c_void_p, C.c_int64, C.POINTER(C.c_int64)]),
+    "omr_upsert_batch": (C.c_int, [C.c_void_p, C.POINTER(Row), C.c_void_p, C.c_int32, C.c_int32]),
+    "omr_compact": (C.c_int, [C.c_void_p, C.POINTER(C.c_int64)]),
+    "omr_free_slots": (C.c_int64, [C.c_void_p]),
+    "omr_row_entity": (C.c_int, [C.c_void_p, C.c_int64, C.c_void_p, C.POINTER(C.c_uint32)]),
+    "omr_selfjoin_rows": (C.c_int, [C.c_void_p, C.POINTER(SelfJoinOpts), C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64,
+                                    C.POINTER(C.c_int64)]),
     "omr_bitmap_words": (C.c_int64, [C.c_void_p]),
     "omr_device_build_bitmaps": (C.c_int, [C.c_void_p, C.POINTER(Filter), C.c_int32, C.c_void_p, C.c_void_p]),
     "omr_device_search": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p,

@@ -17,7 +17,7 @@ PKG = Path(__file__).resolve().parent
 CSRC = PKG / "csrc"
 LIB_DIR = PKG / "lib"
 LIB = LIB_DIR / "libomnia_recall.so"
-SOURCES = ["k_ingest.cu", "k_score_stream.cu", "k_score_umma.cu", "k_select.cu", "k_post.cu", "k_exchange.cu", "k_pca.cu", "store.cu", "noalloc.cu"]
+SOURCES = ["k_ingest.cu", "k_score_stream.cu", "k_score_umma.cu", "k_select.cu", "k_post.cu", "k_exchange.cu", "k_pca.cu", "k_join.cu", "store.cu", "noalloc.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-std=c++17", "-O3", "-lineinfo", "-gencode", "arch=compute_100a,code=sm_100a",
          "-Xcompiler", "-fPIC,-fvisibility=hidden", "--expt-relaxed-constexpr"]

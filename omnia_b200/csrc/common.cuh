@@ -21,6 +21,7 @@ constexpr uint8_t kRowSuperseded = 2;
 constexpr uint8_t kRowHasEmbedding = 4;
 constexpr uint8_t kRowMutable = 8;
 constexpr uint8_t kRowEntityRep = 16;
+constexpr uint8_t kRowFree = 32;      // host mirror only: the slot of a hard-deleted row is on the free list
 constexpr uint8_t kRowDeleted = 64;
 
 // Packed candidate key: an order-preserving map of the fp32 score to int32

@@ -22,6 +22,7 @@ __device__ __forceinline__ double warp_sum(double v) {
 // HBM-bound: 4*dim bytes in, 6*pitch bytes out per row.
 __global__ void __launch_bounds__(256) normalize_rows_kernel(const float* __restrict__ src, int64_t n, int dim,
                                                              int pitch, int64_t row0,
+                                                             const int64_t* __restrict__ dst_rows,
                                                              __nv_bfloat16* __restrict__ out_bf16,
                                                              float* __restrict__ out_f32,
                                                              double* __restrict__ norm2, int64_t n_pad,
@@ -29,14 +30,15 @@ __global__ void __launch_bounds__(256) normalize_rows_kernel(const float* __rest
   const int lane = threadIdx.x & 31;
   const int64_t r = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   if (r >= n_pad) return;
-  __nv_bfloat16* ob = out_bf16 + (row0 + r) * pitch;
-  float* of = out_f32 ? out_f32 + (row0 + r) * pitch : nullptr;
+  const int64_t dst = (dst_rows && r < n) ? dst_rows[r] : row0 + r;   // scattered upserts name their rows
+  __nv_bfloat16* ob = out_bf16 + dst * pitch;
+  float* of = out_f32 ? out_f32 + dst * pitch : nullptr;
   if (r >= n) {  // padding rows of a query batch: all zero
     for (int i = lane; i < pitch; i += 32) {
       ob[i] = __float2bfloat16_rn(0.0f);
       if (of) of[i] = 0.0f;
     }
-    if (lane == 0 && norm2) norm2[row0 + r] = 0.0;
+    if (lane == 0 && norm2) norm2[dst] = 0.0;
     return;
   }
   const float* s = src + r * dim;
@@ -52,7 +54,7 @@ __global__ void __launch_bounds__(256) normalize_rows_kernel(const float* __rest
     if (of) of[i] = v;
     ob[i] = __float2bfloat16_rn(v * inv);
   }
-  if (lane == 0 && norm2) norm2[row0 + r] = ss;
+  if (lane == 0 && norm2) norm2[dst] = ss;
   // a NaN element makes the sum NaN, an infinite one makes it +inf (fp64 cannot overflow on fp32 squares)
   if (lane == 0 && bad_flag && !isfinite(ss)) atomicOr(bad_flag, ss != ss ? 1 : 2);
 }
@@ -100,12 +102,12 @@ __global__ void __launch_bounds__(256) build_bitmaps_kernel(RowMetaView m, int64
 
 }  // namespace
 
-int launch_ingest_rows(const float* src, int64_t n, int dim, int pitch, int64_t row0, __nv_bfloat16* rows_bf16,
-                       float* rows_f32, double* norm2, cudaStream_t st) {
+int launch_ingest_rows(const float* src, int64_t n, int dim, int pitch, int64_t row0, const int64_t* dst_rows,
+                       __nv_bfloat16* rows_bf16, float* rows_f32, double* norm2, int32_t* bad_flag, cudaStream_t st) {
   if (n <= 0) return 0;
   const int warps = 8;
   normalize_rows_kernel<<<(unsigned)((n + warps - 1) / warps), warps * 32, 0, st>>>(
-      src, n, dim, pitch, row0, rows_bf16, rows_f32, norm2, n, nullptr);
+      src, n, dim, pitch, row0, dst_rows, rows_bf16, rows_f32, norm2, n, bad_flag);
   OMR_CUDA_OK(cudaGetLastError());
   return 0;
 }
@@ -120,7 +122,7 @@ int launch_prep_queries(const float* q, int nq, int qpad, int dim, int pitch, __
     carveout_set = true;
   }
   normalize_rows_kernel<<<(unsigned)((qpad + warps - 1) / warps), warps * 32, 0, st>>>(
-      q, nq, dim, pitch, 0, qn, nullptr, qnorm2, qpad, bad_flag);
+      q, nq, dim, pitch, 0, nullptr, qn, nullptr, qnorm2, qpad, bad_flag);
   OMR_CUDA_OK(cudaGetLastError());
   return 0;
 }

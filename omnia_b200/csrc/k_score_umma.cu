@@ -59,7 +59,6 @@ struct __align__(8) PipeBarriers {
 
 enum { kEpiTop2 = 0, kEpiPairs = 1, kEpiEmit = 2 };
 
-struct PairStage;
 constexpr int kPairStageBytes = 1024 * 8 + 32;
 constexpr int kSmemBytes = kStages * kStageBytes + (int)sizeof(PipeBarriers) + kPairStageBytes + 1024;  // +1024: manual alignment
 
@@ -206,12 +205,13 @@ __device__ void refresh_threshold(const EmitView& ev, int q, int lane, uint32_t*
 // Body of warp 3 in an emission launch: serve refresh requests until the four epilogue warps are done.
 __device__ void refresh_loop(const EmitView& ev, RefreshQueue* rq, int lane) {
   while (true) {
-    const unsigned int done = *reinterpret_cast<volatile unsigned int*>(&rq->epi_done);
+    unsigned int done = lane == 0 ? *reinterpret_cast<volatile unsigned int*>(&rq->epi_done) : 0u;
+    done = __shfl_sync(0xffffffffu, done, 0);
     const unsigned int v0 = atomicExch(&rq->slot[lane], 0u);
     const unsigned int v1 = atomicExch(&rq->slot[lane + 32], 0u);
     unsigned int b0 = __ballot_sync(0xffffffffu, v0 != 0u), b1 = __ballot_sync(0xffffffffu, v1 != 0u);
     if (!(b0 | b1)) {
-      if (__shfl_sync(0xffffffffu, done, 0) >= 4u) break;
+      if (done >= 4u) break;
       __nanosleep(400);
       continue;
     }
@@ -228,66 +228,163 @@ __device__ void refresh_loop(const EmitView& ev, RefreshQueue* rq, int lane) {
   }
 }
 
-// Epilogue of the self-join: emit (a, b) for a < b when the approximate cosine clears the
-// (margin-lowered) floor and both rows are members of the join.  Pairs are staged in shared
-// memory and flushed once per tile with ONE global atomic per CTA (the pair list is compacted in
-// shared memory first); a pair that finds the stage full goes straight to global memory.
-constexpr int kPairStage = 1024;
-struct PairStage {
-  PairCand buf[kPairStage];
-  unsigned int count;
-  unsigned long long base;
+// Epilogue of the self-join: emit (a, b) for a < b when the approximate cosine clears the (margin-lowered)
+// floor and both rows are members of the join.
+//  * A 31-step max over the 32 scores of a chunk decides first whether anything can pass; most chunks end there.
+//  * Appends are aggregated per warp: one global atomicAdd per chunk that has passes, however many pass (on
+//    tie-heavy corpora a chunk can pass whole), no shared-memory stage and no CTA barrier.
+//  * With a LIMIT (`ORDER BY similarity DESC LIMIT n`, consolidation/prefilter.go:129-130) the join keeps a
+//    running cut: passing pairs are counted in a histogram of their approximate scores (per CTA in shared
+//    memory, folded into a global one by warp 3), and the lower edge T of the bin at which the count from the top
+//    reaches n is a lower bound of the n-th best approximate score.  A pair of the final top n scores at least
+//    T - 2 * margin approximately (same argument as the recall thresholds, kernels.cuh), so the cut
+//    max(floor - margin, T - 2 * margin) never drops one, and on a corpus of near-duplicates it keeps the
+//    candidate list at the size of the duplicate clusters instead of every pair above the floor.
+constexpr int kJoinBins = 2048;
+struct JoinHist {
+  unsigned int bins[kJoinBins];
+  unsigned int epi_done;
+  unsigned int dirty;
 };
-static_assert(sizeof(PairStage) <= 1024 * 8 + 32, "PairStage outgrew its shared-memory slot");
+static_assert(sizeof(JoinHist) <= kPairStageBytes, "JoinHist outgrew its shared-memory slot");
+
 struct PairEpilogue {
   const uint32_t* member;  // bitmap over rows
   PairCand* pairs;
   unsigned long long cap;
   unsigned long long* count;
-  float threshold;
+  float threshold;         // floor - margin
+  // LIMIT mode (run_cut != nullptr)
+  int32_t* run_cut;        // ordered-int image of the running cut, raised with atomicMax
+  unsigned int* ghist;     // [kJoinBins] approximate-score histogram of the pairs emitted so far
+  const uint16_t* kind;    // per row; nullptr = no `e1.kind = e2.kind` rule
+  float hist_lo, hist_scale;  // bin = (score - hist_lo) * hist_scale
+  float band;              // 2 * margin
+  int limit;
+  // per tile
   int32_t row_a;
   bool a_member;
-  PairStage* stage;  // shared memory of this CTA
+  uint16_t kind_a;
+  float cut;               // max(threshold, running cut) when the tile began
+  JoinHist* hist;          // shared memory of this CTA
 
-  __device__ __forceinline__ void chunk(int b_tile, int c, const uint32_t (&v)[32]) {
-    const int32_t b0 = b_tile * kTileRows + c * 32;
-    uint32_t mask = __ldg(member + (b0 >> 5));
-    if (!a_member) mask = 0;
-    // rows b <= a are the lower triangle: drop them
-    if (row_a >= b0 + 31) mask = 0;
-    else if (row_a >= b0) mask &= ~((2u << (row_a - b0)) - 1u);
-    uint32_t pass = 0;
+  __device__ __forceinline__ void begin_tile(int32_t row) {
+    row_a = row;
+    a_member = (__ldg(member + (row_a >> 5)) >> (row_a & 31)) & 1u;
+    cut = threshold;
+    if (run_cut) cut = fmaxf(cut, ordered_to_score(__ldcg(run_cut)));
+    if (kind) kind_a = __ldg(kind + row_a);
+  }
+
+  __device__ __forceinline__ void chunk(int b_tile, int c, const uint32_t (&v)[32], int lane) {
+    float m = __uint_as_float(v[0]);
 #pragma unroll
-    for (int j = 0; j < 32; j++) pass |= (__uint_as_float(v[j]) >= threshold) ? (1u << j) : 0u;
-    pass &= mask;
+    for (int j = 1; j < 32; j++) m = fmaxf(m, __uint_as_float(v[j]));
+    const bool maybe = a_member && m >= cut;
+    if (!__any_sync(0xffffffffu, maybe)) return;
+    const int32_t b0 = b_tile * kTileRows + c * 32;
+    uint32_t pass = 0;
+    if (maybe) {
+      uint32_t mask = __ldg(member + (b0 >> 5));
+      // rows b <= a are the lower triangle: drop them
+      if (row_a >= b0 + 31) mask = 0;
+      else if (row_a >= b0) mask &= ~((2u << (row_a - b0)) - 1u);
+#pragma unroll
+      for (int j = 0; j < 32; j++) pass |= (__uint_as_float(v[j]) >= cut) ? (1u << j) : 0u;
+      pass &= mask;
+      if (kind) {
+        uint32_t rest = pass;
+        while (rest) {
+          const int j = __ffs(rest) - 1;
+          rest &= rest - 1;
+          if (__ldg(kind + b0 + j) != kind_a) pass &= ~(1u << j);
+        }
+      }
+      if (run_cut && pass) {
+        uint32_t rest = pass;
+        while (rest) {
+          const int j = __ffs(rest) - 1;
+          rest &= rest - 1;
+          const int bin = (int)fminf(fmaxf((__uint_as_float(pick32(v, j)) - hist_lo) * hist_scale, 0.0f), (float)(kJoinBins - 1));
+          atomicAdd(&hist->bins[bin], 1u);
+        }
+        hist->dirty = 1u;
+      }
+    }
+    // warp-aggregated append
+    const int mine = __popc(pass);
+    int incl = mine;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int t = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += t;
+    }
+    const int total = __shfl_sync(0xffffffffu, incl, 31);
+    if (total == 0) return;
+    unsigned long long base = 0;
+    if (lane == 31) base = atomicAdd(count, (unsigned long long)total);
+    base = __shfl_sync(0xffffffffu, base, 31) + (unsigned long long)(incl - mine);
     while (pass) {
       const int j = __ffs(pass) - 1;
       pass &= pass - 1;
-      const unsigned int slot = atomicAdd(&stage->count, 1u);
-      if (slot < (unsigned)kPairStage) {
-        stage->buf[slot] = PairCand{row_a, b0 + j};
-      } else {
-        const unsigned long long g = atomicAdd(count, 1ull);
-        if (g < cap) pairs[g] = PairCand{row_a, b0 + j};
-      }
+      if (base < cap) pairs[base] = PairCand{row_a, b0 + j};
+      base++;
     }
   }
-
-  // All 128 epilogue threads, once per tile (t = thread index inside the epilogue group).
-  __device__ __forceinline__ void flush(int t) {
-    asm volatile("bar.sync 2, 128;" ::: "memory");
-    const unsigned int n = min(stage->count, (unsigned)kPairStage);
-    if (n == 0) return;                       // uniform: every thread read the same count
-    if (t == 0) stage->base = atomicAdd(count, (unsigned long long)n);
-    asm volatile("bar.sync 2, 128;" ::: "memory");
-    const unsigned long long base = stage->base;
-    for (unsigned int i = t; i < n; i += 128)
-      if (base + i < cap) pairs[base + i] = stage->buf[i];
-    asm volatile("bar.sync 2, 128;" ::: "memory");
-    if (t == 0) stage->count = 0;
-    asm volatile("bar.sync 2, 128;" ::: "memory");  // nobody appends for the next tile before the reset
-  }
 };
+
+// Body of warp 3 in a LIMIT-mode join: fold this CTA's histogram into the global one and raise the running cut,
+// until the four epilogue warps are done.
+__device__ void join_cut_loop(const PairEpilogue& pe, JoinHist* h, int lane) {
+  constexpr int kPerLane = kJoinBins / 32;
+  while (true) {
+    // one lane looks, every lane follows: the branch below holds warp collectives and must not diverge
+    unsigned int done = 0, dirty = 0;
+    if (lane == 0) {
+      done = *reinterpret_cast<volatile unsigned int*>(&h->epi_done);
+      dirty = *reinterpret_cast<volatile unsigned int*>(&h->dirty);
+      if (dirty) h->dirty = 0u;
+    }
+    done = __shfl_sync(0xffffffffu, done, 0);
+    dirty = __shfl_sync(0xffffffffu, dirty, 0);
+    if (dirty) {
+      __syncwarp();
+      for (int b = lane; b < kJoinBins; b += 32) {
+        const unsigned int v = atomicExch(&h->bins[b], 0u);
+        if (v) atomicAdd(pe.ghist + b, v);
+      }
+      __threadfence();
+      // lane L owns bins [kJoinBins - kPerLane*(L+1), kJoinBins - kPerLane*L): lane 0 holds the best scores
+      const int hi = kJoinBins - kPerLane * lane;
+      unsigned int sum = 0;
+      for (int b = hi - kPerLane; b < hi; b++) sum += __ldcg(pe.ghist + b);
+      unsigned int incl = sum;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const unsigned int t = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += t;
+      }
+      const unsigned int who = __ballot_sync(0xffffffffu, incl >= (unsigned)pe.limit);
+      if (who) {
+        const int owner = __ffs(who) - 1;
+        if (lane == owner) {
+          unsigned int acc = incl - sum;
+          int b = hi - 1;
+          for (; b >= hi - kPerLane; b--) {
+            acc += __ldcg(pe.ghist + b);
+            if (acc >= (unsigned)pe.limit) break;
+          }
+          const float T = pe.hist_lo + (float)b / pe.hist_scale;   // lower edge of the bin
+          atomicMax(pe.run_cut, score_to_ordered(T - pe.band));
+        }
+      }
+      __syncwarp();
+    } else {
+      if (done >= 4u) break;
+      __nanosleep(2000);
+    }
+  }
+}
 
 template <int kEpi, int S>
 struct KernelArgs {
@@ -309,7 +406,7 @@ struct KernelArgs {
   int32_t* cand_keys;
   int64_t keys_per_query;
   EmitView ev;     // emission mode
-  unsigned long long* timer;  // nullable: [0] = earliest CTA start, [1] = latest CTA end (%globaltimer, ns)
+  unsigned long long* timer;  // nullable: [0] earliest / [2] latest CTA start, [1] latest / [3] earliest CTA end (%globaltimer, ns)
   // self-join
   PairEpilogue pe;
 };
@@ -362,12 +459,23 @@ __global__ void __launch_bounds__(kNumThreads, 1)
   uint8_t* smem_a = smem;
   uint8_t* smem_b = smem + kStages * kABytes;
   PipeBarriers* bars = reinterpret_cast<PipeBarriers*>(smem + kStages * kStageBytes);
-  PairStage* pstage = reinterpret_cast<PairStage*>(reinterpret_cast<uint8_t*>(bars) + ((sizeof(PipeBarriers) + 15) & ~size_t(15)));
-  RefreshQueue* rq = reinterpret_cast<RefreshQueue*>(pstage);
+  uint8_t* aux = reinterpret_cast<uint8_t*>(bars) + ((sizeof(PipeBarriers) + 15) & ~size_t(15));
+  RefreshQueue* rq = reinterpret_cast<RefreshQueue*>(aux);   // recall, emission mode
+  JoinHist* jh = reinterpret_cast<JoinHist*>(aux);           // self-join, LIMIT mode
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  if (kSelfJoin && threadIdx.x == 0) pstage->count = 0;
-  if (args.timer && threadIdx.x == 0) atomicMin(args.timer, ptx::globaltimer());
+  if (kSelfJoin) {
+    for (int i = threadIdx.x; i < kJoinBins; i += kNumThreads) jh->bins[i] = 0u;
+    if (threadIdx.x == 0) {
+      jh->epi_done = 0u;
+      jh->dirty = 0u;
+    }
+  }
+  if (args.timer && threadIdx.x == 0) {
+    const unsigned long long t = ptx::globaltimer();
+    atomicMin(args.timer, t);
+    atomicMax(args.timer + 2, t);
+  }
   if (kEpi == kEpiEmit) {
     if (threadIdx.x < kRefreshSlots) rq->slot[threadIdx.x] = 0u;
     if (threadIdx.x == 0) {
@@ -459,6 +567,8 @@ __global__ void __launch_bounds__(kNumThreads, 1)
   } else if (kEpi == kEpiEmit && warp == 3) {
     // ---------------- threshold refresh ----------------
     refresh_loop(args.ev, rq, lane);
+  } else if (kSelfJoin && warp == 3) {
+    if (args.pe.run_cut) join_cut_loop(args.pe, jh, lane);
   } else if (warp >= kEpilogueWarp0) {
     // ---------------- epilogue ----------------
     const int quarter = warp & 3;  // TMEM lanes [32*quarter, 32*quarter+32) are this warp's
@@ -470,7 +580,7 @@ __global__ void __launch_bounds__(kNumThreads, 1)
     ee.ev = args.ev;
     ee.rq = rq;
     PairEpilogue pe = args.pe;
-    pe.stage = pstage;
+    pe.hist = jh;
     for (int64_t w = blockIdx.x; w < args.n_work; w += gridDim.x) {
       int a_tile, b_tile;
       if (!decode_work<kSelfJoin>(args.work_first + w * args.work_step, args.n_a_tiles, args.n_b_tiles, args.sb, a_tile,
@@ -490,8 +600,7 @@ __global__ void __launch_bounds__(kNumThreads, 1)
           te.begin_tile();
         }
       } else {
-        pe.row_a = a_tile * kQueryTile + t_local;
-        pe.a_member = (__ldg(pe.member + (pe.row_a >> 5)) >> (pe.row_a & 31)) & 1u;
+        pe.begin_tile(a_tile * kQueryTile + t_local);
       }
       ptx::mbar_wait(&bars->tmem_full[as], aphase);
       ptx::tc_fence_after_sync();
@@ -509,24 +618,31 @@ __global__ void __launch_bounds__(kNumThreads, 1)
           te.chunk(b_tile, c, v0);
           te.chunk(b_tile, c + 1, v1);
         } else {
-          pe.chunk(b_tile, c, v0);
-          pe.chunk(b_tile, c + 1, v1);
+          pe.chunk(b_tile, c, v0, lane);
+          pe.chunk(b_tile, c + 1, v1, lane);
         }
       }
       ptx::tc_fence_before_sync();
       ptx::mbar_arrive(&bars->tmem_empty[as]);
-      if (kSelfJoin) pe.flush(t_local);
     }
     if (kEpi == kEpiEmit) {
       __syncwarp();
       if (lane == 0) atomicAdd(&rq->epi_done, 1u);
+    }
+    if (kSelfJoin) {
+      __syncwarp();
+      if (lane == 0) atomicAdd(&jh->epi_done, 1u);
     }
   }
 
   ptx::tc_fence_before_sync();
   __syncthreads();
   if (warp == 2) ptx::tmem_dealloc(tmem_base, kTmemCols);
-  if (args.timer && threadIdx.x == 0) atomicMax(args.timer + 1, ptx::globaltimer());
+  if (args.timer && threadIdx.x == 0) {
+    const unsigned long long t = ptx::globaltimer();
+    atomicMax(args.timer + 1, t);
+    atomicMin(args.timer + 3, t);
+  }
 }
 
 // ---------------------------------------------------------------------------------------
@@ -599,12 +715,23 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kNumThreads, 1)
   uint8_t* smem_a = smem;
   uint8_t* smem_b = smem + kStages2 * kABytes;
   PipeBarriers2* bars = reinterpret_cast<PipeBarriers2*>(smem + kStages2 * kStageBytes2);
-  PairStage* pstage = reinterpret_cast<PairStage*>(reinterpret_cast<uint8_t*>(bars) + ((sizeof(PipeBarriers2) + 15) & ~size_t(15)));
-  RefreshQueue* rq = reinterpret_cast<RefreshQueue*>(pstage);
+  uint8_t* aux = reinterpret_cast<uint8_t*>(bars) + ((sizeof(PipeBarriers2) + 15) & ~size_t(15));
+  RefreshQueue* rq = reinterpret_cast<RefreshQueue*>(aux);   // recall, emission mode
+  JoinHist* jh = reinterpret_cast<JoinHist*>(aux);           // self-join, LIMIT mode
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  if (kSelfJoin && threadIdx.x == 0) pstage->count = 0;
-  if (args.timer && threadIdx.x == 0) atomicMin(args.timer, ptx::globaltimer());
+  if (kSelfJoin) {
+    for (int i = threadIdx.x; i < kJoinBins; i += kNumThreads) jh->bins[i] = 0u;
+    if (threadIdx.x == 0) {
+      jh->epi_done = 0u;
+      jh->dirty = 0u;
+    }
+  }
+  if (args.timer && threadIdx.x == 0) {
+    const unsigned long long t = ptx::globaltimer();
+    atomicMin(args.timer, t);
+    atomicMax(args.timer + 2, t);
+  }
   if (kEpi == kEpiEmit) {
     if (threadIdx.x < kRefreshSlots) rq->slot[threadIdx.x] = 0u;
     if (threadIdx.x == 0) {
@@ -701,6 +828,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kNumThreads, 1)
   } else if (kEpi == kEpiEmit && warp == 3) {
     // ---------------- threshold refresh (one warp per CTA) ----------------
     refresh_loop(args.ev, rq, lane);
+  } else if (kSelfJoin && warp == 3) {
+    if (args.pe.run_cut) join_cut_loop(args.pe, jh, lane);
   } else if (warp >= kEpilogueWarp0) {
     // ---------------- epilogue (both CTAs, own TMEM lanes) ----------------
     const int quarter = warp & 3;
@@ -712,7 +841,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kNumThreads, 1)
     ee.ev = args.ev;
     ee.rq = rq;
     PairEpilogue pe = args.pe;
-    pe.stage = pstage;
+    pe.hist = jh;
     for (int64_t w = cluster; w < args.n_work; w += n_clusters) {
       int a_tile, b_tile;
       if (!decode_work2<kSelfJoin>(args.work_first + w * args.work_step, args.n_a_tiles, args.n_b_tiles, args.sb, n_clusters,
@@ -732,8 +861,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kNumThreads, 1)
           te.begin_tile();
         }
       } else {
-        pe.row_a = q;
-        pe.a_member = (__ldg(pe.member + (pe.row_a >> 5)) >> (pe.row_a & 31)) & 1u;
+        pe.begin_tile(q);
       }
       ptx::mbar_wait(&bars->tmem_full[as], aphase);
       ptx::tc_fence_after_sync();
@@ -751,24 +879,31 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kNumThreads, 1)
           te.chunk(b_tile, c, v0);
           te.chunk(b_tile, c + 1, v1);
         } else {
-          pe.chunk(b_tile, c, v0);
-          pe.chunk(b_tile, c + 1, v1);
+          pe.chunk(b_tile, c, v0, lane);
+          pe.chunk(b_tile, c + 1, v1, lane);
         }
       }
       ptx::tc_fence_before_sync();
       ptx::mbar_arrive_cluster(&bars->tmem_empty[as], 0);
-      if (kSelfJoin) pe.flush(t_local);
     }
     if (kEpi == kEpiEmit) {
       __syncwarp();
       if (lane == 0) atomicAdd(&rq->epi_done, 1u);
+    }
+    if (kSelfJoin) {
+      __syncwarp();
+      if (lane == 0) atomicAdd(&jh->epi_done, 1u);
     }
   }
 
   ptx::tc_fence_before_sync();
   ptx::cluster_sync_all();
   if (warp == 2) ptx::tmem_dealloc_2sm(tmem_base, kTmemCols);
-  if (args.timer && threadIdx.x == 0) atomicMax(args.timer + 1, ptx::globaltimer());
+  if (args.timer && threadIdx.x == 0) {
+    const unsigned long long t = ptx::globaltimer();
+    atomicMax(args.timer + 1, t);
+    atomicMin(args.timer + 3, t);
+  }
 }
 
 template <int S>
@@ -920,33 +1055,61 @@ int launch_score_umma2(const CUtensorMap& tmap_q, const CUtensorMap& tmap_rows_h
   return fail_msg(-2, "sub-bucket size must be 32, 64, 128 or 256, got %d", S);
 }
 
-// Self-join on CTA pairs: tmap_half is the 128-row-box map of the member matrix (it serves both operands:
-// each CTA loads its half of the 256-row A tile and its half of the 256-row B tile).
-int launch_selfjoin_umma2(const CUtensorMap& tmap_half, int64_t n, int k_blocks, int part_index, int part_count,
-                          float threshold, const uint32_t* member_bitmap, PairCand* pairs, unsigned long long cap,
-                          unsigned long long* pair_count, int num_sms, cudaStream_t st) {
-  if (n <= 0) return 0;
-  const int64_t nb = (n + kTileRows - 1) / kTileRows;
-  KernelArgs<kEpiPairs, 256> a{};
-  a.n_a_tiles = (int)nb;
-  a.n_b_tiles = (int)nb;
+// Work items of one partition of the join's tile-pair space (super-blocks over the upper triangle, see
+// decode_work / decode_work2); a launch may cover any contiguous range of them.
+static int join_sb(int k_blocks) {
+  // super-block edge: two row blocks of sb * 256 rows must sit in L2 together (126 MB, two dies); 24 tiles =
+  // 18.9 MB per block at pitch 1536, scaled up for narrower rows
   int sb = 24;
   if (k_blocks > 0) sb = std::max(8, std::min(96, 24 * 24 / k_blocks));
   if (const char* e = getenv("OMR_SELFJOIN_SB")) sb = std::max(1, atoi(e));
-  a.sb = sb;
+  return sb;
+}
+
+int64_t selfjoin_items(int64_t n, int k_blocks, int part_index, int part_count, bool pair_kernel) {
+  if (n <= 0) return 0;
+  const int64_t nb = (n + kTileRows - 1) / kTileRows;
+  const int sb = join_sb(k_blocks);
   const int64_t NB = (nb + sb - 1) / sb;
-  const int64_t total = NB * (NB + 1) / 2 * ((int64_t)sb * sb);
+  const int64_t total = NB * (NB + 1) / 2 * ((pair_kernel ? 1ll : 2ll) * sb * sb);
   if (part_count < 1) part_count = 1;
-  a.work_first = part_index;
-  a.work_step = part_count;
-  a.n_work = part_index < total ? (total - part_index + part_count - 1) / part_count : 0;
+  return part_index < total ? (total - part_index + part_count - 1) / part_count : 0;
+}
+
+template <typename Args>
+static void fill_join_args(Args& a, const JoinLaunch& j, int64_t items) {
+  const int part_count = j.part_count < 1 ? 1 : j.part_count;
+  const int64_t first = std::max<int64_t>(0, j.chunk_first);
+  const int64_t count = j.chunk_items < 0 ? items - first : std::min(j.chunk_items, items - first);
+  a.sb = join_sb(j.k_blocks);
+  a.work_first = j.part_index + first * part_count;   // partition p of P takes the items p, p+P, p+2P, ... (interleaved:
+  a.work_step = part_count;                           // balanced); a chunk is a contiguous range of those
+  a.n_work = std::max<int64_t>(0, count);
+  a.k_blocks = j.k_blocks;
+  a.pe.member = j.member_bitmap;
+  a.pe.pairs = j.pairs;
+  a.pe.cap = j.cap;
+  a.pe.count = j.pair_count;
+  a.pe.threshold = j.threshold;
+  a.pe.run_cut = j.limit > 0 ? j.run_cut : nullptr;
+  a.pe.ghist = j.ghist;
+  a.pe.kind = j.kind;
+  a.pe.hist_lo = j.hist_lo;
+  a.pe.hist_scale = j.hist_scale;
+  a.pe.band = j.band;
+  a.pe.limit = j.limit;
+}
+
+// Self-join on CTA pairs: tmap_half is the 128-row-box map of the member matrix (it serves both operands:
+// each CTA loads its half of the 256-row A tile and its half of the 256-row B tile).
+int launch_selfjoin_umma2(const CUtensorMap& tmap_half, const JoinLaunch& j, int num_sms, cudaStream_t st) {
+  if (j.n <= 0) return 0;
+  const int64_t nb = (j.n + kTileRows - 1) / kTileRows;
+  KernelArgs<kEpiPairs, 256> a{};
+  a.n_a_tiles = (int)nb;
+  a.n_b_tiles = (int)nb;
+  fill_join_args(a, j, selfjoin_items(j.n, j.k_blocks, j.part_index, j.part_count, true));
   if (a.n_work == 0) return 0;
-  a.k_blocks = k_blocks;
-  a.pe.member = member_bitmap;
-  a.pe.pairs = pairs;
-  a.pe.cap = cap;
-  a.pe.count = pair_count;
-  a.pe.threshold = threshold;
   auto kern = score_umma2_kernel<kEpiPairs, 256>;
   OMR_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes2));
   int64_t clusters = num_sms / 2;
@@ -956,33 +1119,15 @@ int launch_selfjoin_umma2(const CUtensorMap& tmap_half, int64_t n, int k_blocks,
   return 0;
 }
 
-int launch_selfjoin_umma(const CUtensorMap& tmap_a, const CUtensorMap& tmap_b, int64_t n, int k_blocks,
-                         int part_index, int part_count, float threshold, const uint32_t* member_bitmap, PairCand* pairs, unsigned long long cap,
-                         unsigned long long* pair_count, int num_sms, cudaStream_t st) {
-  if (n <= 0) return 0;
-  const int64_t nb = (n + kTileRows - 1) / kTileRows;
+int launch_selfjoin_umma(const CUtensorMap& tmap_a, const CUtensorMap& tmap_b, const JoinLaunch& j, int num_sms,
+                         cudaStream_t st) {
+  if (j.n <= 0) return 0;
+  const int64_t nb = (j.n + kTileRows - 1) / kTileRows;
   KernelArgs<kEpiPairs, 256> a{};
   a.n_a_tiles = (int)(2 * nb);
   a.n_b_tiles = (int)nb;
-  // super-block edge: two row blocks of sb * 256 rows must sit in L2 together (126 MB, two dies); 24 tiles =
-  // 18.9 MB per block at pitch 1536, scaled up for narrower rows
-  int sb = 24;
-  if (k_blocks > 0) sb = std::max(8, std::min(96, 24 * 24 / k_blocks));
-  if (const char* e = getenv("OMR_SELFJOIN_SB")) sb = std::max(1, atoi(e));
-  a.sb = sb;
-  const int64_t NB = (nb + sb - 1) / sb;
-  const int64_t total = NB * (NB + 1) / 2 * (2ll * sb * sb);
-  if (part_count < 1) part_count = 1;
-  a.work_first = part_index;          // partition p of P takes the items p, p+P, p+2P, ... (interleaved: balanced)
-  a.work_step = part_count;
-  a.n_work = part_index < total ? (total - part_index + part_count - 1) / part_count : 0;
+  fill_join_args(a, j, selfjoin_items(j.n, j.k_blocks, j.part_index, j.part_count, false));
   if (a.n_work == 0) return 0;
-  a.k_blocks = k_blocks;
-  a.pe.member = member_bitmap;
-  a.pe.pairs = pairs;
-  a.pe.cap = cap;
-  a.pe.count = pair_count;
-  a.pe.threshold = threshold;
 #ifdef OMR_UMMA_EXPERIMENTS
   a.n_stages = kStages;
   a.exp = 0;

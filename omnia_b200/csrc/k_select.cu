@@ -11,8 +11,6 @@
 //   exact_scan /  the fallback for queries whose certificate fails: every eligible row
 //   select_exact  is scored exactly, then the k nearest are selected
 //   merge_topk    G shards' local answers -> the global one
-//   pair_rescore  exact similarity for self-join candidate pairs
-//                 (internal/memory/consolidation/prefilter.go:117,128)
 #include "kernels.cuh"
 
 namespace omr {
@@ -504,20 +502,6 @@ __global__ void __launch_bounds__(256) merge_topk_kernel(const int64_t* __restri
   }
 }
 
-__global__ void __launch_bounds__(256) pair_rescore_kernel(ShardView sh, const PairCand* __restrict__ pairs,
-                                                           unsigned long long n_pairs, double* __restrict__ sim) {
-  const unsigned long long wid = (unsigned long long)blockIdx.x * 8 + (threadIdx.x >> 5);
-  const int lane = threadIdx.x & 31;
-  if (wid >= n_pairs) return;
-  const PairCand p = pairs[wid];
-  const float* a = sh.rows_f32 + (int64_t)p.a * sh.pitch;
-  const float* b = sh.rows_f32 + (int64_t)p.b * sh.pitch;
-  double dot = 0.0;
-  for (int i = lane; i < sh.dim; i += 32) dot += (double)a[i] * (double)b[i];
-  dot = warp_sum_d(dot);
-  if (lane == 0) sim[wid] = clamp_sim(dot / sqrt(sh.norm2[p.a] * sh.norm2[p.b]));
-}
-
 __global__ void __launch_bounds__(256) gather_rows_kernel(const __nv_bfloat16* __restrict__ src, int pitch,
                                                           const int32_t* __restrict__ idx, int64_t m,
                                                           __nv_bfloat16* __restrict__ dst) {
@@ -527,6 +511,18 @@ __global__ void __launch_bounds__(256) gather_rows_kernel(const __nv_bfloat16* _
   const uint4* s = reinterpret_cast<const uint4*>(src + (int64_t)idx[r] * pitch);
   uint4* d = reinterpret_cast<uint4*>(dst + r * pitch);
   for (int i = lane; i < pitch / 8; i += 32) d[i] = s[i];
+}
+
+// dst row r = src row idx[r], rows of `units` 8-byte words (compaction of the resident matrices and columns)
+__global__ void __launch_bounds__(256) gather_units_kernel(const uint2* __restrict__ src, int64_t units,
+                                                           const int32_t* __restrict__ idx, int64_t m,
+                                                           uint2* __restrict__ dst) {
+  const int64_t r = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (r >= m) return;
+  const uint2* s = src + (int64_t)idx[r] * units;
+  uint2* d = dst + r * units;
+  for (int64_t i = lane; i < units; i += 32) d[i] = s[i];
 }
 
 __global__ void iota_kernel(int32_t* p, int n) {
@@ -675,10 +671,11 @@ int launch_merge_topk(const int64_t* in_rows, const double* in_dist, int G, int 
   return 0;
 }
 
-int launch_pair_rescore(const ShardView& sh, const PairCand* pairs, unsigned long long n_pairs, double* sim,
-                        cudaStream_t st) {
-  if (n_pairs == 0) return 0;
-  pair_rescore_kernel<<<(unsigned)((n_pairs + 7) / 8), 256, 0, st>>>(sh, pairs, n_pairs, sim);
+int launch_gather_row_bytes(const void* src, size_t row_bytes, const int32_t* idx, int64_t m, void* dst, cudaStream_t st) {
+  if (m <= 0) return 0;
+  if (row_bytes % 8) return fail_msg(-1, "gather: row of %zu bytes is not a multiple of 8", row_bytes);
+  gather_units_kernel<<<(unsigned)((m + 7) / 8), 256, 0, st>>>(reinterpret_cast<const uint2*>(src), (int64_t)(row_bytes / 8), idx,
+                                                              m, reinterpret_cast<uint2*>(dst));
   OMR_CUDA_OK(cudaGetLastError());
   return 0;
 }

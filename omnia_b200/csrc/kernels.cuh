@@ -8,8 +8,9 @@
 namespace omr {
 
 // ---- ingest / query preparation (k_ingest.cu) ------------------------------
-int launch_ingest_rows(const float* src, int64_t n, int dim, int pitch, int64_t row0, __nv_bfloat16* rows_bf16,
-                       float* rows_f32, double* norm2, cudaStream_t st);
+// rows land at row0 + i, or at dst_rows[i] when given (device array); bad_flag as launch_prep_queries
+int launch_ingest_rows(const float* src, int64_t n, int dim, int pitch, int64_t row0, const int64_t* dst_rows,
+                       __nv_bfloat16* rows_bf16, float* rows_f32, double* norm2, int32_t* bad_flag, cudaStream_t st);
 // bad_flag (nullable): set to 1 / 2 when a query holds a NaN / an infinite element
 int launch_prep_queries(const float* q, int nq, int qpad, int dim, int pitch, __nv_bfloat16* qn, double* qnorm2,
                         int32_t* bad_flag, cudaStream_t st);
@@ -59,9 +60,10 @@ int launch_score_umma2_emit(const CUtensorMap& tmap_q, const CUtensorMap& tmap_r
                             int n_tiles, int k_blocks, const uint32_t* bitmaps, int words_per_group,
                             const int32_t* query_group, const EmitView& ev, unsigned long long* timer, int num_sms,
                             cudaStream_t st);
-// `timer` (nullable, device): [0] receives the earliest CTA start and [1] the latest CTA end of the launch in
-// %globaltimer nanoseconds ([0] must start at ~0ull, [1] at 0): the kernel's own duration even when it queued
-// behind another batch's kernels, which stream events around it cannot tell apart.
+// `timer` (nullable, device, 4 words): [0] receives the earliest and [2] the latest CTA start, [1] the latest and
+// [3] the earliest CTA end of the launch in %globaltimer nanoseconds ([0] and [3] must start at ~0ull, [1] and [2]
+// at 0): the kernel's own duration even when it queued behind another batch's kernels, which stream events
+// around it cannot tell apart, and how ragged its start and its end were.
 // Per query: keep the list entries within `band` of the k-th best approximate score, rescore them exactly
 // from the fp32 master (best K2 first, then whatever the exact k-th distance found so far still allows),
 // ORDER BY distance LIMIT k with the cutoff, and clear the list for the lane's next batch (k_emit.cu).
@@ -186,16 +188,34 @@ int launch_exchange_merge(const ExchangeView& x, int slot, unsigned long long ep
 struct PairCand {
   int32_t a, b;
 };
-int launch_selfjoin_umma(const CUtensorMap& tmap_a, const CUtensorMap& tmap_b, int64_t n, int k_blocks,
-                         int part_index, int part_count, float threshold, const uint32_t* member_bitmap, PairCand* pairs, unsigned long long cap,
-                         unsigned long long* pair_count, int num_sms, cudaStream_t st);
+// One launch of the join kernel over a contiguous range of one partition's work items.
+struct JoinLaunch {
+  int64_t n = 0;            // member rows (compact index space)
+  int k_blocks = 0;
+  int part_index = 0, part_count = 1;
+  float threshold = 0.0f;   // floor - margin
+  const uint32_t* member_bitmap = nullptr;
+  PairCand* pairs = nullptr;
+  unsigned long long cap = 0;
+  unsigned long long* pair_count = nullptr;
+  // LIMIT mode (limit > 0): running cut from a histogram of the emitted pairs' approximate scores
+  int limit = 0;
+  int32_t* run_cut = nullptr;      // ordered-int image; starts at kOrderedNegInf
+  unsigned int* ghist = nullptr;   // [kJoinHistBins], zeroed
+  const uint16_t* kind = nullptr;  // per member row; nullptr = no kind rule
+  float hist_lo = 0.0f, hist_scale = 0.0f, band = 0.0f;
+  // this launch: items [chunk_first, chunk_first + chunk_items) of the partition (chunk_items < 0 = to the end)
+  int64_t chunk_first = 0, chunk_items = -1;
+};
+constexpr int kJoinHistBins = 2048;
+int64_t selfjoin_items(int64_t n, int k_blocks, int part_index, int part_count, bool pair_kernel);
+int launch_selfjoin_umma(const CUtensorMap& tmap_a, const CUtensorMap& tmap_b, const JoinLaunch& j, int num_sms,
+                         cudaStream_t st);
 // the same join on CTA pairs (cta_group::2, A and B tiles of 256 rows); tmap_half has a 128-row box
-int launch_selfjoin_umma2(const CUtensorMap& tmap_half, int64_t n, int k_blocks, int part_index, int part_count,
-                          float threshold, const uint32_t* member_bitmap, PairCand* pairs, unsigned long long cap,
-                          unsigned long long* pair_count, int num_sms, cudaStream_t st);
-int launch_pair_rescore(const ShardView& sh, const PairCand* pairs, unsigned long long n_pairs, double* sim,
-                        cudaStream_t st);
+int launch_selfjoin_umma2(const CUtensorMap& tmap_half, const JoinLaunch& j, int num_sms, cudaStream_t st);
 int launch_gather_rows(const ShardView& sh, const int32_t* idx, int64_t m, __nv_bfloat16* dst, cudaStream_t st);
+// dst row r = src row idx[r] for rows of row_bytes (a multiple of 8) bytes; dst must not overlap src
+int launch_gather_row_bytes(const void* src, size_t row_bytes, const int32_t* idx, int64_t m, void* dst, cudaStream_t st);
 
 // ---- PCA moments / projection over resident rows (k_pca.cu) -------------------
 int pca_mean_chunks(int64_t n);

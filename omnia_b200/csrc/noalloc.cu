@@ -11,8 +11,9 @@
 //
 // It is a variant of the engine's exact fallback (exact_scan_kernel + select_exact_kernel
 // in k_select.cu): same arithmetic (fp32 inputs, fp64 products and sums, pgvector's
-// 1 - clamp(dot / sqrt(na * nb))), same (distance, row) order, but on caller-owned rows with
-// the row norms computed on the fly.  Nothing in the existing code paths changes.
+// 1 - clamp(dot / sqrt(na * nb))), same (distance, row) order -- rows tied at the k-th distance
+// are taken smallest row number first, by an ordered scan, never by arrival order -- but on
+// caller-owned rows with the row norms computed on the fly.  Nothing in the existing code paths changes.
 //
 // Sharing and ordering rules for users of this entry point:
 //  * All calls on one GPU share the one array, and it keeps whatever the previous call left.
@@ -83,7 +84,7 @@ __global__ void __launch_bounds__(1024) noalloc_select_kernel(const unsigned cha
                                                               int32_t* __restrict__ out_count) {
   __shared__ uint32_t hist[256];
   __shared__ unsigned long long s_prefix, s_mask;
-  __shared__ uint32_t s_need, s_out, s_eq;
+  __shared__ uint32_t s_need, s_out;
   __shared__ double sd[kMaxK];
   __shared__ int64_t sr[kMaxK];
   const unsigned long long finite = *reinterpret_cast<const unsigned long long*>(scratch);
@@ -100,7 +101,6 @@ __global__ void __launch_bounds__(1024) noalloc_select_kernel(const unsigned cha
     s_mask = 0;
     s_need = (uint32_t)k;
     s_out = 0;
-    s_eq = 0;
   }
   __syncthreads();
   unsigned long long T = kInf - 1;
@@ -131,12 +131,27 @@ __global__ void __launch_bounds__(1024) noalloc_select_kernel(const unsigned cha
     T = s_prefix;
     need_eq = s_need;
   }
-  for (int64_t i = threadIdx.x; i < n; i += blockDim.x) {
-    const unsigned long long u = d[i];
-    if (u >= kInf) continue;
-    bool take = u < T;
-    if (u == T) take = atomicAdd(&s_eq, 1u) < need_eq;
-    if (finite <= (unsigned long long)k) take = true;
+  // Rows strictly nearer than T are all taken.  Of the rows AT distance T exactly `need_eq` are taken, and they
+  // are the ones with the smallest row numbers: the block walks the rows in order and every tied row learns how
+  // many tied rows precede it (ballot inside the warp, per-warp counts across the block), so the answer is the
+  // same on every run even when exact duplicates straddle the k-th place.
+  __shared__ uint32_t s_warp_ties[32];
+  __shared__ uint32_t s_tie_base;
+  if (threadIdx.x == 0) s_tie_base = 0;
+  __syncthreads();
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+  const bool all_rank = finite <= (unsigned long long)k;
+  for (int64_t i0 = 0; i0 < n; i0 += blockDim.x) {
+    const int64_t i = i0 + threadIdx.x;
+    const unsigned long long u = i < n ? d[i] : kInf;
+    const bool fin = u < kInf;
+    const bool tie = fin && !all_rank && u == T;
+    const uint32_t ballot = __ballot_sync(0xffffffffu, tie);
+    if (lane == 0) s_warp_ties[wid] = __popc(ballot);
+    __syncthreads();
+    uint32_t before = s_tie_base + __popc(ballot & ((1u << lane) - 1u));
+    for (int w = 0; w < wid; w++) before += s_warp_ties[w];
+    const bool take = fin && (all_rank || u < T || (tie && before < need_eq));
     if (take) {
       const uint32_t o = atomicAdd(&s_out, 1u);
       if (o < (uint32_t)P) {
@@ -144,6 +159,13 @@ __global__ void __launch_bounds__(1024) noalloc_select_kernel(const unsigned cha
         sr[o] = i;
       }
     }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      uint32_t t = 0;
+      for (int w = 0; w < nwarps; w++) t += s_warp_ties[w];
+      s_tie_base += t;
+    }
+    __syncthreads();
   }
   for (int size = 2; size <= P; size <<= 1) {
     for (int stride = size >> 1; stride > 0; stride >>= 1) {

@@ -44,6 +44,20 @@ extern bool g_force_ldg_stream;
 int launch_iota(int32_t* p, int n, cudaStream_t st);
 int launch_fill_empty(int64_t* rows, double* dist, int32_t* count, int nq, int k, cudaStream_t st);
 int launch_pair_remap(PairCand* pairs, unsigned long long n, const int32_t* remap, cudaStream_t st);
+// k_join.cu
+int join_scan_blocks(int64_t n);
+int launch_join_member_scan(const RowMetaView& meta, int64_t n, uint32_t workspace, int require_mutable, uint32_t* bitmap,
+                            int32_t* block_counts, int32_t* block_offsets, int64_t* d_total, cudaStream_t st);
+int launch_join_member_scatter(const uint32_t* bitmap, int64_t n, const int32_t* block_offsets, const uint16_t* kind,
+                               int32_t* idx, uint16_t* kind_c, cudaStream_t st);
+int launch_compact_member_bits(int64_t m, int64_t words, uint32_t* bits, cudaStream_t st);
+size_t join_select_state_bytes();
+int launch_pair_keys(const ShardView& sh, PairCand* pairs, unsigned long long n_pairs, const void* entity_key,
+                     const uint16_t* kind, int require_same_kind, double floor_d, double* sim, void* keys,
+                     unsigned long long* n_valid, cudaStream_t st);
+int launch_pair_select(const PairCand* pairs, const double* sim, const void* keys, unsigned long long n_pairs, int limit,
+                       void* state, unsigned long long out_cap, PairCand* out_pairs, double* out_sim,
+                       unsigned long long* out_count, int num_sms, cudaStream_t st);
 
 namespace {
 
@@ -168,6 +182,7 @@ struct omr_store {
   float* d_conf = nullptr;
   uint8_t* d_flags = nullptr;
   int64_t* d_valid = nullptr;
+  unsigned long long* d_entity_key = nullptr;   // [cap][2]: the row's entity uuid as two big-endian words (memcmp order)
   CUtensorMap tmap_rows_b{}, tmap_rows_a{};
 
   // host mirrors and identity maps
@@ -236,15 +251,31 @@ struct omr_store {
   DevBuf<uint32_t> w_bitmaps, w_live, w_member;
   DevBuf<int64_t> w_out_rows;
   DevBuf<DeviceFilter> w_filters;
-  DevBuf<PairCand> w_pairs;
-  DevBuf<unsigned long long> w_pair_count;
+  // ---- self-join (its own stream and scratch: recall keeps running while a join is in flight) ----
+  DevBuf<PairCand> w_pairs, w_out_pairs;
+  DevBuf<unsigned long long> w_pair_count;   // [0] candidates, [1] valid pairs, [2] selected pairs
   DevBuf<__nv_bfloat16> w_gather;
+  DevBuf<int32_t> w_jcounts, w_joffsets, w_run_cut;
+  DevBuf<int64_t> w_jtotal;
+  DevBuf<uint16_t> w_kind_c;
+  DevBuf<uint32_t> w_jbits, w_ghist;
+  DevBuf<unsigned long long> w_keys;
+  DevBuf<uint8_t> w_jstate;
+  DevBuf<double> w_out_sim;
+  PinBuf<unsigned long long> jpin;
+  cudaStream_t jstream = nullptr;
+  cudaEvent_t jev0 = nullptr, jev1 = nullptr, jchunk[2] = {nullptr, nullptr};
+  // Lock order: join_gate, then mu.  A join holds join_gate from start to end and mu only while it reads or
+  // writes host state; every call that changes rows takes join_gate first, so it waits for a running join, while
+  // recall (mu only) proceeds beside it.
+  std::mutex join_gate;
+  int selfjoin(const omr_selfjoin_opts* o, std::vector<PairCand>* pairs, std::vector<double>* sims);
   PinBuf<uint8_t> pin_in, pin_out;
   bool live_dirty = true;
   bool post_timing = false;  // OMR_POST_TIMING=1: per-phase clock stamps of the fused post kernel
   bool legacy_post = false;  // OMR_LEGACY_POST=1: use the unfused select/rescore/finalize chain
 
-  std::atomic<int64_t> st_launches{0}, st_searches{0}, st_queries{0}, st_rescued{0}, st_fallback{0}, st_listed{0};
+  std::atomic<int64_t> st_launches{0}, st_searches{0}, st_queries{0}, st_rescued{0}, st_fallback{0}, st_listed{0}, st_join_candidates{0};
   // Coalescing of concurrent host calls (dedup-on-write micro-batching): while one
   // search runs, the calls that arrive queue up and the next leader takes them all as ONE batch.
   struct HostReq {
@@ -269,7 +300,8 @@ struct omr_store {
   void run_batch(std::vector<HostReq*>& batch);
   // optional device timing of the dominant kernel (the approximate scorer), for bench.py's roofline
   bool profiling = false;
-  double scorer_ms_sum = 0.0, phase_ms_sum[3] = {0.0, 0.0, 0.0}, kernel_ns_sum = 0.0;
+  double scorer_ms_sum = 0.0, phase_ms_sum[3] = {0.0, 0.0, 0.0}, kernel_ns_sum = 0.0, kernel_start_skew_ns = 0.0,
+         kernel_end_skew_ns = 0.0;
   int64_t scorer_timed = 0, kernel_ns_n = 0;
   int last_path = 0, last_S = 0, last_K2 = 0;
 
@@ -291,7 +323,13 @@ struct omr_store {
 
   int open();
   void destroy();
-  int append(int64_t count, const float* vecs, int64_t row0);
+  int append(int64_t count, const float* vecs, int64_t row0, const int64_t* dst = nullptr);
+  void release_row(int64_t r);
+  int64_t recycle_row(std::vector<int64_t>* touched);
+  int compact(int64_t* reclaimed);
+  std::vector<int64_t> free_rows;   // hard-deleted slots waiting for a new tenant (entries may be stale: see recycle_row)
+  DevBuf<int32_t> w_bad, w_cidx;
+  DevBuf<int64_t> w_dst;
   int push_meta(int64_t row0, int64_t count);
   int push_flag(int64_t row);
   int to_device_filter(const omr_filter& f, DeviceFilter* out, double* maxd);
@@ -336,6 +374,11 @@ int omr_store::open() {
   OMR_CUDA_OK(cudaMalloc(&d_conf, c * 4));
   OMR_CUDA_OK(cudaMalloc(&d_flags, c));
   OMR_CUDA_OK(cudaMalloc(&d_valid, c * 8));
+  OMR_CUDA_OK(cudaMalloc(&d_entity_key, c * 16));
+  OMR_CUDA_OK(cudaStreamCreateWithFlags(&jstream, cudaStreamNonBlocking));
+  OMR_CUDA_OK(cudaEventCreate(&jev0));
+  OMR_CUDA_OK(cudaEventCreate(&jev1));
+  for (cudaEvent_t& e : jchunk) OMR_CUDA_OK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
   OMR_CUDA_OK(cudaMemset(d_bf16, 0, c * pitch * sizeof(__nv_bfloat16)));
   OMR_CUDA_OK(cudaMemset(d_f32, 0, c * pitch * sizeof(float)));
   OMR_CUDA_OK(cudaMemset(d_norm2, 0, c * sizeof(double)));
@@ -352,7 +395,7 @@ int omr_store::open() {
     OMR_CUDA_OK(cudaEventCreate(&L.ev0));
     OMR_CUDA_OK(cudaEventCreate(&L.ev1));
     for (cudaEvent_t& e : L.ph) OMR_CUDA_OK(cudaEventCreate(&e));
-    if ((rc = L.pin.reserve(8))) return rc;
+    if ((rc = L.pin.reserve(12))) return rc;
     if ((rc = L.counters.reserve(8))) return rc;
   }
   return 0;
@@ -361,7 +404,8 @@ int omr_store::open() {
 void omr_store::destroy() {
   cudaSetDevice(cfg.device);
   if (stream) cudaStreamSynchronize(stream);
-  void* ptrs[] = {d_bf16, d_f32, d_norm2, d_ws, d_user, d_agent, d_kind, d_purpose, d_conf, d_flags, d_valid};
+  if (jstream) cudaStreamSynchronize(jstream);
+  void* ptrs[] = {d_bf16, d_f32, d_norm2, d_ws, d_user, d_agent, d_kind, d_purpose, d_conf, d_flags, d_valid, d_entity_key};
   for (void* p : ptrs)
     if (p) cudaFree(p);
   for (Lane& L : lanes) {
@@ -385,6 +429,13 @@ void omr_store::destroy() {
   w_idx.release(); w_sel_bound.release(); w_queries.release(); w_stage.release(); w_bitmaps.release();
   w_live.release(); w_member.release(); w_out_rows.release(); w_filters.release(); w_pairs.release();
   w_pair_count.release(); w_gather.release();
+  w_bad.release(); w_dst.release(); w_cidx.release();
+  w_out_pairs.release(); w_jcounts.release(); w_joffsets.release(); w_run_cut.release(); w_jtotal.release();
+  w_kind_c.release(); w_jbits.release(); w_ghist.release(); w_keys.release(); w_jstate.release(); w_out_sim.release();
+  jpin.release();
+  for (cudaEvent_t e : {jev0, jev1, jchunk[0], jchunk[1]})
+    if (e) cudaEventDestroy(e);
+  if (jstream) cudaStreamDestroy(jstream);
   pin_in.release(); pin_out.release();
   if (stream) cudaStreamDestroy(stream);
 }
@@ -401,6 +452,20 @@ int omr_store::push_meta(int64_t row0, int64_t count) {
   OMR_CUDA_OK(cudaMemcpyAsync(d_conf + row0, h_conf.data() + row0, c * 4, cudaMemcpyHostToDevice, stream));
   OMR_CUDA_OK(cudaMemcpyAsync(d_flags + row0, h_flags.data() + row0, c, cudaMemcpyHostToDevice, stream));
   OMR_CUDA_OK(cudaMemcpyAsync(d_valid + row0, h_valid.data() + row0, c * 8, cudaMemcpyHostToDevice, stream));
+  // the row's entity uuid as two big-endian words, so that an unsigned compare on the device is Postgres' memcmp
+  std::vector<unsigned long long> ek(2 * c);
+  for (size_t i = 0; i < c; i++) {
+    uint8_t b[16];
+    key_to(entity_id[h_entity[row0 + (int64_t)i]], b);
+    unsigned long long hi = 0, lo = 0;
+    for (int j = 0; j < 8; j++) {
+      hi = (hi << 8) | b[j];
+      lo = (lo << 8) | b[8 + j];
+    }
+    ek[2 * i] = hi;
+    ek[2 * i + 1] = lo;
+  }
+  OMR_CUDA_OK(cudaMemcpyAsync(d_entity_key + 2 * row0, ek.data(), c * 16, cudaMemcpyHostToDevice, stream));
   OMR_CUDA_OK(cudaStreamSynchronize(stream));
   live_dirty = true;
   return 0;
@@ -412,20 +477,136 @@ int omr_store::push_flag(int64_t row) {
   return 0;
 }
 
-// Streams `count` host vectors through a bounded staging buffer into rows [row0, row0+count).
-int omr_store::append(int64_t count, const float* vecs, int64_t row0) {
+// Streams `count` host vectors through a bounded staging buffer into rows [row0, row0+count), or into the rows
+// `dst` names (host array, any order).  pgvector refuses NaN and infinite elements when a vector is parsed; the
+// ingest kernel flags them and the call fails with pgvector's message (the rows written so far are the caller's to
+// discard: bulk loads write beyond `n` before they publish anything).
+int omr_store::append(int64_t count, const float* vecs, int64_t row0, const int64_t* dst) {
   const int64_t chunk = std::max<int64_t>(1, (int64_t)(64u << 20) / ((int64_t)dim * 4));
   int rc = w_stage.reserve((size_t)std::min(chunk, count) * dim);
   if (rc) return rc;
+  if ((rc = w_bad.reserve(1))) return rc;
+  if (dst && (rc = w_dst.reserve((size_t)std::min(chunk, count)))) return rc;
+  OMR_CUDA_OK(cudaMemsetAsync(w_bad.p, 0, 4, stream));
   for (int64_t off = 0; off < count; off += chunk) {
     const int64_t c = std::min(chunk, count - off);
     OMR_CUDA_OK(cudaMemcpyAsync(w_stage.p, vecs + off * dim, (size_t)c * dim * 4, cudaMemcpyHostToDevice, stream));
-    rc = launch_ingest_rows(w_stage.p, c, dim, pitch, row0 + off, d_bf16, d_f32, d_norm2, stream);
+    if (dst) OMR_CUDA_OK(cudaMemcpyAsync(w_dst.p, dst + off, (size_t)c * 8, cudaMemcpyHostToDevice, stream));
+    rc = launch_ingest_rows(w_stage.p, c, dim, pitch, row0 + off, dst ? w_dst.p : nullptr, d_bf16, d_f32, d_norm2, w_bad.p,
+                            stream);
     if (rc) return rc;
     st_launches++;
     OMR_CUDA_OK(cudaStreamSynchronize(stream));
   }
+  int32_t bad = 0;
+  OMR_CUDA_OK(cudaMemcpy(&bad, w_bad.p, 4, cudaMemcpyDeviceToHost));
+  if (bad & 1) return fail_msg(OMR_E_INVALID, "memory: NaN not allowed in vector");
+  if (bad & 2) return fail_msg(OMR_E_INVALID, "memory: infinite value not allowed in vector");
   return 0;
+}
+
+// A hard-deleted row goes on the free list (once); omr_upsert hands the slot to the next new observation.
+void omr_store::release_row(int64_t r) {
+  if (h_flags[r] & kRowFree) return;
+  h_flags[r] |= kRowFree;
+  free_rows.push_back(r);
+}
+
+// Takes a slot off the free list for a NEW observation: the old tenant leaves the identity maps.  -1 = none free.
+int64_t omr_store::recycle_row(std::vector<int64_t>* touched) {
+  while (!free_rows.empty()) {
+    const int64_t r = free_rows.back();
+    free_rows.pop_back();
+    if (r >= n || !(h_flags[r] & kRowFree)) continue;   // resurrected in place by its own observation id, or compacted away
+    auto it = obs_row.find(obs_id[r]);
+    if (it != obs_row.end() && it->second == r) obs_row.erase(it);
+    const uint32_t ent = h_entity[r];
+    auto& rows = entity_rows[ent];
+    rows.erase(std::remove(rows.begin(), rows.end(), r), rows.end());
+    if (entity_latest[ent] == r) {
+      // the entity's representative is its newest live embedded row, as after a merge
+      int64_t rep = -1;
+      for (int64_t x : rows)
+        if (!(h_flags[x] & kRowDeleted) && x > rep) rep = x;
+      entity_latest[ent] = rep;
+      if (rep >= 0) {
+        h_flags[rep] |= kRowEntityRep;
+        touched->push_back(rep);
+      }
+    }
+    h_flags[r] = 0;
+    return r;
+  }
+  return -1;
+}
+
+
+// Compaction: every hard-deleted row leaves the shard, the rows behind it move down (order kept), and the
+// identity maps follow.  Rows only ever move to a lower index, so the matrices are rewritten in place, a
+// chunk at a time through a staging buffer: the sources of a later chunk all lie behind the chunk being written.
+int omr_store::compact(int64_t* reclaimed) {
+  std::vector<int32_t> keep;
+  keep.reserve((size_t)n);
+  for (int64_t r = 0; r < n; r++)
+    if (!(h_flags[r] & kRowDeleted)) keep.push_back((int32_t)r);
+  const int64_t m = (int64_t)keep.size();
+  *reclaimed = n - m;
+  free_rows.clear();
+  if (m == n) return 0;
+  int64_t f = 0;
+  while (f < m && keep[(size_t)f] == f) f++;   // rows before the first hole stay where they are
+  int rc;
+  if (m > f) {
+    if ((rc = w_cidx.reserve((size_t)(m - f)))) return rc;
+    OMR_CUDA_OK(cudaMemcpyAsync(w_cidx.p, keep.data() + f, (size_t)(m - f) * 4, cudaMemcpyHostToDevice, stream));
+    const int64_t chunk = std::max<int64_t>(256, (int64_t)(64u << 20) / ((int64_t)pitch * 4));
+    if ((rc = w_stage.reserve((size_t)std::min(chunk, m - f) * pitch))) return rc;
+    struct Col { void* base; size_t row_bytes; };
+    const Col cols[] = {{d_f32, (size_t)pitch * 4}, {d_bf16, (size_t)pitch * 2}, {d_norm2, 8}};
+    for (const Col& c : cols) {
+      for (int64_t d0 = f; d0 < m; d0 += chunk) {
+        const int64_t cnt = std::min(chunk, m - d0);
+        if ((rc = launch_gather_row_bytes(c.base, c.row_bytes, w_cidx.p + (d0 - f), cnt, w_stage.p, stream))) return rc;
+        OMR_CUDA_OK(cudaMemcpyAsync(reinterpret_cast<uint8_t*>(c.base) + (size_t)d0 * c.row_bytes, w_stage.p,
+                                    (size_t)cnt * c.row_bytes, cudaMemcpyDeviceToDevice, stream));
+        st_launches++;
+      }
+    }
+  }
+  // the vacated tail reads as empty rows
+  OMR_CUDA_OK(cudaMemsetAsync(d_flags + m, 0, (size_t)(n - m), stream));
+  OMR_CUDA_OK(cudaMemsetAsync(d_norm2 + m, 0, (size_t)(n - m) * 8, stream));
+  OMR_CUDA_OK(cudaMemsetAsync(d_bf16 + (size_t)m * pitch, 0, (size_t)(n - m) * pitch * 2, stream));
+  OMR_CUDA_OK(cudaStreamSynchronize(stream));
+  // host mirrors and identity maps
+  std::vector<int64_t> newpos((size_t)n, -1);
+  for (int64_t i = 0; i < m; i++) newpos[(size_t)keep[(size_t)i]] = i;
+  for (int64_t i = f; i < m; i++) {
+    const int64_t o = keep[(size_t)i];
+    h_ws[i] = h_ws[o]; h_user[i] = h_user[o]; h_agent[i] = h_agent[o]; h_entity[i] = h_entity[o];
+    h_kind[i] = h_kind[o]; h_purpose[i] = h_purpose[o]; h_conf[i] = h_conf[o]; h_flags[i] = h_flags[o];
+    h_valid[i] = h_valid[o]; obs_id[i] = obs_id[o];
+  }
+  obs_row.clear();
+  for (auto& rows : entity_rows) rows.clear();
+  for (int64_t i = 0; i < m; i++) {
+    obs_row[obs_id[i]] = i;
+    entity_rows[h_entity[i]].push_back(i);
+  }
+  for (size_t e = 0; e < entity_latest.size(); e++) {
+    const int64_t old = entity_latest[e];
+    int64_t rep = old >= 0 ? newpos[(size_t)old] : -1;
+    if (rep < 0 && !entity_rows[e].empty()) {   // its representative was deleted: the newest surviving row takes over
+      rep = entity_rows[e].back();
+      h_flags[rep] |= kRowEntityRep;
+    }
+    entity_latest[e] = rep;
+  }
+  const size_t t = (size_t)m;
+  h_ws.resize(t); h_user.resize(t); h_agent.resize(t); h_entity.resize(t); h_kind.resize(t); h_purpose.resize(t);
+  h_conf.resize(t); h_flags.resize(t); h_valid.resize(t); obs_id.resize(t);
+  n = m;
+  return push_meta(0, n);
 }
 
 int omr_store::to_device_filter(const omr_filter& f, DeviceFilter* out, double* maxd) {
@@ -668,9 +849,10 @@ int omr_store::enqueue(Lane& L, const float* d_q, int nq, const uint32_t* d_bitm
         if (profiling) {   // time the full-store scorer, not its seed: events on the stream and, since those also
                            // count the time the kernel queued behind another batch, the kernel's own %globaltimer span
           OMR_CUDA_OK(cudaEventRecord(L.ev0, st));
-          if ((rc = L.ktimer.reserve(2))) return rc;
+          if ((rc = L.ktimer.reserve(4))) return rc;
+          OMR_CUDA_OK(cudaMemsetAsync(L.ktimer.p, 0, 32, st));
           OMR_CUDA_OK(cudaMemsetAsync(L.ktimer.p, 0xFF, 8, st));
-          OMR_CUDA_OK(cudaMemsetAsync(L.ktimer.p + 1, 0, 8, st));
+          OMR_CUDA_OK(cudaMemsetAsync(L.ktimer.p + 3, 0xFF, 8, st));
           timer = L.ktimer.p;
         }
         if (path == 4)
@@ -680,7 +862,7 @@ int omr_store::enqueue(Lane& L, const float* d_q, int nq, const uint32_t* d_bitm
           rc = launch_score_umma_emit(L.tmap_q, tmap_rows_b, nq, qpad / kQueryTile, n_tiles, pitch / kBlockK, d_bitmaps,
                                       wpg, d_qgroup, ev, timer, num_sms, st);
         if (!rc && timer)
-          OMR_CUDA_OK(cudaMemcpyAsync(L.pin.p + 4, L.ktimer.p, 16, cudaMemcpyDeviceToHost, st));
+          OMR_CUDA_OK(cudaMemcpyAsync(L.pin.p + 4, L.ktimer.p, 32, cudaMemcpyDeviceToHost, st));
       } else if (path == 4)
         rc = launch_score_umma2(L.tmap_q, tmap_rows_a, nq, qpad / (2 * kQueryTile), n_tiles, pitch / kBlockK, S, d_bitmaps, wpg,
                                 d_qgroup, L.cand.p, num_sms, st);
@@ -762,10 +944,12 @@ int omr_store::complete(Lane& L, cudaStream_t st) {
       scorer_ms_sum += ms;
       scorer_timed++;
       if (L.phased) {   // seed pass | seed thresholds | (scorer, above) | post kernel
-        unsigned long long t01[2];
-        memcpy(t01, L.pin.p + 4, 16);
+        unsigned long long t01[4];
+        memcpy(t01, L.pin.p + 4, 32);
         if (t01[1] > t01[0]) {
           kernel_ns_sum += (double)(t01[1] - t01[0]);
+          kernel_start_skew_ns += (double)(t01[2] - t01[0]);
+          kernel_end_skew_ns += (double)(t01[1] - t01[3]);
           kernel_ns_n++;
         }
         float a = 0, b = 0, c = 0;
@@ -1110,6 +1294,7 @@ int omr_bulk_load(omr_store* s, const omr_bulk* b) {
   if (!s || !b) return fail_msg(OMR_E_INVALID, "memory: omr_bulk_load: null argument");
   if (b->n <= 0) return OMR_OK;
   if (!b->vectors) return fail_msg(OMR_E_INVALID, "memory: omr_bulk_load: vectors is null");
+  std::lock_guard<std::mutex> gate(s->join_gate);   // rows do not change under a running self-join
   std::lock_guard<std::mutex> lk(s->mu);
   cudaSetDevice(s->cfg.device);
   if (int drc = s->drain()) return drc;
@@ -1158,38 +1343,53 @@ int omr_bulk_load(omr_store* s, const omr_bulk* b) {
     s->h_valid[r] = b->valid_until_us ? b->valid_until_us[i] : OMR_NO_EXPIRY;
     s->obs_id[r] = b->observation_ids ? key_of(b->observation_ids + 16 * i) : key_from_index(r);
   }
-  // identity maps (after validation, so a rejected batch leaves no trace)
+  // The vectors go in first, into rows beyond `n` that nothing can see yet: a NaN or an infinite element fails the
+  // whole load, as the statement would fail in Postgres, and leaves no trace.
+  int rc = s->append(b->n, b->vectors, row0);
+  if (rc) {
+    grow_host(s, row0);
+    return rc;
+  }
+  // identity maps (after validation, so a rejected batch leaves no trace).  An observation id that is already
+  // resident -- in the store or earlier in this batch -- is superseded by the new row: the old row is
+  // hard-deleted (UpdateObservationEmbedding keeps one row per observation, store_write.go:580-600).
   for (int64_t i = 0; i < b->n; i++) {
     const int64_t r = row0 + i;
+    auto old = s->obs_row.find(s->obs_id[r]);
+    if (old != s->obs_row.end() && old->second != r) {
+      const int64_t o = old->second;
+      s->h_flags[o] = (uint8_t)((s->h_flags[o] | kRowDeleted) & ~OMR_ROW_HAS_EMBEDDING);
+      s->release_row(o);
+    }
     s->obs_row[s->obs_id[r]] = r;
     const Key128 e = b->entity_ids ? key_of(b->entity_ids + 16 * i) : s->obs_id[r];
     attach_row(s, r, entity_of(s, e));
   }
   s->n = row0 + b->n;
-  int rc = s->push_meta(0, s->n);  // earlier rows may have lost their EntityRep bit
-  if (rc) return rc;
-  rc = s->append(b->n, b->vectors, row0);
+  rc = s->push_meta(0, s->n);  // earlier rows may have lost their EntityRep bit
   if (rc) return rc;
   s->live_dirty = true;
   return OMR_OK;
 }
 
-int omr_upsert(omr_store* s, const omr_row* row, const float* vec, int32_t dim) {
-  if (!s || !row || !vec) return fail_msg(OMR_E_INVALID, "memory: omr_upsert: null argument");
-  if (dim != s->dim) return fail_msg(OMR_E_DIM, "memory: embedding dimension mismatch: got %d, store has %d", dim, s->dim);
+// Host half of an upsert: picks the row (in place for a resident observation id, else a reclaimed slot, else a new
+// row at the end), fills the host mirrors and the identity maps.  `also` collects other rows whose flags changed.
+static int upsert_host(omr_store* s, const omr_row* row, int64_t* row_out, std::vector<int64_t>* also) {
   if (!row->workspace_id || !row->workspace_id[0]) return fail_msg(OMR_E_WORKSPACE, "memory: workspace_id is required");
-  if (int frc = check_finite(vec, (size_t)dim)) return frc;
-  std::lock_guard<std::mutex> lk(s->mu);
-  cudaSetDevice(s->cfg.device);
-  if (int drc = s->drain()) return drc;
   const Key128 ok = key_of(row->observation_id);
   int64_t r;
   auto it = s->obs_row.find(ok);
   const bool fresh = it == s->obs_row.end();
+  bool appended = false;
   if (fresh) {
-    if (s->n + 1 > s->cfg.capacity) return fail_msg(OMR_E_CAPACITY, "memory: gpu store is full (%lld rows)", (long long)s->n);
-    r = s->n;
-    grow_host(s, r + 1);
+    r = s->recycle_row(also);  // the slot of a hard-deleted row, if one waits
+    if (r < 0) {
+      if (s->n + 1 > s->cfg.capacity)
+        return fail_msg(OMR_E_CAPACITY, "memory: gpu store is full (%lld rows, none reclaimable)", (long long)s->n);
+      r = s->n;
+      grow_host(s, r + 1);
+      appended = true;
+    }
     s->obs_id[r] = ok;
     s->h_flags[r] = 0;
   } else {
@@ -1203,24 +1403,108 @@ int omr_upsert(omr_store* s, const omr_row* row, const float* vec, int32_t dim) 
   s->h_conf[r] = row->confidence;
   s->h_flags[r] = (uint8_t)((s->h_flags[r] & kRowEntityRep) | (row->flags & 0x0F) | OMR_ROW_HAS_EMBEDDING);
   s->h_valid[r] = row->valid_until_us;
-  int64_t lo = r, hi = r;
   if (fresh) {
     s->obs_row[ok] = r;
     const uint32_t ent = entity_of(s, key_of(row->entity_id));
     const int64_t prev = s->entity_latest[ent];
     attach_row(s, r, ent);
-    s->n = r + 1;
-    if (prev >= 0) lo = std::min(lo, prev);
+    if (appended) s->n = r + 1;
+    if (prev >= 0 && prev != r) also->push_back(prev);
   }
-  int rc = s->push_meta(lo, hi - lo + 1);
+  *row_out = r;
+  return OMR_OK;
+}
+
+int omr_upsert(omr_store* s, const omr_row* row, const float* vec, int32_t dim) {
+  if (!s || !row || !vec) return fail_msg(OMR_E_INVALID, "memory: omr_upsert: null argument");
+  if (dim != s->dim) return fail_msg(OMR_E_DIM, "memory: embedding dimension mismatch: got %d, store has %d", dim, s->dim);
+  if (!row->workspace_id || !row->workspace_id[0]) return fail_msg(OMR_E_WORKSPACE, "memory: workspace_id is required");
+  if (int frc = check_finite(vec, (size_t)dim)) return frc;
+  std::lock_guard<std::mutex> gate(s->join_gate);   // rows do not change under a running self-join
+  std::lock_guard<std::mutex> lk(s->mu);
+  cudaSetDevice(s->cfg.device);
+  if (int drc = s->drain()) return drc;
+  int64_t r;
+  std::vector<int64_t> also;
+  int rc = upsert_host(s, row, &r, &also);
   if (rc) return rc;
+  if ((rc = s->push_meta(r, 1))) return rc;
+  for (int64_t x : also)
+    if ((rc = s->push_flag(x))) return rc;
   return s->append(1, vec, r);
+}
+
+int omr_upsert_batch(omr_store* s, const omr_row* rows, const float* vecs, int32_t n, int32_t dim) {
+  if (!s || (n > 0 && (!rows || !vecs))) return fail_msg(OMR_E_INVALID, "memory: omr_upsert_batch: null argument");
+  if (n <= 0) return OMR_OK;
+  if (dim != s->dim) return fail_msg(OMR_E_DIM, "memory: embedding dimension mismatch: got %d, store has %d", dim, s->dim);
+  for (int32_t i = 0; i < n; i++)
+    if (!rows[i].workspace_id || !rows[i].workspace_id[0]) return fail_msg(OMR_E_WORKSPACE, "memory: workspace_id is required");
+  if (int frc = check_finite(vecs, (size_t)n * dim)) return frc;
+  std::lock_guard<std::mutex> gate(s->join_gate);
+  std::lock_guard<std::mutex> lk(s->mu);
+  cudaSetDevice(s->cfg.device);
+  if (int drc = s->drain()) return drc;
+  int rc;
+  std::vector<int64_t> dst((size_t)n), also;
+  for (int32_t i = 0; i < n; i++)
+    if ((rc = upsert_host(s, &rows[i], &dst[(size_t)i], &also))) return rc;   // rows before i stay upserted, as n single calls would
+  // an observation id given twice keeps its last vector: one writer per row in the ingest kernel
+  std::unordered_map<int64_t, int32_t> last;
+  for (int32_t i = 0; i < n; i++) last[dst[(size_t)i]] = i;
+  std::vector<float> picked;
+  const float* src = vecs;
+  std::vector<int64_t> rows_u;
+  if ((int32_t)last.size() != n) {
+    picked.reserve(last.size() * (size_t)dim);
+    for (int32_t i = 0; i < n; i++)
+      if (last[dst[(size_t)i]] == i) {
+        picked.insert(picked.end(), vecs + (size_t)i * dim, vecs + (size_t)(i + 1) * dim);
+        rows_u.push_back(dst[(size_t)i]);
+      }
+    src = picked.data();
+  } else {
+    rows_u = dst;
+  }
+  // metadata: one copy per run of consecutive rows (new rows are consecutive), single flags for the rest
+  std::vector<int64_t> sorted = rows_u;
+  std::sort(sorted.begin(), sorted.end());
+  for (size_t i = 0; i < sorted.size();) {
+    size_t j = i + 1;
+    while (j < sorted.size() && sorted[j] == sorted[j - 1] + 1) j++;
+    if ((rc = s->push_meta(sorted[i], (int64_t)(j - i)))) return rc;
+    i = j;
+  }
+  for (int64_t x : also)
+    if (x < s->n && (rc = s->push_flag(x))) return rc;
+  return s->append((int64_t)rows_u.size(), src, 0, rows_u.data());
+}
+
+int omr_compact(omr_store* s, int64_t* reclaimed) {
+  if (!s) return fail_msg(OMR_E_INVALID, "memory: omr_compact: null argument");
+  std::lock_guard<std::mutex> gate(s->join_gate);
+  std::lock_guard<std::mutex> lk(s->mu);
+  cudaSetDevice(s->cfg.device);
+  if (int drc = s->drain()) return drc;
+  int64_t got = 0;
+  const int rc = s->compact(&got);
+  if (reclaimed) *reclaimed = got;
+  return rc;
+}
+
+int64_t omr_free_slots(const omr_store* s) {
+  if (!s) return 0;
+  int64_t c = 0;
+  for (int64_t r : s->free_rows)
+    if (r < s->n && (s->h_flags[(size_t)r] & kRowFree)) c++;
+  return c;
 }
 
 int omr_update_embedding(omr_store* s, const uint8_t entity_id[16], const float* vec, int32_t dim) {
   if (!s || !entity_id || !vec) return fail_msg(OMR_E_INVALID, "memory: omr_update_embedding: null argument");
   if (dim != s->dim) return fail_msg(OMR_E_DIM, "memory: embedding dimension mismatch: got %d, store has %d", dim, s->dim);
   if (int frc = check_finite(vec, (size_t)dim)) return frc;
+  std::lock_guard<std::mutex> gate(s->join_gate);   // rows do not change under a running self-join
   std::lock_guard<std::mutex> lk(s->mu);
   cudaSetDevice(s->cfg.device);
   if (int drc = s->drain()) return drc;
@@ -1236,6 +1520,7 @@ int omr_update_embedding(omr_store* s, const uint8_t entity_id[16], const float*
 static int edit_rows(omr_store* s, const std::vector<int64_t>& rows, uint32_t set_mask, uint32_t clear_mask) {
   for (int64_t r : rows) {
     s->h_flags[r] = (uint8_t)((s->h_flags[r] | (set_mask & 0x4F)) & ~(clear_mask & 0x4F));
+    if (set_mask & kRowDeleted) s->release_row(r);
     int rc = s->push_flag(r);
     if (rc) return rc;
   }
@@ -1244,6 +1529,7 @@ static int edit_rows(omr_store* s, const std::vector<int64_t>& rows, uint32_t se
 
 int omr_set_row_flags(omr_store* s, const uint8_t observation_id[16], uint32_t set_mask, uint32_t clear_mask) {
   if (!s || !observation_id) return fail_msg(OMR_E_INVALID, "memory: null argument");
+  std::lock_guard<std::mutex> gate(s->join_gate);   // rows do not change under a running self-join
   std::lock_guard<std::mutex> lk(s->mu);
   cudaSetDevice(s->cfg.device);
   if (int drc = s->drain()) return drc;
@@ -1254,6 +1540,7 @@ int omr_set_row_flags(omr_store* s, const uint8_t observation_id[16], uint32_t s
 
 int omr_set_entity_flags(omr_store* s, const uint8_t entity_id[16], uint32_t set_mask, uint32_t clear_mask) {
   if (!s || !entity_id) return fail_msg(OMR_E_INVALID, "memory: null argument");
+  std::lock_guard<std::mutex> gate(s->join_gate);   // rows do not change under a running self-join
   std::lock_guard<std::mutex> lk(s->mu);
   cudaSetDevice(s->cfg.device);
   if (int drc = s->drain()) return drc;
@@ -1293,6 +1580,7 @@ int omr_delete_scope(omr_store* s, const char* workspace_id, const char* virtual
   if (deleted) *deleted = 0;
   if (!s) return fail_msg(OMR_E_INVALID, "memory: null argument");
   if (!workspace_id || !workspace_id[0]) return fail_msg(OMR_E_WORKSPACE, "memory: workspace_id is required");
+  std::lock_guard<std::mutex> gate(s->join_gate);   // rows do not change under a running self-join
   std::lock_guard<std::mutex> lk(s->mu);
   cudaSetDevice(s->cfg.device);
   if (int drc = s->drain()) return drc;
@@ -1310,6 +1598,7 @@ int omr_delete_scope(omr_store* s, const char* workspace_id, const char* virtual
     if (s->h_ws[r0] != ws || (by_user && s->h_user[r0] != user)) continue;
     for (int64_t r : rows) {
       s->h_flags[r] = (uint8_t)((s->h_flags[r] | kRowDeleted) & ~OMR_ROW_HAS_EMBEDDING);
+      s->release_row(r);
       touched.push_back(r);
     }
     count++;
@@ -1330,6 +1619,7 @@ int omr_delete_scope(omr_store* s, const char* workspace_id, const char* virtual
 int omr_rescope(omr_store* s, const uint8_t* observation_ids, int32_t n, const char* virtual_user_id,
                 const char* agent_id) {
   if (!s || (n > 0 && !observation_ids)) return fail_msg(OMR_E_INVALID, "memory: null argument");
+  std::lock_guard<std::mutex> gate(s->join_gate);   // rows do not change under a running self-join
   std::lock_guard<std::mutex> lk(s->mu);
   cudaSetDevice(s->cfg.device);
   if (int drc = s->drain()) return drc;
@@ -1354,6 +1644,7 @@ int omr_rescope(omr_store* s, const uint8_t* observation_ids, int32_t n, const c
 
 int omr_merge_entities(omr_store* s, const uint8_t canonical_id[16], const uint8_t* merge_ids, int32_t n) {
   if (!s || !canonical_id || (n > 0 && !merge_ids)) return fail_msg(OMR_E_INVALID, "memory: null argument");
+  std::lock_guard<std::mutex> gate(s->join_gate);   // rows do not change under a running self-join
   std::lock_guard<std::mutex> lk(s->mu);
   cudaSetDevice(s->cfg.device);
   if (int drc = s->drain()) return drc;
@@ -1402,6 +1693,7 @@ int omr_merge_entities(omr_store* s, const uint8_t canonical_id[16], const uint8
 
 int omr_clear(omr_store* s) {
   if (!s) return fail_msg(OMR_E_INVALID, "memory: null argument");
+  std::lock_guard<std::mutex> gate(s->join_gate);   // rows do not change under a running self-join
   std::lock_guard<std::mutex> lk(s->mu);
   cudaSetDevice(s->cfg.device);
   if (int drc = s->drain()) return drc;
@@ -1409,12 +1701,14 @@ int omr_clear(omr_store* s) {
   grow_host(s, 0);
   s->entity_id.clear(); s->entity_latest.clear(); s->entity_rows.clear();
   s->obs_row.clear(); s->entity_idx.clear();
+  s->free_rows.clear();
   s->live_dirty = true;
   return OMR_OK;
 }
 
 int omr_set_valid_until(omr_store* s, const uint8_t observation_id[16], int64_t valid_until_us) {
   if (!s || !observation_id) return fail_msg(OMR_E_INVALID, "memory: null argument");
+  std::lock_guard<std::mutex> gate(s->join_gate);   // rows do not change under a running self-join
   std::lock_guard<std::mutex> lk(s->mu);
   cudaSetDevice(s->cfg.device);
   if (int drc = s->drain()) return drc;
@@ -1427,6 +1721,7 @@ int omr_set_valid_until(omr_store* s, const uint8_t observation_id[16], int64_t 
 
 int omr_set_confidence(omr_store* s, const uint8_t observation_id[16], float confidence) {
   if (!s || !observation_id) return fail_msg(OMR_E_INVALID, "memory: null argument");
+  std::lock_guard<std::mutex> gate(s->join_gate);   // rows do not change under a running self-join
   std::lock_guard<std::mutex> lk(s->mu);
   cudaSetDevice(s->cfg.device);
   if (int drc = s->drain()) return drc;
@@ -1836,132 +2131,252 @@ int omr_device_merge_topk(omr_store* s, const int64_t* d_in_rows, const double* 
                            (cudaStream_t)stream);
 }
 
-int omr_selfjoin(omr_store* s, const omr_selfjoin_opts* o, omr_pair* out, int64_t cap, int64_t* found) {
-  if (!s || !o || !found || (cap > 0 && !out)) return fail_msg(OMR_E_INVALID, "memory: omr_selfjoin: null argument");
-  if (!o->workspace_id || !o->workspace_id[0]) return fail_msg(OMR_E_WORKSPACE, "memory: workspace_id is required");
-  std::lock_guard<std::mutex> lk(s->mu);
-  cudaSetDevice(s->cfg.device);
-  if (int drc = s->drain()) return drc;
-  *found = 0;
-  uint32_t ws;
-  if (!s->ws_names.lookup(o->workspace_id, &ws) || s->n == 0) return OMR_OK;
-  // Members: one row per entity of the workspace that carries a usable embedding.
-  std::vector<double> hnorm((size_t)s->n);
-  OMR_CUDA_OK(cudaMemcpy(hnorm.data(), s->d_norm2, (size_t)s->n * 8, cudaMemcpyDeviceToHost));
-  std::vector<int32_t> idx;
-  for (int64_t r = 0; r < s->n; r++) {
-    const uint8_t f = s->h_flags[r];
-    if (s->h_ws[r] != ws || !(f & OMR_ROW_HAS_EMBEDDING) || !(f & kRowEntityRep) || (f & kRowDeleted)) continue;
-    if (!(hnorm[r] > 0.0) || hnorm[r] != hnorm[r] || hnorm[r] > 1e300) continue;  // NaN similarity never passes `>= floor`
-    if (o->require_mutable && !(f & OMR_ROW_MUTABLE)) continue;
-    idx.push_back((int32_t)r);
+// The join proper: member scan, tensor-core candidate pass (chunked launches, cancellable between chunks),
+// exact rescore + row-pair rules + `ORDER BY similarity DESC LIMIT n` on the device.  Returns the selected pairs
+// as (canonical row, dupe row) of THIS shard with their exact similarities, best first.  Caller holds join_gate.
+int omr_store::selfjoin(const omr_selfjoin_opts* o, std::vector<PairCand>* out_pairs, std::vector<double>* out_sims) {
+  out_pairs->clear();
+  out_sims->clear();
+  uint32_t ws = 0;
+  int64_t n_rows = 0;
+  {
+    std::lock_guard<std::mutex> lk(mu);
+    cudaSetDevice(cfg.device);
+    if (int drc = drain()) return drc;   // only for what earlier calls left on the shared stream
+    if (!ws_names.lookup(o->workspace_id, &ws) || n == 0) return OMR_OK;
+    n_rows = n;
+    OMR_CUDA_OK(cudaStreamSynchronize(stream));   // pending metadata pushes are visible to jstream
   }
-  const int64_t m = (int64_t)idx.size();
-  if (m < 2) return OMR_OK;
-  cudaStream_t st = s->stream;
+  cudaSetDevice(cfg.device);
+  cudaStream_t st = jstream;
   int rc;
-  const bool identity = m == s->n;
-  const int64_t m_pad = ((m + kTileRows - 1) / kTileRows) * kTileRows;
-  CUtensorMap ta, tb;
-  if (identity) {
-    ta = s->tmap_rows_a;
-    tb = s->tmap_rows_b;
-  } else {
-    if ((rc = s->w_gather.reserve((size_t)m_pad * s->pitch))) return rc;
-    if ((rc = s->w_idx.reserve((size_t)m))) return rc;
-    OMR_CUDA_OK(cudaMemcpyAsync(s->w_idx.p, idx.data(), (size_t)m * 4, cudaMemcpyHostToDevice, st));
-    OMR_CUDA_OK(cudaMemsetAsync(s->w_gather.p + (size_t)m * s->pitch, 0, (size_t)(m_pad - m) * s->pitch * 2, st));
-    if ((rc = launch_gather_rows(s->view(), s->w_idx.p, m, s->w_gather.p, st))) return rc;
-    s->st_launches++;
-    if ((rc = s->make_tmap(&ta, s->w_gather.p, (uint64_t)m_pad, kQueryTile))) return rc;
-    if ((rc = s->make_tmap(&tb, s->w_gather.p, (uint64_t)m_pad, kTileRows))) return rc;
-  }
-  std::vector<uint32_t> member((size_t)(m_pad / 32), 0u);
-  for (int64_t i = 0; i < m; i++) member[(size_t)(i >> 5)] |= 1u << (i & 31);
-  if ((rc = s->w_member.reserve(member.size()))) return rc;
-  OMR_CUDA_OK(cudaMemcpyAsync(s->w_member.p, member.data(), member.size() * 4, cudaMemcpyHostToDevice, st));
-  if ((rc = s->w_pair_count.reserve(1))) return rc;
   const int part_count = o->part_count > 0 ? o->part_count : 1;
   const int part_index = o->part_index;
   if (part_index < 0 || part_index >= part_count) return fail_msg(OMR_E_INVALID, "memory: self-join part %d of %d", part_index, part_count);
-  const double floor_d = (double)o->similarity_floor;  // float32 widened once, as Postgres does
-  // Extra candidates cost nothing here, so the join always uses the deterministic bound of the bf16 stage
-  // (2^-8 from the two roundings of unit vectors, plus fp32 accumulation over <= 2048 terms) rather than the
-  // statistical recall margin: the pair set is exact under any rounding pattern.
-  const float thr = (float)(floor_d - std::max((double)s->margin, 4.5e-3));
-  unsigned long long pcap = std::max<unsigned long long>(s->w_pairs.n, 1ull << 20);
-  unsigned long long cnt = 0;
-  for (int attempt = 0; attempt < 2; attempt++) {
-    if ((rc = s->w_pairs.reserve((size_t)pcap))) return rc;
-    OMR_CUDA_OK(cudaMemsetAsync(s->w_pair_count.p, 0, 8, st));
-    if (s->profiling) OMR_CUDA_OK(cudaEventRecord(s->lanes[0].ev0, st));
-    // CTA-pair kernel by default: the join runs for seconds under the board power cap, where a third less
-    // L2->SM traffic per flop is worth 13 % (1.53 s vs 1.72-1.77 s at 1M x 1536); force_path = 2 keeps the
-    // 1-CTA kernel
-    if (s->cfg.force_path != 2)
-      rc = launch_selfjoin_umma2(ta, m, s->pitch / kBlockK, part_index, part_count, thr, s->w_member.p, s->w_pairs.p, pcap,
-                                 s->w_pair_count.p, s->num_sms, st);
-    else
-      rc = launch_selfjoin_umma(ta, tb, m, s->pitch / kBlockK, part_index, part_count, thr, s->w_member.p, s->w_pairs.p, pcap,
-                                s->w_pair_count.p, s->num_sms, st);
-    if (rc) return rc;
-    if (s->profiling) OMR_CUDA_OK(cudaEventRecord(s->lanes[0].ev1, st));
-    s->st_launches++;
-    OMR_CUDA_OK(cudaMemcpyAsync(&cnt, s->w_pair_count.p, 8, cudaMemcpyDeviceToHost, st));
-    OMR_CUDA_OK(cudaStreamSynchronize(st));
-    if (s->profiling) {
-      float ms = 0.0f;
-      OMR_CUDA_OK(cudaEventElapsedTime(&ms, s->lanes[0].ev0, s->lanes[0].ev1));
-      s->scorer_ms_sum += ms;
-      s->scorer_timed++;
-    }
-    if (cnt <= pcap) break;
-    if (attempt == 1) return fail_msg(OMR_E_CAPACITY, "memory: self-join candidate count kept growing");
-    pcap = cnt + (cnt >> 3);
-  }
-  if (cnt == 0) return OMR_OK;
-  if (!identity) {
-    if ((rc = launch_pair_remap(s->w_pairs.p, cnt, s->w_idx.p, st))) return rc;
-    s->st_launches++;
-  }
-  if ((rc = s->w_pair_sim.reserve((size_t)cnt))) return rc;
-  if ((rc = launch_pair_rescore(s->view(), s->w_pairs.p, cnt, s->w_pair_sim.p, st))) return rc;
-  s->st_launches++;
-  std::vector<PairCand> hp((size_t)cnt);
-  std::vector<double> hs((size_t)cnt);
-  OMR_CUDA_OK(cudaMemcpyAsync(hp.data(), s->w_pairs.p, (size_t)cnt * sizeof(PairCand), cudaMemcpyDeviceToHost, st));
-  OMR_CUDA_OK(cudaMemcpyAsync(hs.data(), s->w_pair_sim.p, (size_t)cnt * 8, cudaMemcpyDeviceToHost, st));
+  auto cancelled = [&]() { return o->cancel && *o->cancel != 0; };
+
+  // ---- members: one row per entity of the workspace that carries a usable embedding (device scan)
+  const int blocks = join_scan_blocks(n_rows);
+  if ((rc = w_member.reserve((size_t)((n_rows + 31) / 32) + 8))) return rc;
+  if ((rc = w_jcounts.reserve((size_t)blocks))) return rc;
+  if ((rc = w_joffsets.reserve((size_t)blocks))) return rc;
+  if ((rc = w_jtotal.reserve(1))) return rc;
+  if ((rc = jpin.reserve(8))) return rc;
+  if ((rc = launch_join_member_scan(meta(), n_rows, ws, o->require_mutable, w_member.p, w_jcounts.p, w_joffsets.p,
+                                    w_jtotal.p, st)))
+    return rc;
+  st_launches += 2;
+  OMR_CUDA_OK(cudaMemcpyAsync(jpin.p, w_jtotal.p, 8, cudaMemcpyDeviceToHost, st));
   OMR_CUDA_OK(cudaStreamSynchronize(st));
-  struct P { double sim; int64_t c, d; };
-  std::vector<P> keep;
-  for (size_t i = 0; i < (size_t)cnt; i++) {
-    if (!(hs[i] >= floor_d)) continue;
-    const int64_t a = hp[i].a, b = hp[i].b;
-    if (o->require_same_kind && s->h_kind[a] != s->h_kind[b]) continue;
-    uint8_t ia[16], ib[16];
-    key_to(s->entity_id[s->h_entity[a]], ia);
-    key_to(s->entity_id[s->h_entity[b]], ib);
-    const int c = memcmp(ia, ib, 16);
-    if (c == 0) continue;
-    keep.push_back(c < 0 ? P{hs[i], a, b} : P{hs[i], b, a});
+  const int64_t m = (int64_t)jpin.p[0];
+  if (m < 2) return OMR_OK;
+  const bool identity = m == n_rows;
+  const int64_t m_pad = ((m + kTileRows - 1) / kTileRows) * kTileRows;
+  if ((rc = w_idx.reserve((size_t)m))) return rc;
+  if ((rc = w_kind_c.reserve((size_t)m_pad))) return rc;
+  if ((rc = launch_join_member_scatter(w_member.p, n_rows, w_joffsets.p, d_kind, w_idx.p, w_kind_c.p, st))) return rc;
+  st_launches++;
+  CUtensorMap ta, tb;
+  if (identity) {
+    ta = tmap_rows_a;
+    tb = tmap_rows_b;
+  } else {
+    if ((rc = w_gather.reserve((size_t)m_pad * pitch))) return rc;
+    OMR_CUDA_OK(cudaMemsetAsync(w_gather.p + (size_t)m * pitch, 0, (size_t)(m_pad - m) * pitch * 2, st));
+    if ((rc = launch_gather_rows(view(), w_idx.p, m, w_gather.p, st))) return rc;
+    st_launches++;
+    if ((rc = make_tmap(&ta, w_gather.p, (uint64_t)m_pad, kQueryTile))) return rc;
+    if ((rc = make_tmap(&tb, w_gather.p, (uint64_t)m_pad, kTileRows))) return rc;
   }
-  std::sort(keep.begin(), keep.end(), [](const P& x, const P& y) {
-    if (x.sim != y.sim) return x.sim > y.sim;
-    if (x.c != y.c) return x.c < y.c;
-    return x.d < y.d;
+  if ((rc = w_jbits.reserve((size_t)(m_pad / 32)))) return rc;
+  if ((rc = launch_compact_member_bits(m, m_pad / 32, w_jbits.p, st))) return rc;
+  st_launches++;
+
+  // ---- candidate pass
+  const double floor_d = (double)o->similarity_floor;  // float32 widened once, as Postgres does
+  // Extra candidates cost little here, so the join always uses at least the deterministic bound of the bf16
+  // stage (2^-8 from the two roundings of unit vectors, plus fp32 accumulation over <= 2048 terms): the pair set
+  // is exact under any rounding pattern.
+  const double eps = std::max((double)margin, 4.5e-3);
+  JoinLaunch jl;
+  jl.n = m;
+  jl.k_blocks = pitch / kBlockK;
+  jl.part_index = part_index;
+  jl.part_count = part_count;
+  jl.threshold = (float)(floor_d - eps);
+  jl.member_bitmap = w_jbits.p;
+  jl.limit = o->limit > 0 ? o->limit : 0;
+  if ((rc = w_pair_count.reserve(4))) return rc;
+  if (jl.limit > 0) {
+    if ((rc = w_run_cut.reserve(1))) return rc;
+    if ((rc = w_ghist.reserve((size_t)kJoinHistBins))) return rc;
+    jl.run_cut = w_run_cut.p;
+    jl.ghist = w_ghist.p;
+    jl.kind = o->require_same_kind ? w_kind_c.p : nullptr;
+    jl.band = (float)(2.0 * eps);
+    jl.hist_lo = jl.threshold;
+    jl.hist_scale = (float)((double)kJoinHistBins / std::max(1e-6, 1.0 + eps - (double)jl.threshold));
+  }
+  const bool pair_kernel = cfg.force_path != 2;
+  // CTA-pair kernel by default: the join runs for seconds under the board power cap, where a third less
+  // L2->SM traffic per flop is worth 13 % (1.53 s vs 1.72-1.77 s at 1M x 1536); force_path = 2 keeps the
+  // 1-CTA kernel
+  const int64_t items = selfjoin_items(m, jl.k_blocks, part_index, part_count, pair_kernel);
+  // chunks of ~50 ms so that a cancel request (checked between chunks, two in flight) is honoured quickly
+  int64_t chunk = std::max<int64_t>(4096, ((int64_t)(pair_kernel ? 1 : 2) << 18) * 24 / std::max(1, jl.k_blocks));
+  if (const char* e = getenv("OMR_SELFJOIN_CHUNK")) chunk = std::max<int64_t>(1, atoll(e));
+  unsigned long long pcap = std::max<unsigned long long>(w_pairs.n, 1ull << 20);
+  if (const char* e = getenv("OMR_SELFJOIN_PCAP")) pcap = std::max<unsigned long long>(1ull, strtoull(e, nullptr, 10));
+  unsigned long long cnt = 0;
+  for (int attempt = 0; attempt < 3; attempt++) {
+    if ((rc = w_pairs.reserve((size_t)pcap))) return rc;
+    jl.pairs = w_pairs.p;
+    jl.cap = pcap;
+    jl.pair_count = w_pair_count.p;
+    OMR_CUDA_OK(cudaMemsetAsync(w_pair_count.p, 0, 32, st));
+    if (jl.limit > 0) {
+      const int32_t neg = kOrderedNegInf;
+      jpin.p[4] = (unsigned long long)(uint32_t)neg;
+      OMR_CUDA_OK(cudaMemcpyAsync(w_run_cut.p, jpin.p + 4, 4, cudaMemcpyHostToDevice, st));
+      OMR_CUDA_OK(cudaMemsetAsync(w_ghist.p, 0, (size_t)kJoinHistBins * 4, st));
+    }
+    if (profiling) OMR_CUDA_OK(cudaEventRecord(jev0, st));
+    int c = 0;
+    for (int64_t first = 0; first < items; first += chunk, c++) {
+      jl.chunk_first = first;
+      jl.chunk_items = std::min(chunk, items - first);
+      rc = pair_kernel ? launch_selfjoin_umma2(ta, jl, num_sms, st) : launch_selfjoin_umma(ta, tb, jl, num_sms, st);
+      if (rc) return rc;
+      st_launches++;
+      OMR_CUDA_OK(cudaEventRecord(jchunk[c & 1], st));
+      if (c >= 1) {
+        OMR_CUDA_OK(cudaEventSynchronize(jchunk[(c - 1) & 1]));
+        if (cancelled()) {
+          OMR_CUDA_OK(cudaStreamSynchronize(st));
+          return fail_msg(OMR_E_CANCELLED, "memory: self-join cancelled");
+        }
+      }
+    }
+    if (profiling) OMR_CUDA_OK(cudaEventRecord(jev1, st));
+    OMR_CUDA_OK(cudaMemcpyAsync(jpin.p, w_pair_count.p, 8, cudaMemcpyDeviceToHost, st));
+    OMR_CUDA_OK(cudaStreamSynchronize(st));
+    cnt = jpin.p[0];
+    if (profiling) {
+      float ms = 0.0f;
+      OMR_CUDA_OK(cudaEventElapsedTime(&ms, jev0, jev1));
+      scorer_ms_sum += ms;
+      scorer_timed++;
+    }
+    if (cancelled()) return fail_msg(OMR_E_CANCELLED, "memory: self-join cancelled");
+    if (cnt <= pcap) break;
+    if (attempt == 2) return fail_msg(OMR_E_CAPACITY, "memory: self-join candidate count kept growing");
+    pcap = cnt + (cnt >> 3);   // the list was too short: rerun with room for what this pass counted
+  }
+  st_join_candidates += (int64_t)cnt;
+  if (cnt == 0) return OMR_OK;
+
+  // ---- exact similarity, row-pair rules, ORDER BY / LIMIT: all on the device
+  if (!identity) {
+    if ((rc = launch_pair_remap(w_pairs.p, cnt, w_idx.p, st))) return rc;
+    st_launches++;
+  }
+  if ((rc = w_pair_sim.reserve((size_t)cnt))) return rc;
+  if ((rc = w_keys.reserve((size_t)cnt * 2))) return rc;
+  if ((rc = w_jstate.reserve(join_select_state_bytes()))) return rc;
+  if ((rc = launch_pair_keys(view(), w_pairs.p, cnt, d_entity_key, d_kind, o->require_same_kind, floor_d, w_pair_sim.p,
+                             w_keys.p, w_pair_count.p + 1, st)))
+    return rc;
+  st_launches++;
+  OMR_CUDA_OK(cudaMemcpyAsync(jpin.p + 1, w_pair_count.p + 1, 8, cudaMemcpyDeviceToHost, st));
+  OMR_CUDA_OK(cudaStreamSynchronize(st));
+  const unsigned long long n_valid = jpin.p[1];
+  if (n_valid == 0) return OMR_OK;
+  const unsigned long long out_cap = jl.limit > 0 ? std::min<unsigned long long>(n_valid, (unsigned long long)jl.limit) : n_valid;
+  if ((rc = w_out_pairs.reserve((size_t)out_cap))) return rc;
+  if ((rc = w_out_sim.reserve((size_t)out_cap))) return rc;
+  if ((rc = launch_pair_select(w_pairs.p, w_pair_sim.p, w_keys.p, cnt, jl.limit, w_jstate.p, out_cap, w_out_pairs.p,
+                               w_out_sim.p, w_pair_count.p + 2, num_sms, st)))
+    return rc;
+  st_launches += jl.limit > 0 ? 17 : 1;
+  out_pairs->resize((size_t)out_cap);
+  out_sims->resize((size_t)out_cap);
+  OMR_CUDA_OK(cudaMemcpyAsync(out_pairs->data(), w_out_pairs.p, (size_t)out_cap * sizeof(PairCand), cudaMemcpyDeviceToHost, st));
+  OMR_CUDA_OK(cudaMemcpyAsync(out_sims->data(), w_out_sim.p, (size_t)out_cap * 8, cudaMemcpyDeviceToHost, st));
+  OMR_CUDA_OK(cudaMemcpyAsync(jpin.p + 2, w_pair_count.p + 2, 8, cudaMemcpyDeviceToHost, st));
+  OMR_CUDA_OK(cudaStreamSynchronize(st));
+  if (jpin.p[2] != out_cap)
+    return fail_msg(OMR_E_CUDA, "memory: gpu: self-join selection kept %llu of %llu pairs", jpin.p[2], out_cap);
+  // best first: similarity DESC, then (canonical row, dupe row), the order the selection used
+  std::vector<size_t> order((size_t)out_cap);
+  for (size_t i = 0; i < order.size(); i++) order[i] = i;
+  std::sort(order.begin(), order.end(), [&](size_t x, size_t y) {
+    if ((*out_sims)[x] != (*out_sims)[y]) return (*out_sims)[x] > (*out_sims)[y];
+    if ((*out_pairs)[x].a != (*out_pairs)[y].a) return (*out_pairs)[x].a < (*out_pairs)[y].a;
+    return (*out_pairs)[x].b < (*out_pairs)[y].b;
   });
-  int64_t total = (int64_t)keep.size();
-  if (o->limit > 0) total = std::min<int64_t>(total, o->limit);
+  std::vector<PairCand> sp(order.size());
+  std::vector<double> ss(order.size());
+  for (size_t i = 0; i < order.size(); i++) {
+    sp[i] = (*out_pairs)[order[i]];
+    ss[i] = (*out_sims)[order[i]];
+  }
+  out_pairs->swap(sp);
+  out_sims->swap(ss);
+  return OMR_OK;
+}
+
+int omr_selfjoin(omr_store* s, const omr_selfjoin_opts* o, omr_pair* out, int64_t cap, int64_t* found) {
+  if (!s || !o || !found || (cap > 0 && !out)) return fail_msg(OMR_E_INVALID, "memory: omr_selfjoin: null argument");
+  if (!o->workspace_id || !o->workspace_id[0]) return fail_msg(OMR_E_WORKSPACE, "memory: workspace_id is required");
+  *found = 0;
+  std::lock_guard<std::mutex> gate(s->join_gate);
+  std::vector<PairCand> pairs;
+  std::vector<double> sims;
+  if (int rc = s->selfjoin(o, &pairs, &sims)) return rc;
+  std::lock_guard<std::mutex> lk(s->mu);   // host identity maps
+  const int64_t total = (int64_t)pairs.size();
   *found = total;
   for (int64_t i = 0; i < std::min(total, cap); i++) {
     omr_pair& p = out[i];
-    key_to(s->entity_id[s->h_entity[keep[i].c]], p.canonical_id);
-    key_to(s->entity_id[s->h_entity[keep[i].d]], p.dupe_id);
-    p.similarity = keep[i].sim;
-    p.canonical_row = s->cfg.row_base + keep[i].c * s->cfg.row_stride;
-    p.dupe_row = s->cfg.row_base + keep[i].d * s->cfg.row_stride;
-    p.kind = s->h_kind[keep[i].c];
+    key_to(s->entity_id[s->h_entity[pairs[i].a]], p.canonical_id);
+    key_to(s->entity_id[s->h_entity[pairs[i].b]], p.dupe_id);
+    p.similarity = sims[i];
+    p.canonical_row = s->cfg.row_base + (int64_t)pairs[i].a * s->cfg.row_stride;
+    p.dupe_row = s->cfg.row_base + (int64_t)pairs[i].b * s->cfg.row_stride;
+    p.kind = s->h_kind[pairs[i].a];
   }
+  return OMR_OK;
+}
+
+int omr_selfjoin_rows(omr_store* s, const omr_selfjoin_opts* o, int64_t* canonical_rows, int64_t* dupe_rows,
+                      double* similarities, int64_t cap, int64_t* found) {
+  if (!s || !o || !found || (cap > 0 && (!canonical_rows || !dupe_rows || !similarities)))
+    return fail_msg(OMR_E_INVALID, "memory: omr_selfjoin_rows: null argument");
+  if (!o->workspace_id || !o->workspace_id[0]) return fail_msg(OMR_E_WORKSPACE, "memory: workspace_id is required");
+  *found = 0;
+  std::lock_guard<std::mutex> gate(s->join_gate);
+  std::vector<PairCand> pairs;
+  std::vector<double> sims;
+  if (int rc = s->selfjoin(o, &pairs, &sims)) return rc;
+  const int64_t total = (int64_t)pairs.size();
+  *found = total;
+  for (int64_t i = 0; i < std::min(total, cap); i++) {
+    canonical_rows[i] = s->cfg.row_base + (int64_t)pairs[i].a * s->cfg.row_stride;
+    dupe_rows[i] = s->cfg.row_base + (int64_t)pairs[i].b * s->cfg.row_stride;
+    similarities[i] = sims[i];
+  }
+  return OMR_OK;
+}
+
+int omr_row_entity(omr_store* s, int64_t row, uint8_t entity_id[16], uint32_t* kind) {
+  if (!s || !entity_id) return fail_msg(OMR_E_INVALID, "memory: omr_row_entity: null argument");
+  std::lock_guard<std::mutex> lk(s->mu);
+  const int64_t stride = s->cfg.row_stride > 0 ? s->cfg.row_stride : 1;
+  const int64_t local = (row - s->cfg.row_base) / stride;
+  if (row < s->cfg.row_base || (row - s->cfg.row_base) % stride != 0 || local >= s->n)
+    return fail_msg(OMR_E_NOT_FOUND, "memory: not found");
+  key_to(s->entity_id[s->h_entity[local]], entity_id);
+  if (kind) *kind = s->h_kind[local];
   return OMR_OK;
 }
 
@@ -2129,6 +2544,9 @@ int omr_get_stats(const omr_store* s, omr_stats* out) {
   for (int i = 0; i < 3; i++) out->phase_ms_sum[i] = s->phase_ms_sum[i];
   out->scorer_kernel_ms_sum = s->kernel_ns_sum * 1e-6;
   out->scorer_kernel_timed = s->kernel_ns_n;
+  out->join_candidates = s->st_join_candidates.load();
+  out->scorer_start_skew_ms_sum = s->kernel_start_skew_ns * 1e-6;
+  out->scorer_end_skew_ms_sum = s->kernel_end_skew_ns * 1e-6;
   return OMR_OK;
 }
 
@@ -2212,7 +2630,7 @@ int omr_set_profiling(omr_store* s, int32_t on) {
   s->scorer_ms_sum = 0.0;
   s->scorer_timed = 0;
   for (double& v : s->phase_ms_sum) v = 0.0;
-  s->kernel_ns_sum = 0.0;
+  s->kernel_ns_sum = s->kernel_start_skew_ns = s->kernel_end_skew_ns = 0.0;
   s->kernel_ns_n = 0;
   return OMR_OK;
 }

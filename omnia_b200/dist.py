@@ -169,19 +169,41 @@ class ShardedRecall:
 
 
 def sharded_selfjoin(store: GPUMemoryStore, workspace_id: str, similarity_floor: float, max_buckets_per_pass: int = 100,
-                     group=None, **kw):
+                     group=None, device=None, **kw):
     """Near-duplicate self-join block-partitioned over the ranks: every rank holds the
-    whole matrix (C4's 3 GB bf16 replicate easily), scans part `rank` of `world` of the tile-pair space, and the
-    variable-length pair lists are exchanged (counts first, then payload, via all_gather_object) and merged:
-    ORDER BY similarity DESC, LIMIT n.  Returns the same list on every rank."""
+    whole matrix (C4's 3 GB bf16 replicate easily) and scans part `rank` of `world` of the tile-pair space; with
+    a LIMIT each rank already returns only its n best pairs (omr_selfjoin_rows selects on the device).  The
+    variable-length lists are exchanged as tensors -- one all_gather of the counts, one of the payload padded to
+    the largest count, (canonical row, dupe row, similarity) -- on the process group's device (NCCL over NVLink
+    on GPUs, gloo in the CPU tests), and merged: ORDER BY similarity DESC (ties by rows), LIMIT n.  Every rank
+    returns the same list."""
     live = dist.is_available() and dist.is_initialized()
     rank = dist.get_rank(group) if live else 0
     world = dist.get_world_size(group) if live else 1
-    mine = store.run_entity_duplicate_candidates(workspace_id, similarity_floor, max_buckets_per_pass,
-                                                 part_index=rank, part_count=world, **kw)
-    if world == 1:
-        return mine
-    parts = [None] * world
-    dist.all_gather_object(parts, mine, group=group)
-    merged = sorted((p for part in parts for p in part), key=lambda p: (-p.similarity, p.canonical_row, p.dupe_row))
-    return merged[:max_buckets_per_pass] if max_buckets_per_pass > 0 else merged
+    c, d, v = store.selfjoin_rows(workspace_id, similarity_floor, max_buckets_per_pass, part_index=rank, part_count=world,
+                                  **kw)
+    if world > 1:
+        if device is None:
+            device = torch.device("cuda", torch.cuda.current_device()) if dist.get_backend(group) == "nccl" else torch.device("cpu")
+        count = torch.tensor([len(c)], dtype=torch.int64, device=device)
+        counts = [torch.zeros_like(count) for _ in range(world)]
+        dist.all_gather(counts, count, group=group)
+        counts = [int(t.item()) for t in counts]
+        width = max(1, max(counts))
+        # one int64 payload [3][width]: rows as they are, similarities by their bit pattern
+        mine = torch.zeros((3, width), dtype=torch.int64)
+        mine[0, :len(c)] = torch.from_numpy(np.ascontiguousarray(c))
+        mine[1, :len(d)] = torch.from_numpy(np.ascontiguousarray(d))
+        mine[2, :len(v)] = torch.from_numpy(np.ascontiguousarray(v).view(np.int64))
+        mine = mine.to(device)
+        parts = [torch.empty_like(mine) for _ in range(world)]
+        dist.all_gather(parts, mine, group=group)
+        parts = [p.cpu().numpy() for p in parts]
+        c = np.concatenate([p[0, :n] for p, n in zip(parts, counts)])
+        d = np.concatenate([p[1, :n] for p, n in zip(parts, counts)])
+        v = np.concatenate([p[2, :n].view(np.float64) for p, n in zip(parts, counts)])
+        order = np.lexsort((d, c, -v))
+        if max_buckets_per_pass > 0:
+            order = order[:max_buckets_per_pass]
+        c, d, v = c[order], d[order], v[order]
+    return store.pairs_from_rows(c, d, v)

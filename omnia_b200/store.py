@@ -213,6 +213,33 @@ class GPUMemoryStore:
         r.confidence, r.flags, r.valid_until_us = float(confidence), int(flags), int(valid_until_us)
         L.check(self._lib.omr_upsert(self._h, C.byref(r), v.ctypes.data, v.shape[0]))
 
+    def upsert_batch(self, observation_ids, entity_ids, scope: Dict[str, str], embeddings, *, kind: str = "",
+                     purpose: str = "", confidence: float = 1.0, flags: int = L.ROW_HAS_EMBEDDING | L.ROW_MUTABLE,
+                     valid_until_us: int = L.NO_EXPIRY) -> None:
+        """n upserts under one scope in one call (omr_upsert_batch): one staged copy, one ingest launch."""
+        v = np.ascontiguousarray(embeddings, np.float32)
+        n = v.shape[0]
+        rows = (L.Row * max(1, n))()
+        ws = _cstr(scope.get(SCOPE_WORKSPACE_ID, ""))
+        user, agent = _cstr(scope.get(SCOPE_VIRTUAL_USER_ID) or None), _cstr(scope.get(SCOPE_AGENT_ID) or None)
+        for i in range(n):
+            r = rows[i]
+            C.memmove(r.observation_id, id_bytes(observation_ids[i]), 16)
+            C.memmove(r.entity_id, id_bytes(entity_ids[i]), 16)
+            r.workspace_id, r.virtual_user_id, r.agent_id = ws, user, agent
+            r.kind, r.purpose = kind.encode(), purpose.encode()
+            r.confidence, r.flags, r.valid_until_us = float(confidence), int(flags), int(valid_until_us)
+        L.check(self._lib.omr_upsert_batch(self._h, rows, v.ctypes.data, n, v.shape[1] if n else self.dim))
+
+    def compact(self) -> int:
+        """Squeezes hard-deleted rows out of the shard (omr_compact); returns how many rows were reclaimed."""
+        got = C.c_int64(0)
+        L.check(self._lib.omr_compact(self._h, C.byref(got)))
+        return int(got.value)
+
+    def free_slots(self) -> int:
+        return int(self._lib.omr_free_slots(self._h))
+
     def update_embedding(self, entity_id: IdLike, embedding) -> None:
         """UpdateEmbedding (store_write.go:557-578)."""
         v = np.ascontiguousarray(embedding, np.float32).reshape(-1)
@@ -361,14 +388,22 @@ class GPUMemoryStore:
         return [(id_str(hits[i].entity_id), hits[i].distance, i + 1) for i in range(cnt.value)]
 
     # -- consolidation -----------------------------------------------------------
+    def _join_opts(self, workspace_id, similarity_floor, limit, require_same_kind, require_mutable, part_index,
+                   part_count, cancel):
+        return L.SelfJoinOpts(_cstr(workspace_id), float(similarity_floor), int(limit), int(require_same_kind),
+                              int(require_mutable), int(part_index), int(part_count),
+                              C.pointer(cancel) if cancel is not None else None)
+
     def run_entity_duplicate_candidates(self, workspace_id: str, similarity_floor: float = 0.85,
                                         max_buckets_per_pass: int = 100, require_same_kind: bool = True,
                                         require_mutable: bool = True, part_index: int = 0,
-                                        part_count: int = 1) -> List[DuplicatePair]:
+                                        part_count: int = 1, cancel=None) -> List[DuplicatePair]:
         """RunEntityDuplicateCandidates (consolidation_prefilter.go:176-203; defaults worker.go:432-451).
-        part_index / part_count: scan only that block partition of the pair space (multi-GPU, see dist.py)."""
-        opts = L.SelfJoinOpts(_cstr(workspace_id), float(similarity_floor), int(max_buckets_per_pass),
-                              int(require_same_kind), int(require_mutable), int(part_index), int(part_count))
+        part_index / part_count: scan only that block partition of the pair space (multi-GPU, see dist.py).
+        cancel: a ctypes.c_int32 another thread may set to 1 (the Go binding's ctx.Done watcher); the join then
+        stops at its next chunk boundary and RecallError(E_CANCELLED) is raised."""
+        opts = self._join_opts(workspace_id, similarity_floor, max_buckets_per_pass, require_same_kind, require_mutable,
+                               part_index, part_count, cancel)
         cap = max_buckets_per_pass if max_buckets_per_pass > 0 else 1 << 16
         while True:
             out = (L.Pair * max(1, cap))()
@@ -380,6 +415,37 @@ class GPUMemoryStore:
         return [DuplicatePair(id_str(p.canonical_id), id_str(p.dupe_id), p.similarity,
                               (self._lib.omr_kind_name(self._h, p.kind) or b"").decode(), p.canonical_row, p.dupe_row)
                 for p in out[:found.value]]
+
+    def selfjoin_rows(self, workspace_id: str, similarity_floor: float = 0.85, limit: int = 100,
+                      require_same_kind: bool = True, require_mutable: bool = True, part_index: int = 0,
+                      part_count: int = 1, cancel=None):
+        """The same join as struct-of-arrays (canonical_row, dupe_row, similarity), best first, no uuid lookup
+        (omr_selfjoin_rows): what the ranks of a partitioned join exchange."""
+        opts = self._join_opts(workspace_id, similarity_floor, limit, require_same_kind, require_mutable, part_index,
+                               part_count, cancel)
+        cap = limit if limit > 0 else 1 << 16
+        while True:
+            a, b, s = np.empty(max(1, cap), np.int64), np.empty(max(1, cap), np.int64), np.empty(max(1, cap), np.float64)
+            found = C.c_int64(0)
+            L.check(self._lib.omr_selfjoin_rows(self._h, C.byref(opts), a.ctypes.data, b.ctypes.data, s.ctypes.data, cap,
+                                                C.byref(found)))
+            if found.value <= cap:
+                break
+            cap = int(found.value)
+        n = int(found.value)
+        return a[:n], b[:n], s[:n]
+
+    def pairs_from_rows(self, canonical_rows, dupe_rows, similarities) -> List[DuplicatePair]:
+        """Rows of a (gathered) join result -> the Bucket records of RunEntityDuplicateCandidates, through this
+        store's identity maps (omr_row_ids)."""
+        out = []
+        for c, d, v in zip(canonical_rows, dupe_rows, similarities):
+            ent_c = (C.c_uint8 * 16)(); ent_d = (C.c_uint8 * 16)(); kind = C.c_uint32(0)
+            L.check(self._lib.omr_row_entity(self._h, int(c), ent_c, C.byref(kind)))
+            L.check(self._lib.omr_row_entity(self._h, int(d), ent_d, None))
+            out.append(DuplicatePair(id_str(ent_c), id_str(ent_d), float(v),
+                                     (self._lib.omr_kind_name(self._h, kind.value) or b"").decode(), int(c), int(d)))
+        return out
 
     # -- Memory Galaxy projection input (SURVEY.md section 8f-4) ------------------------
     def projection_rows(self, flt: FilterSpec, cap: int = 0) -> np.ndarray:

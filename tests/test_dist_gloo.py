@@ -91,6 +91,15 @@ class _StubJoinStore:
         mine.sort(key=lambda p: (-p.similarity, p.canonical_row, p.dupe_row))
         return mine[:max_buckets_per_pass] if max_buckets_per_pass > 0 else mine
 
+    def selfjoin_rows(self, workspace_id, similarity_floor, limit, part_index=0, part_count=1, **kw):
+        mine = self.run_entity_duplicate_candidates(workspace_id, similarity_floor, limit, part_index, part_count)
+        return (np.array([p.canonical_row for p in mine], np.int64), np.array([p.dupe_row for p in mine], np.int64),
+                np.array([p.similarity for p in mine], np.float64))
+
+    def pairs_from_rows(self, c, d, v):
+        from omnia_b200.store import DuplicatePair
+        return [DuplicatePair(f"e{int(x)}", f"e{int(y)}", float(z), "", int(x), int(y)) for x, y, z in zip(c, d, v)]
+
 
 def _join_worker(rank, world, port, limit, out):
     from omnia_b200.dist import sharded_selfjoin

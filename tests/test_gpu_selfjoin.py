@@ -102,3 +102,133 @@ def test_super_block_walk_covers_every_tile_pair_once(monkeypatch, sb, path):
     got = [(min(p.canonical_row, p.dupe_row), max(p.canonical_row, p.dupe_row)) for p in pairs]
     want = sorted((min(int(i), int(j)), max(int(i), int(j))) for i, j, _ in planted)
     assert sorted(got) == want and len(set(got)) == len(got)
+
+
+# ---- ORDER BY similarity DESC LIMIT n on the device (consolidation/prefilter.go:129-130; production call: floor 0.85,
+# ---- limit 100, ee/pkg/memory/consolidation/worker.go:432-441)
+
+def _rows_ids(n):
+    from helpers import ids_from_rows
+    return ids_from_rows(n)
+
+
+@pytest.mark.parametrize("path", [0, 2])
+def test_limit_selects_the_oracles_top_n_in_order(path):
+    n, dim, limit = 13_000, 128, 100
+    corpus, _ = synth.planted_dups(n, dim, n_pairs=400)
+    kind = (np.arange(n) % 3 == 0).astype(np.uint16)
+    flags = np.full(n, ROW_HAS_EMBEDDING | ROW_MUTABLE, np.uint8)
+    with GPUMemoryStore(dim, n, force_path=path) as s:
+        s.bulk_load(corpus, kinds=["a", "b"], kind_idx=kind, flags=flags)
+        for same_kind in (False, True):
+            got, _ = gpu_pairs(s, "default", 0.85, limit=limit, require_same_kind=same_kind)
+            a, b, sim = O.selfjoin(corpus, None, kind, flags, _rows_ids(n), 0.85, same_kind, True, variant=O.VARIANT_F64,
+                                   limit=limit)
+            assert len(got) == len(a) == limit
+            assert [(c, d) for c, d, _ in got] == [(int(x), int(y)) for x, y in zip(a, b)]
+            assert max(abs(g[2] - v) for g, v in zip(got, sim)) < 1e-9
+        st = s.stats()
+    assert st.join_candidates > 0
+
+
+def test_clustered_corpus_limit_100_equals_the_oracle_up_to_ties():
+    """The seeder-shaped corpus (6 topics x 160 sentences, 30 % exact duplicates): every same-topic pair clears a
+    0.85 floor, and thousands of exact-duplicate pairs tie at similarity 1 to the last bit or two.  The engine's
+    top 100 must be the oracle's top 100 up to the identity of pairs whose similarities agree within 1e-9."""
+    n, dim, limit = 8_000, 384, 100
+    corpus = synth.clustered(n, dim)
+    kind = np.zeros(n, np.uint16)
+    flags = np.full(n, ROW_HAS_EMBEDDING | ROW_MUTABLE, np.uint8)
+    with GPUMemoryStore(dim, n) as s:
+        s.bulk_load(corpus)
+        got, _ = gpu_pairs(s, "default", 0.85, limit=limit)
+        st = s.stats()
+    a, b, sim = O.selfjoin(corpus, None, kind, flags, _rows_ids(n), 0.85, variant=O.VARIANT_F64)
+    assert len(a) > 3_000_000, "this corpus is meant to put millions of pairs above the floor"
+    assert st.join_candidates < len(a) // 4, "the running cut must keep the candidate list far below every pair above the floor"
+    key = a * n + b                                   # numpy lookup: a Python dict of 1e7 tuples takes a minute
+    order = np.argsort(key)
+    key, sim_by_key = key[order], sim[order]
+    assert len(got) == limit and len({(c, d) for c, d, _ in got}) == limit
+    for i, (c, d, v) in enumerate(got):
+        j = int(np.searchsorted(key, c * n + d))
+        assert j < len(key) and key[j] == c * n + d, "a returned pair is not a pair of the join"
+        assert abs(sim_by_key[j] - v) < 1e-9, "a returned pair's similarity is off"
+        assert abs(v - sim[i]) < 1e-9, f"rank {i}: similarity {v} vs the oracle's {sim[i]}"
+    # nothing strictly better than the last returned pair may be missing
+    better = np.flatnonzero(sim > got[-1][2] + 1e-9)
+    have = {(c, d) for c, d, _ in got}
+    assert all((int(a[i]), int(b[i])) in have for i in better)
+
+
+def test_clustered_200k_limit_100_structural():
+    """SURVEY.md section 8(d)(ii) at a size the O(n^2) oracle cannot reach: the 100 best pairs of a 200k-row
+    seeder-shaped corpus are exact duplicates (similarity 1 up to the last bits), distinct, canonical before dupe."""
+    n, dim = 200_000, 384
+    corpus = synth.clustered(n, dim)
+    with GPUMemoryStore(dim, n) as s:
+        s.bulk_load(corpus)
+        got, _ = gpu_pairs(s, "default", 0.85, limit=100)
+        st = s.stats()
+    assert len(got) == 100 and len({(c, d) for c, d, _ in got}) == 100
+    for c, d, v in got:
+        assert c < d and v > 1.0 - 1e-12 and np.array_equal(corpus[c], corpus[d])
+    assert all(got[i][2] >= got[i + 1][2] for i in range(99))
+    # every same-topic pair clears the floor (~3.3e9 of them); the running cut keeps the list near the duplicate clusters
+    assert st.join_candidates < 200_000_000
+
+
+def test_candidate_list_regrows_when_it_is_too_short(monkeypatch):
+    n, dim = 5000, 128
+    corpus, _ = synth.planted_dups(n, dim, n_pairs=120)
+    with GPUMemoryStore(dim, n) as s:
+        s.bulk_load(corpus)
+        want, _ = gpu_pairs(s, "default", 0.9)
+    monkeypatch.setenv("OMR_SELFJOIN_PCAP", "16")      # first pass counts, second pass has room
+    with GPUMemoryStore(dim, n) as s:
+        s.bulk_load(corpus)
+        got, _ = gpu_pairs(s, "default", 0.9)
+        top7, _ = gpu_pairs(s, "default", 0.9, limit=7)
+    assert len(want) > 16 and got == want and top7 == want[:7]
+
+
+def test_cancel_flag_stops_the_join(monkeypatch):
+    import ctypes
+    from omnia_b200 import RecallError
+    from omnia_b200 import _lib as L
+    monkeypatch.setenv("OMR_SELFJOIN_CHUNK", "64")     # many chunks, so the flag is looked at
+    n, dim = 6000, 128
+    corpus, _ = synth.planted_dups(n, dim, n_pairs=20)
+    with GPUMemoryStore(dim, n) as s:
+        s.bulk_load(corpus)
+        flag = ctypes.c_int32(1)
+        with pytest.raises(RecallError, match="cancelled") as e:
+            s.run_entity_duplicate_candidates("default", 0.9, 0, cancel=flag)
+        assert e.value.code == L.E_CANCELLED
+        flag.value = 0
+        assert len(s.run_entity_duplicate_candidates("default", 0.9, 0, cancel=flag)) > 0
+
+
+def test_recall_answers_while_a_join_runs():
+    import threading
+    from omnia_b200 import FilterSpec
+    n, dim = 60_000, 256
+    corpus, _ = synth.planted_dups(n, dim, n_pairs=50)
+    queries = synth.queries_from(corpus, 64)
+    with GPUMemoryStore(dim, n) as s:
+        s.bulk_load(corpus)
+        want = s.search_rows(queries, [FilterSpec("default")], 10)
+        pairs0 = s.run_entity_duplicate_candidates("default", 0.9, 0)
+        res = {}
+
+        def join():
+            res["pairs"] = [s.run_entity_duplicate_candidates("default", 0.9, 0) for _ in range(3)]
+
+        t = threading.Thread(target=join)
+        t.start()
+        answers = [s.search_rows(queries, [FilterSpec("default")], 10) for _ in range(20)]
+        t.join()
+    for g in answers:
+        assert all(np.array_equal(x, y) for x, y in zip(want, g))
+    assert all([(p.canonical_row, p.dupe_row) for p in ps] == [(p.canonical_row, p.dupe_row) for p in pairs0]
+               for ps in res["pairs"])

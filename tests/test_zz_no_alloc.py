@@ -80,3 +80,23 @@ def test_fewer_rows_than_k_and_limits_are_refused_clearly():
     rc = lib.omr_exact_topk_noalloc(d_rows.data_ptr(), L.NOALLOC_MAX_ROWS + 1, 64, 64, q.data_ptr(), 5,
                                     o_r.data_ptr(), o_d.data_ptr(), o_c.data_ptr(), None)
     assert rc == L.E_CAPACITY and b"at most 524288 rows" in lib.omr_last_error()
+
+
+def test_against_the_oracle_with_duplicates_straddling_the_kth_place():
+    """Held to the CPU oracle directly, and on a tie: 40 copies of one row are the nearest neighbours of the
+    query, k = 16 cuts through them.  The copies are bit-identical, so their distances are too, and the 16 that
+    come back must be the 16 smallest row numbers (the oracle's ORDER BY distance, row) -- on every run."""
+    from oracle import oracle as O
+    n, dim, k = 9_000, 96, 16
+    corpus = synth.gauss_unit(n, dim, seed=17)
+    rng = np.random.default_rng(3)
+    dup_rows = np.sort(rng.choice(n, 40, replace=False))
+    corpus[dup_rows] = corpus[dup_rows[0]]
+    query = (corpus[dup_rows[0]] + 0.01 * synth.gauss_unit(1, dim, seed=5)[0]).astype(np.float32)
+    d_rows = torch.from_numpy(corpus).cuda()
+    r_rows, r_dist, r_cnt = O.search(corpus, query[None, :], k, variant=O.VARIANT_F64)
+    assert r_rows[0].tolist() == dup_rows[:k].tolist()
+    for _ in range(3):
+        g_rows, g_dist, g_cnt = new_entry_point(d_rows, query, k)
+        assert g_cnt == k and g_rows.tolist() == r_rows[0].tolist()
+        assert np.allclose(g_dist, r_dist[0], rtol=0, atol=ATOL)
