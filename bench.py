@@ -378,8 +378,16 @@ def main():
     st1 = sr.store.stats()
     # the kernel's own span (first CTA start to last CTA end, %globaltimer): with several batches in flight the
     # stream events around the kernel also count the time it queued behind the previous batch
-    scorer_ms_timed = (st1.scorer_kernel_ms_sum / st1.scorer_kernel_timed) if st1.scorer_kernel_timed else \
-        st1.scorer_ms_sum / max(1, st1.scorer_timed)
+    # With batches in flight the CTAs of one launch do not start together (an SM takes its CTA when the previous
+    # batch's CTA leaves it); every CTA has the same share of work, so the launch's duration is taken from the
+    # LAST CTA to start to the last CTA to end.  The full span and the start / end skew are reported beside it.
+    def kernel_ms_of(st):
+        if not st.scorer_kernel_timed:
+            return st.scorer_ms_sum / max(1, st.scorer_timed), None
+        n_t = st.scorer_kernel_timed
+        span, s_skew, e_skew = st.scorer_kernel_ms_sum / n_t, st.scorer_start_skew_ms_sum / n_t, st.scorer_end_skew_ms_sum / n_t
+        return span - s_skew, {"span_ms": span, "start_skew_ms": s_skew, "end_skew_ms": e_skew}
+    scorer_ms_timed, scorer_span_timed = kernel_ms_of(st1)
     phases_ms = [float(x) / max(1, st1.scorer_timed) for x in st1.phase_ms_sum]
     sr.store.set_profiling(False)
     t = torch.tensor([ms_total], dtype=torch.float64, device=dev)
@@ -397,7 +405,17 @@ def main():
     outs = [(np.empty((NQ, TOPK), np.int64), np.empty((NQ, TOPK), np.float64), np.empty(NQ, np.int32)) for _ in range(4)]
 
     if world > 1:
-        dstage = [torch.empty_like(dq[0]) for _ in range(8)]
+        # every rank copies only ITS 1/world slice of the query batch over PCIe; the slices are all-gathered over
+        # NVLink (r1: every rank copied the whole 6.3 MB batch, 8x redundant host->device traffic at N=8)
+        per = (NQ + world - 1) // world
+        hq_slice = []
+        for t in hq:
+            sl = torch.zeros((per, DIM), dtype=torch.float32)
+            part = t[rank * per:min(NQ, (rank + 1) * per)]
+            sl[:part.shape[0]] = part
+            hq_slice.append(sl.pin_memory())
+        dslice = [torch.empty((per, DIM), dtype=torch.float32, device=dev) for _ in range(8)]
+        dstage = [torch.empty((world * per, DIM), dtype=torch.float32, device=dev) for _ in range(8)]
         hres = [(torch.empty((NQ, TOPK), dtype=torch.int64).pin_memory(), torch.empty((NQ, TOPK), dtype=torch.float64).pin_memory(),
                  torch.empty(NQ, dtype=torch.int32).pin_memory()) for _ in range(8)]
 
@@ -431,8 +449,9 @@ def main():
 
             for i in range(first, first + count):
                 j = i & 7
-                dstage[j].copy_(hq[i % N_BATCHES], non_blocking=True)
-                pend.append((sr.begin(dstage[j], TOPK, j), j))
+                dslice[j].copy_(hq_slice[i % N_BATCHES], non_blocking=True)
+                dist.all_gather_into_tensor(dstage[j], dslice[j])
+                pend.append((sr.begin(dstage[j][:NQ], TOPK, j), j))
                 if len(pend) >= 3:
                     drain_one()
             while pend:
@@ -462,7 +481,11 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     e2e_ms = float(t.item())
     e2e = {"value": NQ / (e2e_ms / 1e3), "unit": UNIT, "ms_per_step": e2e_ms,
-           "h2d_bytes_per_step": NQ * DIM * 4 + NQ * 12 + 128, "d2h_bytes_per_step": NQ * TOPK * 16 + NQ * 4}
+           "h2d_bytes_per_step": (NQ * DIM * 4 + NQ * 12 + 128) if world == 1 else world * per * DIM * 4,
+           "d2h_bytes_per_step": (NQ * TOPK * 16 + NQ * 4) * world}
+    if world > 1:
+        e2e["note"] = (f"each rank copies its {per}-query slice host->device ({per * DIM * 4} bytes), the slices are "
+                       "all-gathered over NVLink, every rank reads the merged answer back")
 
     # ---- steady state: the same pipelined loop run for SUSTAINED_S seconds, second half timed, with the
     # clocks it settled at.  Reported next to `value` so that the burst figure is not mistaken for it.
@@ -484,8 +507,7 @@ def main():
         torch.cuda.synchronize()
         barrier()
         sts = sr.store.stats()
-        scorer_ms_sustained = (sts.scorer_kernel_ms_sum / sts.scorer_kernel_timed) if sts.scorer_kernel_timed else \
-            sts.scorer_ms_sum / max(1, sts.scorer_timed)
+        scorer_ms_sustained, scorer_span_sustained = kernel_ms_of(sts)
         sr.store.set_profiling(False)
         ts = torch.tensor([sv0.elapsed_time(sv1)], dtype=torch.float64, device=dev)
         if world > 1:
@@ -494,8 +516,7 @@ def main():
         if rank == 0:
             sustained = {"value": NQ / (sus_ms / 1e3), "unit": UNIT, "ms_per_step": sus_ms, "steps": n_half,
                          "after_s_of_load": round(n_half * sus_ms / 1e3, 2), "scorer_kernel_ms": scorer_ms_sustained,
-                         "scorer_start_skew_ms": sts.scorer_start_skew_ms_sum / max(1, sts.scorer_kernel_timed),
-                         "scorer_end_skew_ms": sts.scorer_end_skew_ms_sum / max(1, sts.scorer_kernel_timed),
+                         "scorer_kernel_span": scorer_span_sustained,
                          "clocks": sampler2.stop()}
 
     # ---- a wrong-but-fast configuration must not produce a headline: one batch of the timed workload is held
@@ -560,7 +581,8 @@ def main():
             # summary of the ncu --set full capture of this command (profiles/ncu_traffic.json, written by
             # scripts/ncu_summarize.py); null when no capture matches this configuration
             "traffic": ncu_traffic(kernel_name, world),
-            "algorithmic_bytes": alg_bytes, "kernel_ms": kernel_ms, "kernel_ms_unpipelined": scorer_ms,
+            "algorithmic_bytes": alg_bytes, "kernel_ms": kernel_ms, "kernel_span": scorer_span_timed,
+            "kernel_ms_unpipelined": scorer_ms,
             "flops_per_launch": flops, "hbm_gbs_algorithmic": hbm_achieved})
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
