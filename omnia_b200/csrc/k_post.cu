@@ -509,13 +509,14 @@ __global__ void __launch_bounds__(kPostThreads, 2) post_kernel(PostArgs a) {
 // so the exact top-k is inside the list and no certificate pass over the store is needed.
 
 constexpr int kEmitThreads = 256;
-constexpr int kEmitCand = 512;  // entries within the band of T that one block can rescore; more -> exact scan
+constexpr int kEmitCandMin = 512;  // entries within the band of T that one block can rescore (1024 when the query's
+                                   // fp64 copy leaves room in the block's ~26 KB); more -> exact scan
 constexpr int kEmitRegs = 16;   // list entries per thread held in registers during the selection
 
 struct EmitSmem {
-  unsigned long long sk[kEmitCand];  // (biased score << 32 | ~row): descending = best score first, smaller row first
-  double sd[kEmitCand];
-  int32_t sr[kEmitCand];
+  unsigned long long* sk;  // [cand] (biased score << 32 | ~row): descending = best score first, smaller row first
+  double* sd;              // [cand]
+  int32_t* sr;             // [cand]
   int cnt[3];
   int n_keep, n_b, fail;
 };
@@ -552,7 +553,14 @@ __global__ void __launch_bounds__(256) emit_seed_kernel(const int32_t* __restric
 __global__ void __launch_bounds__(kEmitThreads, 2) emit_post_kernel(EmitPostArgs a) {
   extern __shared__ __align__(16) uint8_t raw[];
   double* qd = reinterpret_cast<double*>(raw);  // [pitch]
-  EmitSmem& sm = *reinterpret_cast<EmitSmem*>(qd + a.sh.pitch);
+  __shared__ EmitSmem sm;
+  const int kEmitCand = a.cand;
+  if (threadIdx.x == 0) {
+    sm.sk = reinterpret_cast<unsigned long long*>(qd + a.sh.pitch);
+    sm.sd = reinterpret_cast<double*>(sm.sk + kEmitCand);
+    sm.sr = reinterpret_cast<int32_t*>(sm.sd + kEmitCand);
+  }
+  __syncthreads();
   const int q = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   constexpr int kWarps = kEmitThreads / 32;
   const unsigned int n_raw = a.ev.count[q];
@@ -727,6 +735,10 @@ __global__ void __launch_bounds__(kEmitThreads, 2) emit_post_kernel(EmitPostArgs
 
 bool emit_supported(int k) { return k >= 1 && k <= 256; }
 
+// Entries one block can hold: 1024 when they fit beside the query's fp64 copy in what a scorer CTA of the next
+// batch leaves free on an SM (~26 KB), 512 otherwise.
+int emit_post_capacity(int pitch) { return (size_t)pitch * 8 + 1024 * 20 + 256 <= 26 * 1024 ? 1024 : kEmitCandMin; }
+
 int launch_emit_seed(const int32_t* seed_keys, int64_t keys_per_query, const double* qnorm2, int nq, int qpad,
                      const EmitView& ev, cudaStream_t st) {
   if (qpad <= 0) return 0;
@@ -737,8 +749,9 @@ int launch_emit_seed(const int32_t* seed_keys, int64_t keys_per_query, const dou
 
 int launch_emit_post(const EmitPostArgs& a, cudaStream_t st) {
   if (a.nq <= 0) return 0;
-  if (a.K2 < a.k || a.K2 > kEmitCand) return fail_msg(-1, "emission post kernel: first round of %d rows for k = %d", a.K2, a.k);
-  const size_t smem = (size_t)a.sh.pitch * sizeof(double) + sizeof(EmitSmem);
+  if (a.K2 < a.k || a.K2 > a.cand || a.cand < kEmitCandMin)
+    return fail_msg(-1, "emission post kernel: first round of %d rows for k = %d, capacity %d", a.K2, a.k, a.cand);
+  const size_t smem = (size_t)a.sh.pitch * sizeof(double) + (size_t)a.cand * 20;
   static bool attr_set = false;
   if (!attr_set) {
     OMR_CUDA_OK(cudaFuncSetAttribute(emit_post_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 48 * 1024));

@@ -59,7 +59,7 @@ struct __align__(8) PipeBarriers {
 
 enum { kEpiTop2 = 0, kEpiPairs = 1, kEpiEmit = 2 };
 
-constexpr int kPairStageBytes = 1024 * 8 + 32;
+constexpr int kPairStageBytes = 1024 * 8 + 512;
 constexpr int kSmemBytes = kStages * kStageBytes + (int)sizeof(PipeBarriers) + kPairStageBytes + 1024;  // +1024: manual alignment
 
 // Epilogue of the recall scorer: two best keys per sub-bucket for this thread's query.
@@ -98,13 +98,21 @@ struct Top2Epilogue {
 // The slot of shared memory the self-join uses to stage pairs holds, in a recall launch, the
 // refresh warp's work: a ring of query numbers whose threshold is due for a refresh and the
 // scratch the refresh selects in.
-constexpr int kRefreshBuf = 1024;
+constexpr int kRefreshBuf = 512;
 constexpr int kRefreshSlots = 64;
+constexpr int kRing = 512;   // emissions staged per CTA between the epilogue warps and warp 3
+struct RingEntry {
+  unsigned int q1;   // query + 1, written LAST by the producer; 0 = empty
+  int row;
+  uint32_t bits;     // the fp32 score
+};
 struct RefreshQueue {
+  RingEntry ring[kRing];
   uint32_t buf[kRefreshBuf];
-  unsigned int slot[kRefreshSlots];  // query + 1; 0 = empty
+  unsigned int slot[kRefreshSlots];  // query + 1; 0 = empty (refresh requests of the direct path)
   unsigned int tail;
   unsigned int epi_done;             // epilogue warps that have finished their tiles
+  unsigned int ring_tail, ring_head;
 };
 static_assert(sizeof(RefreshQueue) <= kPairStageBytes, "RefreshQueue outgrew the pair-stage slot");
 
@@ -134,6 +142,28 @@ __device__ __noinline__ void emit_entry(int32_t* thr, unsigned int* count, unsig
   }
 }
 
+// What an epilogue thread does with a row that cleared its threshold: it drops (query, row, score) into the CTA's
+// shared-memory ring and goes back to its tile.  Warp 3 drains the ring into the per-query lists (the global
+// atomicAdd, the store, the refresh) off the epilogue's critical path: an append straight from the epilogue costs
+// a round trip to L2 per entry with the whole warp waiting, which on a 125k-row shard -- where the few hundred
+// entries per query all fall into a few dozen tiles -- was a third of the kernel's time.  A full ring (warp 3
+// behind by 128+ entries) falls back to the direct append.
+__device__ __noinline__ void emit_ring(int32_t* thr, unsigned int* count, unsigned long long* list, int cap, int k,
+                                       int trigger, RefreshQueue* rq, int q, int row, uint32_t bits) {
+  const unsigned int head = *reinterpret_cast<volatile unsigned int*>(&rq->ring_head);
+  const unsigned int tail = *reinterpret_cast<volatile unsigned int*>(&rq->ring_tail);
+  if (tail - head < (unsigned)(kRing - 128)) {   // at most 128 epilogue threads can pass this test at once
+    const unsigned int i = atomicAdd(&rq->ring_tail, 1u);
+    RingEntry* e = &rq->ring[i & (kRing - 1)];
+    e->row = row;
+    e->bits = bits;
+    __threadfence_block();
+    *reinterpret_cast<volatile unsigned int*>(&e->q1) = (unsigned)q + 1u;
+    return;
+  }
+  emit_entry(thr, count, list, cap, k, trigger, rq, q, row, bits);
+}
+
 struct EmitEpilogue {
   EmitView ev;
   const uint32_t* bitmap_row;
@@ -155,7 +185,7 @@ struct EmitEpilogue {
     while (pass) {
       const int j = __ffs(pass) - 1;
       pass &= pass - 1;
-      emit_entry(ev.thr, ev.count, ev.list, ev.cap, ev.k, ev.trigger, rq, q, row_tile * kTileRows + c * 32 + j, pick32(v, j));
+      emit_ring(ev.thr, ev.count, ev.list, ev.cap, ev.k, ev.trigger, rq, q, row_tile * kTileRows + c * 32 + j, pick32(v, j));
     }
   }
 };
@@ -172,15 +202,15 @@ __device__ void refresh_threshold(const EmitView& ev, int q, int lane, uint32_t*
   const uint32_t filt = score_to_biased(ordered_to_score(cur) + 0.75f * ev.band);
   const unsigned long long* L = ev.list + (size_t)q * ev.cap;
   int m = 0;
-  for (unsigned int i0 = 0; i0 < n && m <= kRefreshBuf - 128; i0 += 128) {
-    unsigned long long e[4];
+  for (unsigned int i0 = 0; i0 < n && m <= kRefreshBuf - 256; i0 += 256) {
+    unsigned long long e[8];   // eight loads in flight per lane: one L2 round trip per 256 entries
 #pragma unroll
-    for (int u = 0; u < 4; u++) {
+    for (int u = 0; u < 8; u++) {
       const unsigned int i = i0 + u * 32 + lane;
       e[u] = i < n ? __ldcg(L + i) : 0ull;
     }
 #pragma unroll
-    for (int u = 0; u < 4; u++) {
+    for (int u = 0; u < 8; u++) {
       const uint32_t key = (uint32_t)(e[u] >> 32);
       const bool ok = e[u] != 0ull && key >= filt;
       const unsigned int b = __ballot_sync(0xffffffffu, ok);
@@ -202,17 +232,91 @@ __device__ void refresh_threshold(const EmitView& ev, int q, int lane, uint32_t*
   __syncwarp();
 }
 
-// Body of warp 3 in an emission launch: serve refresh requests until the four epilogue warps are done.
+// Body of warp 3 in an emission launch: drain the ring into the per-query lists (one entry per lane), refresh the
+// thresholds that are due, serve the refresh requests of the direct path, until the four epilogue warps are done
+// and the ring is empty.
 __device__ void refresh_loop(const EmitView& ev, RefreshQueue* rq, int lane) {
+  unsigned int head = 0;
   while (true) {
-    unsigned int done = lane == 0 ? *reinterpret_cast<volatile unsigned int*>(&rq->epi_done) : 0u;
+    unsigned int done = 0, tail = 0;
+    if (lane == 0) {
+      done = *reinterpret_cast<volatile unsigned int*>(&rq->epi_done);
+      tail = *reinterpret_cast<volatile unsigned int*>(&rq->ring_tail);
+    }
     done = __shfl_sync(0xffffffffu, done, 0);
+    tail = __shfl_sync(0xffffffffu, tail, 0);
+    const unsigned int avail = tail - head;
+    if (avail) {
+      // up to four entries per lane per round, their four atomicAdds in flight together
+      const unsigned int n = avail < 128u ? avail : 128u;
+      int q = -1;
+      bool due = false;
+      unsigned int q1s[4], slots[4];
+      int rows[4];
+      uint32_t bitss[4];
+#pragma unroll
+      for (int u = 0; u < 4; u++) {
+        q1s[u] = 0u;
+        const unsigned int i = (unsigned)lane + 32u * u;
+        if (i < n) {
+          RingEntry* e = &rq->ring[(head + i) & (kRing - 1)];
+          while ((q1s[u] = *reinterpret_cast<volatile unsigned int*>(&e->q1)) == 0u) {   // index taken, entry still being written
+          }
+          __threadfence_block();
+          rows[u] = *reinterpret_cast<volatile int*>(&e->row);
+          bitss[u] = *reinterpret_cast<volatile uint32_t*>(&e->bits);
+          *reinterpret_cast<volatile unsigned int*>(&e->q1) = 0u;
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < 4; u++)
+        if (q1s[u]) slots[u] = atomicAdd(ev.count + (q1s[u] - 1u), 1u);
+#pragma unroll
+      for (int u = 0; u < 4; u++) {
+        if (!q1s[u]) continue;
+        const int qq = (int)q1s[u] - 1;
+        if (slots[u] < (unsigned)ev.cap) {
+          __stcg(ev.list + (size_t)qq * ev.cap + slots[u],
+                 ((unsigned long long)score_to_biased(__uint_as_float(bitss[u])) << 32) | (unsigned long long)(uint32_t)rows[u]);
+        } else if (slots[u] == (unsigned)ev.cap) {
+          atomicMax(ev.thr + qq, kOrderedPosInf);  // list full: the exact scan answers this query, stop feeding it
+        }
+        const unsigned int c1 = slots[u] + 1;
+        if ((c1 & (unsigned)(ev.trigger - 1)) == 0u || c1 == (unsigned)ev.k) {
+          due = true;
+          q = qq;
+        }
+      }
+      __syncwarp();
+      head += n;
+      if (lane == 0) *reinterpret_cast<volatile unsigned int*>(&rq->ring_head) = head;
+      // A refresh only helps tiles that are still to come, and the appends must not wait long behind it: one
+      // refresh per round of up to 128 appends, more only while the ring is nearly empty, none once the epilogue
+      // warps are done.  A dropped request leaves the threshold valid, only a little lower than it could be.
+      unsigned int b = __ballot_sync(0xffffffffu, due);
+      for (int served = 0; b && done < 4u; served++) {
+        unsigned int backlog = lane == 0 ? *reinterpret_cast<volatile unsigned int*>(&rq->ring_tail) - head : 0u;
+        backlog = __shfl_sync(0xffffffffu, backlog, 0);
+        if (served > 0 && backlog >= 32u) break;   // one refresh per round always (large k lives on them), more when idle
+        const int src = __ffs(b) - 1;
+        b &= b - 1;
+        refresh_threshold(ev, __shfl_sync(0xffffffffu, q, src), lane, rq->buf);
+      }
+      continue;
+    }
+    if (done >= 4u) break;   // ring empty (tail was read after done) and nobody left to benefit from a refresh
     const unsigned int v0 = atomicExch(&rq->slot[lane], 0u);
     const unsigned int v1 = atomicExch(&rq->slot[lane + 32], 0u);
     unsigned int b0 = __ballot_sync(0xffffffffu, v0 != 0u), b1 = __ballot_sync(0xffffffffu, v1 != 0u);
     if (!(b0 | b1)) {
-      if (done >= 4u) break;
-      __nanosleep(400);
+      if (done >= 4u) {
+        // the epilogue warps counted themselves done after their last emission: one more look at the ring
+        unsigned int t2 = lane == 0 ? *reinterpret_cast<volatile unsigned int*>(&rq->ring_tail) : 0u;
+        t2 = __shfl_sync(0xffffffffu, t2, 0);
+        if (t2 == head) break;
+        continue;
+      }
+      __nanosleep(200);
       continue;
     }
     while (b0) {
@@ -478,9 +582,12 @@ __global__ void __launch_bounds__(kNumThreads, 1)
   }
   if (kEpi == kEpiEmit) {
     if (threadIdx.x < kRefreshSlots) rq->slot[threadIdx.x] = 0u;
+    for (int i = threadIdx.x; i < kRing; i += kNumThreads) rq->ring[i].q1 = 0u;
     if (threadIdx.x == 0) {
       rq->tail = 0u;
       rq->epi_done = 0u;
+      rq->ring_tail = 0u;
+      rq->ring_head = 0u;
     }
   }
 
@@ -626,6 +733,7 @@ __global__ void __launch_bounds__(kNumThreads, 1)
       ptx::mbar_arrive(&bars->tmem_empty[as]);
     }
     if (kEpi == kEpiEmit) {
+      __threadfence_block();   // this warp's ring entries are visible before it counts itself done
       __syncwarp();
       if (lane == 0) atomicAdd(&rq->epi_done, 1u);
     }
@@ -734,9 +842,12 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kNumThreads, 1)
   }
   if (kEpi == kEpiEmit) {
     if (threadIdx.x < kRefreshSlots) rq->slot[threadIdx.x] = 0u;
+    for (int i = threadIdx.x; i < kRing; i += kNumThreads) rq->ring[i].q1 = 0u;
     if (threadIdx.x == 0) {
       rq->tail = 0u;
       rq->epi_done = 0u;
+      rq->ring_tail = 0u;
+      rq->ring_head = 0u;
     }
   }
   const uint32_t rank = ptx::cluster_ctarank();
@@ -887,6 +998,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kNumThreads, 1)
       ptx::mbar_arrive_cluster(&bars->tmem_empty[as], 0);
     }
     if (kEpi == kEpiEmit) {
+      __threadfence_block();   // this warp's ring entries are visible before it counts itself done
       __syncwarp();
       if (lane == 0) atomicAdd(&rq->epi_done, 1u);
     }

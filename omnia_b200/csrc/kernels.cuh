@@ -73,6 +73,7 @@ struct EmitPostArgs {
   const double* qnorm2 = nullptr;
   EmitView ev;
   int nq = 0, k = 10, K2 = 16;
+  int cand = 512;                    // entries inside the band one block can rescore (emit_post_capacity)
   const double* max_dist = nullptr;
   float margin = 0.0f;
   int64_t row_base = 0, row_stride = 1;
@@ -85,6 +86,7 @@ struct EmitPostArgs {
   int32_t* listed_total = nullptr;   // list entries consumed (diagnostics)
 };
 bool emit_supported(int k);
+int emit_post_capacity(int pitch);
 int launch_emit_post(const EmitPostArgs& a, cudaStream_t st);
 
 // ---- select / exact rescore / finalize (k_select.cu) -------------------------

@@ -697,6 +697,7 @@ int omr_store::prepare_emit(Lane& L, int qpad, int k, int n_tiles, cudaStream_t 
   ev.band = 2.0f * margin;
   ev.cap = std::min(16384, std::max(2048, pow2ceil_i(48 * k)));
   ev.trigger = std::max(32, pow2ceil_i(2 * k));
+  if (const char* e = getenv("OMR_EMIT_TRIGGER")) ev.trigger = std::max(32, pow2ceil_i(atoi(e)));   // tuning knob
   const int wave = std::max(1, num_sms / std::max(1, qpad / kQueryTile));
   *seed_n = std::min(n_tiles, std::max((k + 7) / 8 + 1, std::min(std::min(20, wave), std::max(1, n_tiles / 16))));
   *seed_kpq = (int64_t)*seed_n * (kTileRows / 32) * 2;
@@ -876,7 +877,8 @@ int omr_store::enqueue(Lane& L, const float* d_q, int nq, const uint32_t* d_bitm
     if (emit) {
       EmitPostArgs pa;
       pa.sh = sh; pa.q = d_q; pa.qnorm2 = L.qnorm2.p; pa.ev = ev;
-      pa.nq = nq; pa.k = k; pa.K2 = cfg.rescore_width > 0 ? std::min(std::max(K2, k), 512) : std::max(16, k + 6);
+      pa.cand = emit_post_capacity(pitch);
+      pa.nq = nq; pa.k = k; pa.K2 = cfg.rescore_width > 0 ? std::min(std::max(K2, k), pa.cand) : std::max(16, k + 6);
       pa.max_dist = d_maxdist; pa.margin = margin;
       pa.row_base = cfg.row_base; pa.row_stride = cfg.row_stride;
       pa.out_rows = d_rows; pa.out_dist = d_dist; pa.out_count = d_count;
