@@ -696,7 +696,10 @@ int omr_store::prepare_emit(Lane& L, int qpad, int k, int n_tiles, cudaStream_t 
   ev.k = k;
   ev.band = 2.0f * margin;
   ev.cap = std::min(16384, std::max(2048, pow2ceil_i(48 * k)));
-  ev.trigger = std::max(32, pow2ceil_i(2 * k));
+  // measured (profiles/r02_trigger_sweep.txt): a refresh costs warp 3 a few microseconds, so too small a trigger
+  // starves the appends on short shards (125k rows, k = 10: scorer 0.39 ms at 32, 0.28 ms at 128) and too large a
+  // one lets the lists of a large k overflow (k = 100: 256 and 512 are equal, 1024 sends queries to the exact scan)
+  ev.trigger = std::max(128, pow2ceil_i(2 * k));
   if (const char* e = getenv("OMR_EMIT_TRIGGER")) ev.trigger = std::max(32, pow2ceil_i(atoi(e)));   // tuning knob
   const int wave = std::max(1, num_sms / std::max(1, qpad / kQueryTile));
   *seed_n = std::min(n_tiles, std::max((k + 7) / 8 + 1, std::min(std::min(20, wave), std::max(1, n_tiles / 16))));
