@@ -551,7 +551,9 @@ def main():
         # Pairing: the timed region is K steps right after ARM_IDLE_S of idle, i.e. the burst power
         # state, so its kernel time is held against the BURST cuBLAS peak; the steady-state pass is held against
         # the sustained peak.  Neither figure is divided by the other state's peak.
-        kernel_ms = scorer_ms_timed if scorer_ms_timed > 0 else scorer_ms
+        # the single-query path has no in-kernel timer: its kernel time comes from the unpipelined pass (events
+        # around the kernel, nothing else in flight)
+        kernel_ms = scorer_ms_timed if (scorer_span_timed is not None and scorer_ms_timed > 0) else scorer_ms
         achieved = flops / (kernel_ms / 1e3) / 1e12 if kernel_ms > 0 else None
         peak_burst = float(peaks["bf16_tflops"])
         peak_sus = float(peaks.get("bf16_tflops_sustained", peak_burst))

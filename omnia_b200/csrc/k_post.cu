@@ -532,15 +532,24 @@ __global__ void __launch_bounds__(256) emit_seed_kernel(const int32_t* __restric
     const double n2 = qnorm2[q];
     if (n2 > 0.0 && n2 < INFINITY) {
       const int32_t* keys = seed_keys + (int64_t)q * kpq;
+      // the keys of this query in registers (kpq <= 40 tiles x 16 = 640 = 20 per lane), one load round trip
+      constexpr int kPer = 20;
+      uint32_t u[kPer];
+#pragma unroll
+      for (int j = 0; j < kPer; j++) {
+        const int64_t i = lane + 32 * j;
+        u[j] = i < kpq ? ((uint32_t)(__ldg(keys + i) & ~0xFF) ^ 0x80000000u) : 0u;   // kKeyNone -> 0, below every candidate
+      }
       uint32_t prefix = 0;
       for (int bit = 31; bit >= 0; bit--) {
         const uint32_t cand = prefix | (1u << bit);
         int c = 0;
-        for (int64_t j = lane; j < kpq; j += 32) c += ((uint32_t)(__ldg(keys + j) & ~0xFF) ^ 0x80000000u) >= cand;
+#pragma unroll
+        for (int j = 0; j < kPer; j++) c += u[j] >= cand;
         c = __reduce_add_sync(0xffffffffu, c);
         if (c >= ev.k) prefix = cand;
       }
-      // fewer than k keys (kKeyNone maps below every candidate value): no bound yet
+      // fewer than k keys: no bound yet
       thr = prefix == 0u ? kOrderedNegInf : score_to_ordered(biased_to_score(prefix) - ev.band);
     }
   }

@@ -177,10 +177,15 @@ struct EmitEpilogue {
   }
 
   __device__ __forceinline__ void chunk(int row_tile, int c, const uint32_t (&v)[32]) {
+    // a 31-step max decides first whether anything in the chunk can pass: the common case ends there, at half the
+    // instructions of 32 compare-and-or steps, and no bitmap word is even loaded
+    float m = __uint_as_float(v[0]);
+#pragma unroll
+    for (int j = 1; j < 32; j++) m = fmaxf(m, __uint_as_float(v[j]));
+    if (!(m >= t)) return;
     uint32_t pass = 0;
 #pragma unroll
     for (int j = 0; j < 32; j++) pass |= (__uint_as_float(v[j]) >= t) ? (1u << j) : 0u;
-    if (pass == 0u) return;  // the common case: no bitmap word is even loaded
     pass &= __ldg(bitmap_row + (int64_t)row_tile * 8 + c);
     while (pass) {
       const int j = __ffs(pass) - 1;
@@ -202,7 +207,10 @@ __device__ void refresh_threshold(const EmitView& ev, int q, int lane, uint32_t*
   const uint32_t filt = score_to_biased(ordered_to_score(cur) + 0.75f * ev.band);
   const unsigned long long* L = ev.list + (size_t)q * ev.cap;
   int m = 0;
-  for (unsigned int i0 = 0; i0 < n && m <= kRefreshBuf - 256; i0 += 256) {
+  // Only the newest entries are read: they passed the highest thresholds, so they hold the best scores, and the
+  // k-th largest of ANY k distinct rows is a valid bound.  Three round trips to L2 at most, however long the list.
+  const unsigned int first = n > 768u ? n - 768u : 0u;
+  for (unsigned int i0 = first; i0 < n && m <= kRefreshBuf - 256; i0 += 256) {
     unsigned long long e[8];   // eight loads in flight per lane: one L2 round trip per 256 entries
 #pragma unroll
     for (int u = 0; u < 8; u++) {
