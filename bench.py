@@ -386,7 +386,10 @@ def main():
             return st.scorer_ms_sum / max(1, st.scorer_timed), None
         n_t = st.scorer_kernel_timed
         span, s_skew, e_skew = st.scorer_kernel_ms_sum / n_t, st.scorer_start_skew_ms_sum / n_t, st.scorer_end_skew_ms_sum / n_t
-        return span - s_skew, {"span_ms": span, "start_skew_ms": s_skew, "end_skew_ms": e_skew}
+        return span - s_skew, {"span_ms": span, "start_skew_ms": s_skew, "end_skew_ms": e_skew,
+                               "idle_before_next_scorer_ms": st.scorer_gap_ms_sum / n_t,
+                               "post_kernel_span_ms": st.post_span_ms_sum / n_t,
+                               "post_end_after_scorer_end_ms": st.post_end_after_scorer_ms_sum / n_t}
     scorer_ms_timed, scorer_span_timed = kernel_ms_of(st1)
     phases_ms = [float(x) / max(1, st1.scorer_timed) for x in st1.phase_ms_sum]
     sr.store.set_profiling(False)

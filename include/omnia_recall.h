@@ -389,6 +389,9 @@ typedef struct omr_stats {
   int64_t join_candidates;   /* candidate pairs the self-join's tensor-core pass emitted (before the exact rescore) */
   double scorer_start_skew_ms_sum; /* latest minus earliest CTA start of those launches, summed */
   double scorer_end_skew_ms_sum;   /* latest minus earliest CTA end, summed */
+  double scorer_gap_ms_sum;        /* idle between the end of one batch's scorer and the first CTA of the next, summed */
+  double post_span_ms_sum;         /* first block start to last block end of the finishing kernel, summed */
+  double post_end_after_scorer_ms_sum; /* how long after its scorer's end a batch's finishing kernel ended, summed */
 } omr_stats;
 OMR_API int omr_get_stats(const omr_store* s, omr_stats* out);
 /* Brackets the approximate scorer (the dominant kernel) with CUDA events on the search stream

@@ -75,7 +75,8 @@ class Stats(C.Structure):
                 ("phase_ms_sum", C.c_double * 3), ("scorer_kernel_ms_sum", C.c_double),
                 ("scorer_kernel_timed", C.c_int64), ("join_candidates", C.c_int64),
                 ("scorer_start_skew_ms_sum", C.c_double),
-                ("scorer_end_skew_ms_sum", C.c_double)]
+                ("scorer_end_skew_ms_sum", C.c_double), ("scorer_gap_ms_sum", C.c_double),
+                ("post_span_ms_sum", C.c_double), ("post_end_after_scorer_ms_sum", C.c_double)]
 
 
 # name -> (restype, argtypes).  tests/test_abi.py checks this table against the header.

@@ -572,6 +572,11 @@ __global__ void __launch_bounds__(kEmitThreads, 2) emit_post_kernel(EmitPostArgs
   __syncthreads();
   const int q = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   constexpr int kWarps = kEmitThreads / 32;
+  if (a.timer && tid == 0) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    atomicMin(a.timer, t);
+  }
   const unsigned int n_raw = a.ev.count[q];
   const int n = (int)min(n_raw, (unsigned)a.ev.cap);
   unsigned long long* list = a.ev.list + (size_t)q * a.ev.cap;
@@ -593,9 +598,26 @@ __global__ void __launch_bounds__(kEmitThreads, 2) emit_post_kernel(EmitPostArgs
     e[j] = i < n ? __ldcg(list + i) : 0ull;
   }
   __syncthreads();
-  // ---- T = k-th largest approximate score in the list (bit by bit, largest prefix with >= k entries at or above it)
+  // ---- The query's final threshold is already (a lower bound of T) - band, so "every entry at or above it" holds
+  // every row of the answer; after the scorer's last refresh that set is only a little larger than the band of T
+  // itself.  Only when it does not fit the block's capacity is T found exactly (k-th largest entry, bit by bit,
+  // 32 block-wide rounds) and the band cut at T - band.
+  const int32_t thr_final = a.ev.thr[q];
+  const uint32_t cut0 = thr_final == kOrderedPosInf ? 0xFFFFFFFFu : max(1u, (uint32_t)thr_final ^ 0x80000000u);
+  {
+    int c = 0;
+#pragma unroll
+    for (int j = 0; j < kEmitRegs; j++) c += (uint32_t)(e[j] >> 32) >= cut0;
+    for (int i = kEmitRegs * kEmitThreads + tid; i < n; i += kEmitThreads) c += (uint32_t)(__ldcg(list + i) >> 32) >= cut0;
+    c = __reduce_add_sync(0xffffffffu, c);
+    if (lane == 0 && c) atomicAdd(&sm.n_b, c);
+  }
+  __syncthreads();
+  const bool loose_fits = sm.n_b <= kEmitCand;
+  __syncthreads();
+  if (tid == 0) sm.n_b = 0;
   uint32_t prefix = 0;
-  for (int bit = 31; bit >= 0; bit--) {
+  for (int bit = loose_fits ? -1 : 31; bit >= 0; bit--) {
     const uint32_t cand = prefix | (1u << bit);
     int c = 0;
 #pragma unroll
@@ -609,7 +631,7 @@ __global__ void __launch_bounds__(kEmitThreads, 2) emit_post_kernel(EmitPostArgs
     if (*slot >= a.k) prefix = cand;
   }
   // ---- keep what lies within the band of T (everything when the list holds fewer than k rows)
-  uint32_t cut = prefix == 0u ? 1u : score_to_biased(biased_to_score(prefix) - a.ev.band);
+  uint32_t cut = loose_fits ? cut0 : (prefix == 0u ? 1u : score_to_biased(biased_to_score(prefix) - a.ev.band));
   if (maxd < INFINITY) {  // `<= maxDistance`: a row that passes scores at least 1 - maxd - margin approximately
     const uint32_t c2 = score_to_biased((float)(1.0 - maxd) - a.margin - 1e-6f);
     cut = max(cut, c2);
@@ -738,6 +760,11 @@ __global__ void __launch_bounds__(kEmitThreads, 2) emit_post_kernel(EmitPostArgs
     a.out_dist[(int64_t)q * a.k + i] = ok ? sm.sd[i] : INFINITY;
   }
   if (tid == 0) a.out_count[q] = found;
+  if (a.timer && tid == 0) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    atomicMax(a.timer + 1, t);
+  }
 }
 
 }  // namespace

@@ -84,6 +84,7 @@ struct EmitPostArgs {
   int32_t* fail_count = nullptr;
   int32_t* rescued_total = nullptr;  // rows rescored in the second round
   int32_t* listed_total = nullptr;   // list entries consumed (diagnostics)
+  unsigned long long* timer = nullptr;  // nullable: [0] earliest block start, [1] latest block end (%globaltimer ns)
 };
 bool emit_supported(int k);
 int emit_post_capacity(int pitch);

@@ -219,7 +219,12 @@ struct omr_store {
     cudaStream_t stream = nullptr;
     cudaEvent_t ev_in = nullptr, ev_done = nullptr, ev0 = nullptr, ev1 = nullptr;
     cudaEvent_t ph[3] = {nullptr, nullptr, nullptr};   // profiling: before the seed pass, after it, after the post kernel
-    bool busy = false, immediate = false, timed = false, phased = false;
+    // The finishing kernel of a batch runs on a LOW-priority stream of its own (ordered by events): its thousand
+    // small blocks must not take the SMs ahead of the next batch's scorer CTAs, which need a whole SM's shared
+    // memory each and fit beside at most one of them.
+    cudaStream_t pstream = nullptr;
+    cudaEvent_t ev_scored = nullptr, ev_post = nullptr;
+    bool busy = false, immediate = false, timed = false, phased = false, want_post_timer = false;
     // the batch in flight
     const float* d_q = nullptr;
     const uint32_t* d_bitmaps = nullptr;
@@ -303,6 +308,8 @@ struct omr_store {
   double scorer_ms_sum = 0.0, phase_ms_sum[3] = {0.0, 0.0, 0.0}, kernel_ns_sum = 0.0, kernel_start_skew_ns = 0.0,
          kernel_end_skew_ns = 0.0;
   int64_t scorer_timed = 0, kernel_ns_n = 0;
+  unsigned long long last_main_end_ns = 0;
+  double gap_ns_sum = 0.0, post_ns_sum = 0.0, post_lag_ns_sum = 0.0;
   int last_path = 0, last_S = 0, last_K2 = 0;
 
   int64_t words() const { return (cap / kTileRows) * 8; }
@@ -389,13 +396,18 @@ int omr_store::open() {
   rc = make_tmap(&tmap_rows_a, d_bf16, (uint64_t)cap, kQueryTile);
   if (rc) return rc;
   for (Lane& L : lanes) {
-    OMR_CUDA_OK(cudaStreamCreateWithFlags(&L.stream, cudaStreamNonBlocking));
+    int prio_lo = 0, prio_hi = 0;
+    OMR_CUDA_OK(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));   // numerically lower = higher priority
+    OMR_CUDA_OK(cudaStreamCreateWithPriority(&L.stream, cudaStreamNonBlocking, prio_hi));
+    OMR_CUDA_OK(cudaStreamCreateWithPriority(&L.pstream, cudaStreamNonBlocking, prio_lo));
+    OMR_CUDA_OK(cudaEventCreateWithFlags(&L.ev_scored, cudaEventDisableTiming));
+    OMR_CUDA_OK(cudaEventCreateWithFlags(&L.ev_post, cudaEventDisableTiming));
     OMR_CUDA_OK(cudaEventCreateWithFlags(&L.ev_in, cudaEventDisableTiming));
     OMR_CUDA_OK(cudaEventCreateWithFlags(&L.ev_done, cudaEventDisableTiming));
     OMR_CUDA_OK(cudaEventCreate(&L.ev0));
     OMR_CUDA_OK(cudaEventCreate(&L.ev1));
     for (cudaEvent_t& e : L.ph) OMR_CUDA_OK(cudaEventCreate(&e));
-    if ((rc = L.pin.reserve(12))) return rc;
+    if ((rc = L.pin.reserve(16))) return rc;
     if ((rc = L.counters.reserve(8))) return rc;
   }
   return 0;
@@ -416,8 +428,12 @@ void omr_store::destroy() {
     L.ethr.release(); L.seed_keys.release(); L.ecount.release(); L.elist.release(); L.ktimer.release();
     L.qn.release(); L.qnorm2.release(); L.cand.release(); L.fail_list.release(); L.counters.release();
     L.extra_cnt.release(); L.timing.release(); L.pin.release();
-    for (cudaEvent_t e : {L.ev_in, L.ev_done, L.ev0, L.ev1, L.ph[0], L.ph[1], L.ph[2]})
+    for (cudaEvent_t e : {L.ev_in, L.ev_done, L.ev0, L.ev1, L.ph[0], L.ph[1], L.ph[2], L.ev_scored, L.ev_post})
       if (e) cudaEventDestroy(e);
+    if (L.pstream) {
+      cudaStreamSynchronize(L.pstream);
+      cudaStreamDestroy(L.pstream);
+    }
     if (L.stream) cudaStreamDestroy(L.stream);
   }
   for (void* p : xopened) cudaIpcCloseMemHandle(p);
@@ -853,10 +869,11 @@ int omr_store::enqueue(Lane& L, const float* d_q, int nq, const uint32_t* d_bitm
         if (profiling) {   // time the full-store scorer, not its seed: events on the stream and, since those also
                            // count the time the kernel queued behind another batch, the kernel's own %globaltimer span
           OMR_CUDA_OK(cudaEventRecord(L.ev0, st));
-          if ((rc = L.ktimer.reserve(4))) return rc;
-          OMR_CUDA_OK(cudaMemsetAsync(L.ktimer.p, 0, 32, st));
+          if ((rc = L.ktimer.reserve(6))) return rc;
+          OMR_CUDA_OK(cudaMemsetAsync(L.ktimer.p, 0, 48, st));
           OMR_CUDA_OK(cudaMemsetAsync(L.ktimer.p, 0xFF, 8, st));
           OMR_CUDA_OK(cudaMemsetAsync(L.ktimer.p + 3, 0xFF, 8, st));
+          OMR_CUDA_OK(cudaMemsetAsync(L.ktimer.p + 4, 0xFF, 8, st));
           timer = L.ktimer.p;
         }
         if (path == 4)
@@ -867,6 +884,7 @@ int omr_store::enqueue(Lane& L, const float* d_q, int nq, const uint32_t* d_bitm
                                       wpg, d_qgroup, ev, timer, num_sms, st);
         if (!rc && timer)
           OMR_CUDA_OK(cudaMemcpyAsync(L.pin.p + 4, L.ktimer.p, 32, cudaMemcpyDeviceToHost, st));
+        if (!rc && timer) L.want_post_timer = true;
       } else if (path == 4)
         rc = launch_score_umma2(L.tmap_q, tmap_rows_a, nq, qpad / (2 * kQueryTile), n_tiles, pitch / kBlockK, S, d_bitmaps, wpg,
                                 d_qgroup, L.cand.p, num_sms, st);
@@ -887,7 +905,14 @@ int omr_store::enqueue(Lane& L, const float* d_q, int nq, const uint32_t* d_bitm
       pa.out_rows = d_rows; pa.out_dist = d_dist; pa.out_count = d_count;
       pa.fail_list = L.fail_list.p; pa.fail_count = fail_count; pa.rescued_total = extra_total;
       pa.listed_total = L.counters.p + 3;
-      if ((rc = launch_emit_post(pa, st))) return rc;
+      if (L.want_post_timer) pa.timer = L.ktimer.p + 4;
+      OMR_CUDA_OK(cudaEventRecord(L.ev_scored, st));
+      OMR_CUDA_OK(cudaStreamWaitEvent(L.pstream, L.ev_scored, 0));
+      if ((rc = launch_emit_post(pa, L.pstream))) return rc;
+      OMR_CUDA_OK(cudaEventRecord(L.ev_post, L.pstream));
+      OMR_CUDA_OK(cudaStreamWaitEvent(st, L.ev_post, 0));
+      if (L.want_post_timer) OMR_CUDA_OK(cudaMemcpyAsync(L.pin.p + 12, L.ktimer.p + 4, 16, cudaMemcpyDeviceToHost, st));
+      L.want_post_timer = false;
       if (profiling) OMR_CUDA_OK(cudaEventRecord(L.ph[2], st));
       L.phased = profiling;
       st_launches += 1;
@@ -956,6 +981,16 @@ int omr_store::complete(Lane& L, cudaStream_t st) {
           kernel_start_skew_ns += (double)(t01[2] - t01[0]);
           kernel_end_skew_ns += (double)(t01[1] - t01[3]);
           kernel_ns_n++;
+          // idle between consecutive scorers on this GPU (batches are finished in the order they began)
+          if (last_main_end_ns && t01[0] > last_main_end_ns && t01[0] - last_main_end_ns < 50000000ull)
+            gap_ns_sum += (double)(t01[0] - last_main_end_ns);
+          last_main_end_ns = t01[1];
+          unsigned long long tp[2];
+          memcpy(tp, L.pin.p + 12, 16);
+          if (tp[1] > tp[0]) {
+            post_ns_sum += (double)(tp[1] - tp[0]);
+            post_lag_ns_sum += (double)(tp[1] > t01[1] ? tp[1] - t01[1] : 0);
+          }
         }
         float a = 0, b = 0, c = 0;
         OMR_CUDA_OK(cudaEventElapsedTime(&a, L.ph[0], L.ph[1]));
@@ -2549,6 +2584,9 @@ int omr_get_stats(const omr_store* s, omr_stats* out) {
   for (int i = 0; i < 3; i++) out->phase_ms_sum[i] = s->phase_ms_sum[i];
   out->scorer_kernel_ms_sum = s->kernel_ns_sum * 1e-6;
   out->scorer_kernel_timed = s->kernel_ns_n;
+  out->scorer_gap_ms_sum = s->gap_ns_sum * 1e-6;
+  out->post_span_ms_sum = s->post_ns_sum * 1e-6;
+  out->post_end_after_scorer_ms_sum = s->post_lag_ns_sum * 1e-6;
   out->join_candidates = s->st_join_candidates.load();
   out->scorer_start_skew_ms_sum = s->kernel_start_skew_ns * 1e-6;
   out->scorer_end_skew_ms_sum = s->kernel_end_skew_ns * 1e-6;
@@ -2636,6 +2674,8 @@ int omr_set_profiling(omr_store* s, int32_t on) {
   s->scorer_timed = 0;
   for (double& v : s->phase_ms_sum) v = 0.0;
   s->kernel_ns_sum = s->kernel_start_skew_ns = s->kernel_end_skew_ns = 0.0;
+  s->gap_ns_sum = s->post_ns_sum = s->post_lag_ns_sum = 0.0;
+  s->last_main_end_ns = 0;
   s->kernel_ns_n = 0;
   return OMR_OK;
 }
