@@ -49,7 +49,7 @@ def ncu_traffic(kernel: str, world: int):
     if not p.exists():
         return None
     for e in json.loads(p.read_text()):
-        if e.get("kernel") == kernel and (e.get("rows"), e.get("dim"), e.get("queries"), e.get("k"), e.get("world", 1)) == \
+        if str(e.get("kernel", "")).split("<")[0] == kernel and "<0" not in str(e.get("kernel")) and (e.get("rows"), e.get("dim"), e.get("queries"), e.get("k"), e.get("world", 1)) == \
                 (N_ROWS, DIM, NQ, TOPK, world):
             return float(e["dram_bytes_read"]) + float(e["dram_bytes_write"])
     return None

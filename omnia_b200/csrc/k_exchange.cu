@@ -91,9 +91,18 @@ __global__ void __launch_bounds__(256) exchange_merge_kernel(ExchangeView x, int
   int64_t* sr = reinterpret_cast<int64_t*>(sd + P);
   const uint8_t* own = reinterpret_cast<const uint8_t*>(x.peers[x.rank]);
   (void)epoch;
-  (void)error_word;
   const int q = blockIdx.x;
   const int G = x.world;
+  // A peer never published this batch (the wait kernel gave up): the slot holds stale or partial data.  The answer
+  // is marked unusable (count -1, empty rows) instead of merged; the host raises the error with the next call.
+  if (*reinterpret_cast<volatile unsigned int*>(error_word) != 0u) {
+    for (int i = threadIdx.x; i < k; i += blockDim.x) {
+      out_rows[(int64_t)q * k + i] = -1;
+      out_dist[(int64_t)q * k + i] = INFINITY;
+    }
+    if (threadIdx.x == 0) out_count[q] = -1;
+    return;
+  }
   for (int i = threadIdx.x; i < P; i += blockDim.x) {
     int64_t r = -1;
     double d = INFINITY;

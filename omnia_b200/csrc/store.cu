@@ -299,7 +299,7 @@ struct omr_store {
   std::vector<void*> xopened;         // peer mappings to close
   std::vector<unsigned long long> xslot_epoch;
   int xnq_max = 0, xk_max = 0;
-  DevBuf<unsigned int> xwords;        // [0..15] scatter block counters, [16] error word
+  DevBuf<unsigned int> xwords;        // [0] error word, then 16 scatter block counters per lane
   PinBuf<unsigned int> xerr_pin;
   int submit(HostReq& r);
   void run_batch(std::vector<HostReq*>& batch);
@@ -2023,6 +2023,10 @@ int omr_exchange_alloc(omr_store* s, int32_t world, int32_t nq_max, int32_t k_ma
   if (!s || !d_buf || !bytes) return fail_msg(OMR_E_INVALID, "memory: omr_exchange_alloc: null argument");
   if (world < 1 || world > kMaxWorld || nq_max < 1 || k_max < 1 || slots < 1 || slots > 64)
     return fail_msg(OMR_E_INVALID, "memory: omr_exchange_alloc: world 1..%d, slots 1..64", kMaxWorld);
+  // a slot must not be rewritten before every rank has merged it: 2 x (batches in flight) + 1
+  if (world > 1 && slots < 2 * (omr_store::kLanes - 1) + 1)
+    return fail_msg(OMR_E_INVALID, "memory: omr_exchange_alloc: at least %d slots (2 x batches in flight + 1), got %d",
+                    2 * (omr_store::kLanes - 1) + 1, slots);
   std::lock_guard<std::mutex> lk(s->mu);
   cudaSetDevice(s->cfg.device);
   if (s->xbuf) return fail_msg(OMR_E_INVALID, "memory: the exchange buffer of this store is already allocated");

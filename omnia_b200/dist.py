@@ -40,7 +40,7 @@ class ShardedRecall:
     """The local shard plus the exchange step.  With no process group it is a single shard."""
 
     def __init__(self, dim: int, n_rows_total: int, device: int, group=None, exchange: str = "nccl",
-                 nq_max: int = 1024, k_max: int = 128, slots: int = 8, **store_kw):
+                 nq_max: int = 1024, k_max: int = 128, slots: int = 9, **store_kw):
         self.group = group
         live = dist.is_available() and dist.is_initialized()
         self.rank = dist.get_rank(group) if live else 0

@@ -89,7 +89,7 @@ def rrf_fuse(fts_ranked: Sequence[str], cos_ranked: Sequence[str], k: float = RR
 
 def retrieve_hybrid(store: GPUMemoryStore, scope: Mapping[str, str], query: str, query_embedding,
                     fts_ranked: Sequence[str], rows: Mapping[str, EntityRow], limit: int = 0,
-                    min_confidence: float = 0.0, now_us: int = 0) -> Optional[List[ScoredMemory]]:
+                    min_confidence: float = 0.0, now_us: Optional[int] = None) -> Optional[List[ScoredMemory]]:
     """RetrieveHybrid (store_read.go:351-406) with the cosine arm on the GPU.
 
     Returns None when the reference falls through to the FTS-only Retrieve (empty query text or empty
@@ -181,7 +181,7 @@ class MultiTierRequest:
     half_life: TierHalfLife = field(default_factory=TierHalfLife)
 
 
-def multi_tier_filter(req: MultiTierRequest, now_us: int = 0) -> FilterSpec:
+def multi_tier_filter(req: MultiTierRequest, now_us: Optional[int] = None) -> FilterSpec:
     """The shared `candidates` predicate (retrieve_multi_tier_hybrid.go:132-138; retrieve_multi_tier.go:313-328):
     an unset user or agent means IS NULL, a set one means IS NULL OR = x."""
     return FilterSpec(req.workspace_id,
@@ -202,7 +202,7 @@ def rank_hybrid_results(results: List[ScoredMemory], ranker=None) -> None:
 
 def retrieve_multi_tier_hybrid(store: GPUMemoryStore, req: MultiTierRequest, query_embedding,
                                fts_ranked: Sequence[str], rows: Mapping[str, EntityRow],
-                               now_us: int = 0) -> Optional[List[ScoredMemory]]:
+                               now_us: Optional[int] = None) -> Optional[List[ScoredMemory]]:
     """RetrieveMultiTierHybrid (retrieve_multi_tier_hybrid.go:180-227) with the cosine arm on the GPU.
     Returns None where the reference falls through to the FTS-only RetrieveMultiTier (:181-183)."""
     if not req.query or query_embedding is None or len(query_embedding) == 0:

@@ -86,13 +86,19 @@ def _str_array(items: Sequence[str]):
     return arr
 
 
+def _now_us(now_us) -> int:
+    """The query's now() for `valid_until > now()`: the wall clock unless the caller pins it (tests do)."""
+    import time
+    return int(time.time() * 1e6) if now_us is None else int(now_us)
+
+
 class FilterSpec:
     """Reference row a8 -- the WHERE clause of a recall query.  Keeps its C strings alive."""
 
     def __init__(self, workspace_id: str, virtual_user_id: Optional[str] = None, user_mode: Optional[int] = None,
                  agent_id: Optional[str] = None, agent_mode: Optional[int] = None, kinds: Sequence[str] = (),
                  purposes: Sequence[str] = (), min_confidence: float = 0.0, max_distance: float = float("nan"),
-                 now_us: int = 0):
+                 now_us: Optional[int] = None):
         # single-tier default: a nil scope value means "no constraint" (store.go:252-253)
         if user_mode is None:
             user_mode = L.MATCH_EQ if virtual_user_id is not None else L.MATCH_ANY
@@ -102,7 +108,7 @@ class FilterSpec:
         self._purposes = _str_array(purposes)
         self.c = L.Filter(_cstr(workspace_id), _cstr(virtual_user_id), user_mode, _cstr(agent_id), agent_mode,
                           C.cast(self._kinds, L.c_str_p), len(kinds), C.cast(self._purposes, L.c_str_p),
-                          len(purposes), float(min_confidence), float(max_distance), int(now_us))
+                          len(purposes), float(min_confidence), float(max_distance), _now_us(now_us))
 
     @staticmethod
     def from_scope(scope: Dict[str, str], **kw) -> "FilterSpec":
@@ -354,7 +360,7 @@ class GPUMemoryStore:
         return rows, dist, counts
 
     def find_similar_observations(self, scope: Dict[str, str], query_embedding, k: int,
-                                  min_similarity: float, now_us: int = 0) -> List[SimilarObservation]:
+                                  min_similarity: float, now_us: Optional[int] = None) -> List[SimilarObservation]:
         """FindSimilarObservations (store_read.go:243-306): most similar first, similarity >= min."""
         if not scope.get(SCOPE_WORKSPACE_ID):
             raise L.RecallError(L.E_WORKSPACE, "memory: workspace_id is required")
@@ -367,7 +373,7 @@ class GPUMemoryStore:
     def pre_write_dedup(self, scope: Dict[str, str], embedding, *,
                         auto_supersede_above: float = DEFAULT_AUTO_SUPERSEDE_SIMILARITY,
                         surface_duplicates_above: float = DEFAULT_SURFACE_DUPLICATE_SIMILARITY,
-                        candidate_limit: int = DEFAULT_DUPLICATE_CANDIDATE_LIMIT, now_us: int = 0):
+                        candidate_limit: int = DEFAULT_DUPLICATE_CANDIDATE_LIMIT, now_us: Optional[int] = None):
         """The embedding-similarity branch of SaveMemoryWithResult (internal/memory/api/service_write.go:63-104,
         213-228): FindSimilarObservations(scope, vec, candidateLimit, surfaceDuplicatesAbove); a top match at or
         above autoSupersedeAbove routes to AppendObservationToEntity (auto-supersede), anything else lands
