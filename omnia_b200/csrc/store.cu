@@ -711,7 +711,9 @@ int omr_store::prepare_emit(Lane& L, int qpad, int k, int n_tiles, cudaStream_t 
   EmitView ev;
   ev.k = k;
   ev.band = 2.0f * margin;
-  ev.cap = std::min(16384, std::max(2048, pow2ceil_i(48 * k)));
+  // entries per query: a 10M-row scan at k = 100 ends with ~4200 on average, and a query that overflows costs an
+  // exact scan of the whole shard
+  ev.cap = std::min(16384, std::max(2048, pow2ceil_i(96 * k)));
   // measured (profiles/r02_trigger_sweep.txt): a refresh costs warp 3 a few microseconds, so too small a trigger
   // starves the appends on short shards (125k rows, k = 10: scorer 0.39 ms at 32, 0.28 ms at 128) and too large a
   // one lets the lists of a large k overflow (k = 100: 256 and 512 are equal, 1024 sends queries to the exact scan)
