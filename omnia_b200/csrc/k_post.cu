@@ -15,6 +15,7 @@
 // random order, only a few entries larger.  All of them are rescored; every key that is not
 // collected is < M, which is the bound the certificate uses.
 #include "kernels.cuh"
+#include "ptx.cuh"
 
 namespace omr {
 
@@ -526,6 +527,8 @@ struct EmitSmem {
 __global__ void __launch_bounds__(256) emit_seed_kernel(const int32_t* __restrict__ seed_keys, int64_t kpq,
                                                         const double* __restrict__ qnorm2, int nq, int qpad, EmitView ev) {
   const int q = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  ptx::grid_dep_launch();   // the full-store scorer may start loading; it waits for the thresholds itself
+  ptx::grid_dep_wait();     // the seed keys come from the kernel before this one
   if (q >= qpad) return;
   int32_t thr = kOrderedPosInf;  // padding rows of the last query tile and queries without a cosine emit nothing
   if (q < nq) {
@@ -776,10 +779,24 @@ bool emit_supported(int k) { return k >= 1 && k <= 256; }
 int emit_post_capacity(int pitch) { return (size_t)pitch * 8 + 1024 * 20 + 256 <= 26 * 1024 ? 1024 : kEmitCandMin; }
 
 int launch_emit_seed(const int32_t* seed_keys, int64_t keys_per_query, const double* qnorm2, int nq, int qpad,
-                     const EmitView& ev, cudaStream_t st) {
+                     const EmitView& ev, bool pdl, cudaStream_t st) {
   if (qpad <= 0) return 0;
-  emit_seed_kernel<<<(qpad + 7) / 8, 256, 0, st>>>(seed_keys, keys_per_query, qnorm2, nq, qpad, ev);
-  OMR_CUDA_OK(cudaGetLastError());
+  static bool attr_set = false;
+  if (!attr_set) {   // the scorer's carve-out, so that its blocks can be resident beside a scorer CTA
+    OMR_CUDA_OK(cudaFuncSetAttribute(emit_seed_kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                     cudaSharedmemCarveoutMaxShared));
+    attr_set = true;
+  }
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3((unsigned)((qpad + 7) / 8));
+  cfg.blockDim = dim3(256);
+  cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = pdl ? 1 : 0;
+  OMR_CUDA_OK(cudaLaunchKernelEx(&cfg, emit_seed_kernel, seed_keys, keys_per_query, qnorm2, nq, qpad, ev));
   return 0;
 }
 

@@ -12,16 +12,18 @@
 //               256-row x 64 box (B) land in 128B-swizzled shared memory.
 //   warp 1      one lane issues tcgen05.mma (M=128 queries, N=256 rows, K=16) four
 //               times per K block into one of two 256-column TMEM accumulators.
-//   warp 2      allocates / frees the 512 TMEM columns.
+//   warp 2      allocates / frees the 512 TMEM columns; in emission mode it spends the time between on
+//               the threshold refreshes: for a query whose list has grown by `trigger` entries it takes
+//               the k-th best entry of the list as a new lower bound of the final k-th best score.
 //   warps 4-7   epilogue: thread t owns query t of the tile (TMEM lane t), reads its
 //               256 scores 32 columns at a time with tcgen05.ld, applies the scope
 //               bitmap, and keeps the two best per S-row sub-bucket as packed keys.
 //               In the default recall mode (k <= 256) the epilogue keeps no keys at all: it
 //               compares every score with the query's running emission threshold and appends
 //               the few rows that clear it to the query's candidate list (EmitEpilogue).
-//   warp 3      (emission mode) raises the thresholds: every `trigger` appended entries of a
-//               query it takes the k-th best entry of that query's list as a new lower bound
-//               of the final k-th best score, so the epilogue warps never wait for it.
+//   warp 3      (emission mode) drains the CTA's shared-memory ring of emissions into the per-query
+//               lists in global memory and files the refresh requests, so the epilogue warps wait
+//               neither for an L2 round trip nor for a refresh.
 // While the epilogue drains accumulator i, the tensor core fills accumulator i^1.
 //
 // Rows and queries are unit-normalised before they are rounded to bf16 (k_ingest.cu),
@@ -124,7 +126,7 @@ __device__ __forceinline__ uint32_t pick32(const uint32_t (&v)[32], int j) {
 }
 
 // Appends (score, row) to query q's list; out of line so the scorer's hot loop stays small.  Every
-// `trigger`-th entry of a query (and its k-th) also files a refresh request with this CTA's warp 3.
+// `trigger`-th entry of a query (and its k-th) also files a refresh request with this CTA's warp 2.
 __device__ __noinline__ void emit_entry(int32_t* thr, unsigned int* count, unsigned long long* list, int cap, int k,
                                         int trigger, RefreshQueue* rq, int q, int row, uint32_t bits) {
   const unsigned int slot = atomicAdd(count + q, 1u);
@@ -240,10 +242,10 @@ __device__ void refresh_threshold(const EmitView& ev, int q, int lane, uint32_t*
   __syncwarp();
 }
 
-// Body of warp 3 in an emission launch: drain the ring into the per-query lists (one entry per lane), refresh the
+// Body of warp 3 in an emission launch that does not split the work (EmitView::split == 0, small k): drain the ring into the per-query lists (one entry per lane), refresh the
 // thresholds that are due, serve the refresh requests of the direct path, until the four epilogue warps are done
 // and the ring is empty.
-__device__ void refresh_loop(const EmitView& ev, RefreshQueue* rq, int lane) {
+__device__ void drain_refresh_loop(const EmitView& ev, RefreshQueue* rq, int lane) {
   unsigned int head = 0;
   while (true) {
     unsigned int done = 0, tail = 0;
@@ -324,6 +326,103 @@ __device__ void refresh_loop(const EmitView& ev, RefreshQueue* rq, int lane) {
         if (t2 == head) break;
         continue;
       }
+      __nanosleep(200);
+      continue;
+    }
+    while (b0) {
+      const int src = __ffs(b0) - 1;
+      b0 &= b0 - 1;
+      refresh_threshold(ev, (int)__shfl_sync(0xffffffffu, v0, src) - 1, lane, rq->buf);
+    }
+    while (b1) {
+      const int src = __ffs(b1) - 1;
+      b1 &= b1 - 1;
+      refresh_threshold(ev, (int)__shfl_sync(0xffffffffu, v1, src) - 1, lane, rq->buf);
+    }
+  }
+}
+
+// Body of warp 3 in an emission launch: drain the ring into the per-query lists (up to four entries per lane per
+// round, their atomicAdds in flight together) until the four epilogue warps are done and the ring is empty.  An
+// entry that takes its query's count across a multiple of `trigger` (or to k) files a refresh request for warp 2.
+// Draining and refreshing are two warps' work because at k = 100 a refresh costs as much as draining 500 entries:
+// with both on one warp (ncu, 1.25M x 768, top-100) the ring stood full, two thirds of the emissions took the direct
+// append with their whole epilogue warp waiting on L2, and the tensor pipe idled 43 % of the kernel.
+__device__ void drain_loop(const EmitView& ev, RefreshQueue* rq, int lane) {
+  unsigned int head = 0;
+  while (true) {
+    unsigned int done = 0, tail = 0;
+    if (lane == 0) {
+      done = *reinterpret_cast<volatile unsigned int*>(&rq->epi_done);
+      tail = *reinterpret_cast<volatile unsigned int*>(&rq->ring_tail);
+    }
+    done = __shfl_sync(0xffffffffu, done, 0);
+    tail = __shfl_sync(0xffffffffu, tail, 0);
+    const unsigned int avail = tail - head;
+    if (!avail) {
+      if (done >= 4u) break;   // ring empty: the tail was read after `done`, and the epilogue warps fence before counting
+      __nanosleep(100);
+      continue;
+    }
+    const unsigned int n = avail < 128u ? avail : 128u;
+    unsigned int q1s[4], slots[4];
+    int rows[4];
+    uint32_t bitss[4];
+#pragma unroll
+    for (int u = 0; u < 4; u++) {
+      q1s[u] = 0u;
+      const unsigned int i = (unsigned)lane + 32u * u;
+      if (i < n) {
+        RingEntry* e = &rq->ring[(head + i) & (kRing - 1)];
+        while ((q1s[u] = *reinterpret_cast<volatile unsigned int*>(&e->q1)) == 0u) {   // index taken, entry still being written
+        }
+        __threadfence_block();
+        rows[u] = *reinterpret_cast<volatile int*>(&e->row);
+        bitss[u] = *reinterpret_cast<volatile uint32_t*>(&e->bits);
+        *reinterpret_cast<volatile unsigned int*>(&e->q1) = 0u;
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < 4; u++)
+      if (q1s[u]) slots[u] = atomicAdd(ev.count + (q1s[u] - 1u), 1u);
+#pragma unroll
+    for (int u = 0; u < 4; u++) {
+      if (!q1s[u]) continue;
+      const int qq = (int)q1s[u] - 1;
+      if (slots[u] < (unsigned)ev.cap) {
+        __stcg(ev.list + (size_t)qq * ev.cap + slots[u],
+               ((unsigned long long)score_to_biased(__uint_as_float(bitss[u])) << 32) | (unsigned long long)(uint32_t)rows[u]);
+      } else if (slots[u] == (unsigned)ev.cap) {
+        atomicMax(ev.thr + qq, kOrderedPosInf);  // list full: the exact scan answers this query, stop feeding it
+      }
+      const unsigned int c1 = slots[u] + 1;
+      if ((c1 & (unsigned)(ev.trigger - 1)) == 0u || c1 == (unsigned)ev.k) {
+        const unsigned int i = atomicAdd(&rq->tail, 1u);
+        atomicExch(&rq->slot[i & (kRefreshSlots - 1)], q1s[u]);
+      }
+    }
+    __syncwarp();
+    head += n;
+    if (lane == 0) *reinterpret_cast<volatile unsigned int*>(&rq->ring_head) = head;
+  }
+}
+
+// Body of warp 2 (idle once it has allocated tensor memory) in an emission launch: serve the refresh requests of
+// warp 3 and of the direct path until the epilogue warps of this CTA are done -- a refresh only helps tiles that
+// are still to come.  A request that is overwritten in the 64-slot queue before it is served leaves the threshold
+// valid, only a little lower than it could be.
+__device__ void refresh_loop(const EmitView& ev, RefreshQueue* rq, int lane) {
+  while (true) {
+    unsigned int done = lane == 0 ? *reinterpret_cast<volatile unsigned int*>(&rq->epi_done) : 0u;
+    done = __shfl_sync(0xffffffffu, done, 0);
+    if (done >= 4u) break;
+    const unsigned int v0 = atomicExch(&rq->slot[lane], 0u);
+    const unsigned int v1 = atomicExch(&rq->slot[lane + 32], 0u);
+    // a query filed more than once in this sweep is served once (the lowest lane that holds it)
+    const unsigned int same0 = __match_any_sync(0xffffffffu, v0), same1 = __match_any_sync(0xffffffffu, v1);
+    unsigned int b0 = __ballot_sync(0xffffffffu, v0 != 0u && (same0 & ((1u << lane) - 1u)) == 0u);
+    unsigned int b1 = __ballot_sync(0xffffffffu, v1 != 0u && (same1 & ((1u << lane) - 1u)) == 0u);
+    if (!(b0 | b1)) {
       __nanosleep(200);
       continue;
     }
@@ -576,6 +675,9 @@ __global__ void __launch_bounds__(kNumThreads, 1)
   JoinHist* jh = reinterpret_cast<JoinHist*>(aux);           // self-join, LIMIT mode
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  // seed pass of the emission mode: the seed-threshold kernel and, behind it, the full-store scorer may be
+  // scheduled as soon as every CTA of this kernel is resident (they wait for its results themselves)
+  if (kEpi == kEpiTop2) ptx::grid_dep_launch();
   if (kSelfJoin) {
     for (int i = threadIdx.x; i < kJoinBins; i += kNumThreads) jh->bins[i] = 0u;
     if (threadIdx.x == 0) {
@@ -680,8 +782,16 @@ __global__ void __launch_bounds__(kNumThreads, 1)
       }
     }
   } else if (kEpi == kEpiEmit && warp == 3) {
-    // ---------------- threshold refresh ----------------
-    refresh_loop(args.ev, rq, lane);
+    // ---------------- ring drain ----------------
+    ptx::grid_dep_wait();   // thresholds and counts come from the seed kernel
+    if (args.ev.split) drain_loop(args.ev, rq, lane);
+    else drain_refresh_loop(args.ev, rq, lane);
+  } else if (kEpi == kEpiEmit && warp == 2) {
+    // ---------------- threshold refresh (the allocator warp has nothing else to do until the end) ----------------
+    if (args.ev.split) {
+      ptx::grid_dep_wait();
+      refresh_loop(args.ev, rq, lane);
+    }
   } else if (kSelfJoin && warp == 3) {
     if (args.pe.run_cut) join_cut_loop(args.pe, jh, lane);
   } else if (warp >= kEpilogueWarp0) {
@@ -696,6 +806,8 @@ __global__ void __launch_bounds__(kNumThreads, 1)
     ee.rq = rq;
     PairEpilogue pe = args.pe;
     pe.hist = jh;
+    // the loads and the MMAs above need nothing from the seed kernel; only the thresholds read here do
+    if (kEpi == kEpiEmit) ptx::grid_dep_wait();
     for (int64_t w = blockIdx.x; w < args.n_work; w += gridDim.x) {
       int a_tile, b_tile;
       if (!decode_work<kSelfJoin>(args.work_first + w * args.work_step, args.n_a_tiles, args.n_b_tiles, args.sb, a_tile,
@@ -836,6 +948,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kNumThreads, 1)
   JoinHist* jh = reinterpret_cast<JoinHist*>(aux);           // self-join, LIMIT mode
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  // seed pass of the emission mode: the seed-threshold kernel and, behind it, the full-store scorer may be
+  // scheduled as soon as every CTA of this kernel is resident (they wait for its results themselves)
+  if (kEpi == kEpiTop2) ptx::grid_dep_launch();
   if (kSelfJoin) {
     for (int i = threadIdx.x; i < kJoinBins; i += kNumThreads) jh->bins[i] = 0u;
     if (threadIdx.x == 0) {
@@ -945,8 +1060,16 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kNumThreads, 1)
       }
     }
   } else if (kEpi == kEpiEmit && warp == 3) {
-    // ---------------- threshold refresh (one warp per CTA) ----------------
-    refresh_loop(args.ev, rq, lane);
+    // ---------------- ring drain (one warp per CTA) ----------------
+    ptx::grid_dep_wait();   // thresholds and counts come from the seed kernel
+    if (args.ev.split) drain_loop(args.ev, rq, lane);
+    else drain_refresh_loop(args.ev, rq, lane);
+  } else if (kEpi == kEpiEmit && warp == 2) {
+    // ---------------- threshold refresh (the allocator warp has nothing else to do until the end) ----------------
+    if (args.ev.split) {
+      ptx::grid_dep_wait();
+      refresh_loop(args.ev, rq, lane);
+    }
   } else if (kSelfJoin && warp == 3) {
     if (args.pe.run_cut) join_cut_loop(args.pe, jh, lane);
   } else if (warp >= kEpilogueWarp0) {
@@ -961,6 +1084,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kNumThreads, 1)
     ee.rq = rq;
     PairEpilogue pe = args.pe;
     pe.hist = jh;
+    // the loads and the MMAs above need nothing from the seed kernel; only the thresholds read here do
+    if (kEpi == kEpiEmit) ptx::grid_dep_wait();
     for (int64_t w = cluster; w < args.n_work; w += n_clusters) {
       int a_tile, b_tile;
       if (!decode_work2<kSelfJoin>(args.work_first + w * args.work_step, args.n_a_tiles, args.n_b_tiles, args.sb, n_clusters,
@@ -1026,6 +1151,24 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kNumThreads, 1)
   }
 }
 
+// Launch with the programmatic-serialization attribute when `pdl`: the kernel may start while the kernel before it
+// on `st` still runs, and waits for that kernel's results itself (ptx::grid_dep_wait).
+template <class Kern, class... Args>
+cudaError_t launch_maybe_pdl(Kern kern, unsigned grid, unsigned block, size_t smem, cudaStream_t st, bool pdl,
+                             const Args&... args) {
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(block);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = pdl ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kern, args...);
+}
+
 template <int S>
 int launch_recall2_s(const CUtensorMap& tmap_q, const CUtensorMap& tmap_rows_half, int nq, int n_qtiles256, int n_tiles,
                      int k_blocks, const uint32_t* bitmaps, int words_per_group, const int32_t* query_group,
@@ -1089,7 +1232,7 @@ int launch_recall_s(const CUtensorMap& tmap_q, const CUtensorMap& tmap_rows, int
 
 int launch_score_umma_emit(const CUtensorMap& tmap_q, const CUtensorMap& tmap_rows, int nq, int n_qtiles, int n_tiles,
                            int k_blocks, const uint32_t* bitmaps, int words_per_group, const int32_t* query_group,
-                           const EmitView& ev, unsigned long long* timer, int num_sms, cudaStream_t st) {
+                           const EmitView& ev, unsigned long long* timer, int num_sms, bool pdl, cudaStream_t st) {
   if (n_qtiles <= 0 || n_tiles <= 0) return 0;
   KernelArgs<kEpiEmit, 256> a{};
   a.n_a_tiles = n_qtiles;
@@ -1113,15 +1256,14 @@ int launch_score_umma_emit(const CUtensorMap& tmap_q, const CUtensorMap& tmap_ro
   OMR_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
   int grid = num_sms;
   if ((int64_t)grid > a.n_work) grid = (int)a.n_work;
-  kern<<<grid, kNumThreads, kSmemBytes, st>>>(tmap_q, tmap_rows, a);
-  OMR_CUDA_OK(cudaGetLastError());
+  OMR_CUDA_OK(launch_maybe_pdl(kern, (unsigned)grid, kNumThreads, kSmemBytes, st, pdl, tmap_q, tmap_rows, a));
   return 0;
 }
 
 int launch_score_umma2_emit(const CUtensorMap& tmap_q, const CUtensorMap& tmap_rows_half, int nq, int n_qtiles256,
                             int n_tiles, int k_blocks, const uint32_t* bitmaps, int words_per_group,
                             const int32_t* query_group, const EmitView& ev, unsigned long long* timer, int num_sms,
-                            cudaStream_t st) {
+                            bool pdl, cudaStream_t st) {
   if (n_qtiles256 <= 0 || n_tiles <= 0) return 0;
   KernelArgs<kEpiEmit, 256> a{};
   a.n_a_tiles = n_qtiles256;
@@ -1141,8 +1283,7 @@ int launch_score_umma2_emit(const CUtensorMap& tmap_q, const CUtensorMap& tmap_r
   OMR_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes2));
   int64_t clusters = num_sms / 2;
   if (clusters > a.n_work) clusters = a.n_work;
-  kern<<<(unsigned)(2 * clusters), kNumThreads, kSmemBytes2, st>>>(tmap_q, tmap_rows_half, a);
-  OMR_CUDA_OK(cudaGetLastError());
+  OMR_CUDA_OK(launch_maybe_pdl(kern, (unsigned)(2 * clusters), kNumThreads, kSmemBytes2, st, pdl, tmap_q, tmap_rows_half, a));
   return 0;
 }
 

@@ -48,18 +48,22 @@ struct EmitView {
   int k = 0;
   int trigger = 32; // power of two: a threshold refresh is requested every `trigger` appended entries
   float band = 0.0f;
+  int split = 0;   // 1: warp 3 only drains the ring and warp 2 serves the refreshes (k_score_umma.cu)
 };
 // Seeds thr[] from the top-2-per-32-row keys of the first `seed_tiles` row tiles and zeroes count[].
 // Queries q >= nq (tile padding) and zero-norm queries get a threshold nothing clears.
+// `pdl` (here and in the two scorer launchers below): launch with programmatic stream serialization, so the kernel is
+// scheduled while the one before it on `st` still runs and waits on the device for that kernel's results.  Only
+// for the chain seed scorer -> seed thresholds -> full-store scorer, with nothing else enqueued between them.
 int launch_emit_seed(const int32_t* seed_keys, int64_t keys_per_query, const double* qnorm2, int nq, int qpad,
-                     const EmitView& ev, cudaStream_t st);
+                     const EmitView& ev, bool pdl, cudaStream_t st);
 int launch_score_umma_emit(const CUtensorMap& tmap_q, const CUtensorMap& tmap_rows, int nq, int n_qtiles, int n_tiles,
                            int k_blocks, const uint32_t* bitmaps, int words_per_group, const int32_t* query_group,
-                           const EmitView& ev, unsigned long long* timer, int num_sms, cudaStream_t st);
+                           const EmitView& ev, unsigned long long* timer, int num_sms, bool pdl, cudaStream_t st);
 int launch_score_umma2_emit(const CUtensorMap& tmap_q, const CUtensorMap& tmap_rows_half, int nq, int n_qtiles256,
                             int n_tiles, int k_blocks, const uint32_t* bitmaps, int words_per_group,
                             const int32_t* query_group, const EmitView& ev, unsigned long long* timer, int num_sms,
-                            cudaStream_t st);
+                            bool pdl, cudaStream_t st);
 // `timer` (nullable, device, 4 words): [0] receives the earliest and [2] the latest CTA start, [1] the latest and
 // [3] the earliest CTA end of the launch in %globaltimer nanoseconds ([0] and [3] must start at ~0ull, [1] and [2]
 // at 0): the kernel's own duration even when it queued behind another batch's kernels, which stream events

@@ -33,6 +33,13 @@ __device__ __forceinline__ unsigned long long globaltimer() {
   return t;
 }
 
+// ---- programmatic dependent launch ------------------------------------------
+// A kernel launched with cudaLaunchAttributeProgrammaticStreamSerialization may start once every CTA of the kernel
+// before it on the stream has called grid_dep_launch() (or exited); what that kernel wrote is visible only after
+// grid_dep_wait().  Both are no-ops in a kernel launched without the attribute.
+__device__ __forceinline__ void grid_dep_launch() { asm volatile("griddepcontrol.launch_dependents;"); }
+__device__ __forceinline__ void grid_dep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 // ---- mbarrier -------------------------------------------------------------
 
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {

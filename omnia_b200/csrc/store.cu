@@ -279,6 +279,7 @@ struct omr_store {
   bool live_dirty = true;
   bool post_timing = false;  // OMR_POST_TIMING=1: per-phase clock stamps of the fused post kernel
   bool legacy_post = false;  // OMR_LEGACY_POST=1: use the unfused select/rescore/finalize chain
+  bool use_pdl = true;       // OMR_PDL=0: plain stream order between seed scorer, seed thresholds and scorer
 
   std::atomic<int64_t> st_launches{0}, st_searches{0}, st_queries{0}, st_rescued{0}, st_fallback{0}, st_listed{0}, st_join_candidates{0};
   // Coalescing of concurrent host calls (dedup-on-write micro-batching): while one
@@ -719,8 +720,12 @@ int omr_store::prepare_emit(Lane& L, int qpad, int k, int n_tiles, cudaStream_t 
   // one lets the lists of a large k overflow (k = 100: 256 and 512 are equal, 1024 sends queries to the exact scan)
   ev.trigger = std::max(128, pow2ceil_i(2 * k));
   if (const char* e = getenv("OMR_EMIT_TRIGGER")) ev.trigger = std::max(32, pow2ceil_i(atoi(e)));   // tuning knob
+  ev.split = k > 32 ? 1 : 0;
+  if (const char* e = getenv("OMR_EMIT_SPLIT")) ev.split = e[0] != '0';   // tuning knob
   const int wave = std::max(1, num_sms / std::max(1, qpad / kQueryTile));
   *seed_n = std::min(n_tiles, std::max((k + 7) / 8 + 1, std::min(std::min(20, wave), std::max(1, n_tiles / 16))));
+  if (const char* e = getenv("OMR_SEED_TILES"))   // tuning knob; never fewer tiles than hold k keys
+    *seed_n = std::min(n_tiles, std::max((k + 7) / 8 + 1, std::min(40, atoi(e))));
   *seed_kpq = (int64_t)*seed_n * (kTileRows / 32) * 2;
   if ((rc = L.ethr.reserve((size_t)qpad))) return rc;
   if ((rc = L.ecount.reserve((size_t)qpad))) return rc;
@@ -860,30 +865,38 @@ int omr_store::enqueue(Lane& L, const float* d_q, int nq, const uint32_t* d_bitm
         L.tmap_q_rows = L.qn.n / pitch;
       }
       if (emit) {
-        if (profiling) OMR_CUDA_OK(cudaEventRecord(L.ph[0], st));
-        rc = launch_score_umma(L.tmap_q, tmap_rows_b, nq, qpad / kQueryTile, seed_n, pitch / kBlockK, 32, d_bitmaps, wpg,
-                               d_qgroup, L.seed_keys.p, num_sms, st);
-        if (rc) return rc;
-        if (profiling) OMR_CUDA_OK(cudaEventRecord(L.ph[1], st));
-        if ((rc = launch_emit_seed(L.seed_keys.p, seed_kpq, L.qnorm2.p, nq, qpad, ev, st))) return rc;
-        st_launches += 2;
+        // The three kernels are chained by programmatic dependent launch: the full-store scorer is scheduled onto
+        // SMs as they come free and runs its loads and MMAs while the seed finishes; only its threshold reads wait.
+        // Nothing may be enqueued between them, so with the chain on, the stream events of the two seed phases
+        // collapse onto its start and the scorer is timed by its own %globaltimer span alone.
+        const bool pdl = use_pdl;
         unsigned long long* timer = nullptr;
-        if (profiling) {   // time the full-store scorer, not its seed: events on the stream and, since those also
-                           // count the time the kernel queued behind another batch, the kernel's own %globaltimer span
-          OMR_CUDA_OK(cudaEventRecord(L.ev0, st));
+        if (profiling) {
           if ((rc = L.ktimer.reserve(6))) return rc;
           OMR_CUDA_OK(cudaMemsetAsync(L.ktimer.p, 0, 48, st));
           OMR_CUDA_OK(cudaMemsetAsync(L.ktimer.p, 0xFF, 8, st));
-          OMR_CUDA_OK(cudaMemsetAsync(L.ktimer.p + 3, 0xFF, 8, st));
-          OMR_CUDA_OK(cudaMemsetAsync(L.ktimer.p + 4, 0xFF, 8, st));
+          OMR_CUDA_OK(cudaMemsetAsync(L.ktimer.p + 3, 0xFF, 16, st));
           timer = L.ktimer.p;
+          OMR_CUDA_OK(cudaEventRecord(L.ph[0], st));
+          if (pdl) {
+            OMR_CUDA_OK(cudaEventRecord(L.ph[1], st));
+            OMR_CUDA_OK(cudaEventRecord(L.ev0, st));
+          }
         }
+        rc = launch_score_umma(L.tmap_q, tmap_rows_b, nq, qpad / kQueryTile, seed_n, pitch / kBlockK, 32, d_bitmaps, wpg,
+                               d_qgroup, L.seed_keys.p, num_sms, st);
+        if (rc) return rc;
+        if (profiling && !pdl) OMR_CUDA_OK(cudaEventRecord(L.ph[1], st));
+        if ((rc = launch_emit_seed(L.seed_keys.p, seed_kpq, L.qnorm2.p, nq, qpad, ev, pdl, st))) return rc;
+        st_launches += 2;
+        // without the chain: time the full-store scorer, not its seed, by events on the stream as well
+        if (profiling && !pdl) OMR_CUDA_OK(cudaEventRecord(L.ev0, st));
         if (path == 4)
           rc = launch_score_umma2_emit(L.tmap_q, tmap_rows_a, nq, qpad / (2 * kQueryTile), n_tiles, pitch / kBlockK,
-                                       d_bitmaps, wpg, d_qgroup, ev, timer, num_sms, st);
+                                       d_bitmaps, wpg, d_qgroup, ev, timer, num_sms, pdl, st);
         else
           rc = launch_score_umma_emit(L.tmap_q, tmap_rows_b, nq, qpad / kQueryTile, n_tiles, pitch / kBlockK, d_bitmaps,
-                                      wpg, d_qgroup, ev, timer, num_sms, st);
+                                      wpg, d_qgroup, ev, timer, num_sms, pdl, st);
         if (!rc && timer)
           OMR_CUDA_OK(cudaMemcpyAsync(L.pin.p + 4, L.ktimer.p, 32, cudaMemcpyDeviceToHost, st));
         if (!rc && timer) L.want_post_timer = true;
@@ -1283,6 +1296,7 @@ int omr_open(const omr_config* cfg, omr_store** out) {
   // default: the deterministic error bound of the bf16 stage, valid for every dim <= 2048
   s->margin = cfg->candidate_margin > 0 ? cfg->candidate_margin : 4.5e-3f;
   if (const char* e = getenv("OMR_LEGACY_POST")) s->legacy_post = e[0] == '1';
+  if (const char* e = getenv("OMR_PDL")) s->use_pdl = e[0] != '0';
   if (const char* e = getenv("OMR_POST_TIMING")) s->post_timing = e[0] == '1';
   if (const char* e = getenv("OMR_STREAM_LDG")) g_force_ldg_stream = e[0] == '1';
   int rc = s->open();
@@ -2638,12 +2652,12 @@ int omr_debug_time_scorer(omr_store* s, int32_t nq, int32_t path, int32_t S, int
     if (emit) {
       rc = launch_score_umma(L.tmap_q, s->tmap_rows_b, nq, qpad / kQueryTile, seed_n, s->pitch / kBlockK, 32, s->w_live.p,
                              (int)s->words(), nullptr, L.seed_keys.p, s->num_sms, st);
-      if (!rc) rc = launch_emit_seed(L.seed_keys.p, seed_kpq, L.qnorm2.p, nq, qpad, ev, st);
+      if (!rc) rc = launch_emit_seed(L.seed_keys.p, seed_kpq, L.qnorm2.p, nq, qpad, ev, s->use_pdl, st);
       if (!rc)
         rc = path == 4 ? launch_score_umma2_emit(L.tmap_q, s->tmap_rows_a, nq, qpad / (2 * kQueryTile), n_tiles,
-                                                 s->pitch / kBlockK, s->w_live.p, (int)s->words(), nullptr, ev, nullptr, s->num_sms, st)
+                                                 s->pitch / kBlockK, s->w_live.p, (int)s->words(), nullptr, ev, nullptr, s->num_sms, s->use_pdl, st)
                        : launch_score_umma_emit(L.tmap_q, s->tmap_rows_b, nq, qpad / kQueryTile, n_tiles, s->pitch / kBlockK,
-                                                s->w_live.p, (int)s->words(), nullptr, ev, nullptr, s->num_sms, st);
+                                                s->w_live.p, (int)s->words(), nullptr, ev, nullptr, s->num_sms, s->use_pdl, st);
     } else if (path == 4)
       rc = launch_score_umma2(L.tmap_q, s->tmap_rows_a, nq, qpad / (2 * kQueryTile), n_tiles, s->pitch / kBlockK, S,
                               s->w_live.p, (int)s->words(), nullptr, L.cand.p, s->num_sms, st);
