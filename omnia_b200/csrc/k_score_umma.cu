@@ -242,112 +242,14 @@ __device__ void refresh_threshold(const EmitView& ev, int q, int lane, uint32_t*
   __syncwarp();
 }
 
-// Body of warp 3 in an emission launch that does not split the work (EmitView::split == 0, small k): drain the ring into the per-query lists (one entry per lane), refresh the
-// thresholds that are due, serve the refresh requests of the direct path, until the four epilogue warps are done
-// and the ring is empty.
-__device__ void drain_refresh_loop(const EmitView& ev, RefreshQueue* rq, int lane) {
-  unsigned int head = 0;
-  while (true) {
-    unsigned int done = 0, tail = 0;
-    if (lane == 0) {
-      done = *reinterpret_cast<volatile unsigned int*>(&rq->epi_done);
-      tail = *reinterpret_cast<volatile unsigned int*>(&rq->ring_tail);
-    }
-    done = __shfl_sync(0xffffffffu, done, 0);
-    tail = __shfl_sync(0xffffffffu, tail, 0);
-    const unsigned int avail = tail - head;
-    if (avail) {
-      // up to four entries per lane per round, their four atomicAdds in flight together
-      const unsigned int n = avail < 128u ? avail : 128u;
-      int q = -1;
-      bool due = false;
-      unsigned int q1s[4], slots[4];
-      int rows[4];
-      uint32_t bitss[4];
-#pragma unroll
-      for (int u = 0; u < 4; u++) {
-        q1s[u] = 0u;
-        const unsigned int i = (unsigned)lane + 32u * u;
-        if (i < n) {
-          RingEntry* e = &rq->ring[(head + i) & (kRing - 1)];
-          while ((q1s[u] = *reinterpret_cast<volatile unsigned int*>(&e->q1)) == 0u) {   // index taken, entry still being written
-          }
-          __threadfence_block();
-          rows[u] = *reinterpret_cast<volatile int*>(&e->row);
-          bitss[u] = *reinterpret_cast<volatile uint32_t*>(&e->bits);
-          *reinterpret_cast<volatile unsigned int*>(&e->q1) = 0u;
-        }
-      }
-#pragma unroll
-      for (int u = 0; u < 4; u++)
-        if (q1s[u]) slots[u] = atomicAdd(ev.count + (q1s[u] - 1u), 1u);
-#pragma unroll
-      for (int u = 0; u < 4; u++) {
-        if (!q1s[u]) continue;
-        const int qq = (int)q1s[u] - 1;
-        if (slots[u] < (unsigned)ev.cap) {
-          __stcg(ev.list + (size_t)qq * ev.cap + slots[u],
-                 ((unsigned long long)score_to_biased(__uint_as_float(bitss[u])) << 32) | (unsigned long long)(uint32_t)rows[u]);
-        } else if (slots[u] == (unsigned)ev.cap) {
-          atomicMax(ev.thr + qq, kOrderedPosInf);  // list full: the exact scan answers this query, stop feeding it
-        }
-        const unsigned int c1 = slots[u] + 1;
-        if ((c1 & (unsigned)(ev.trigger - 1)) == 0u || c1 == (unsigned)ev.k) {
-          due = true;
-          q = qq;
-        }
-      }
-      __syncwarp();
-      head += n;
-      if (lane == 0) *reinterpret_cast<volatile unsigned int*>(&rq->ring_head) = head;
-      // A refresh only helps tiles that are still to come, and the appends must not wait long behind it: one
-      // refresh per round of up to 128 appends, more only while the ring is nearly empty, none once the epilogue
-      // warps are done.  A dropped request leaves the threshold valid, only a little lower than it could be.
-      unsigned int b = __ballot_sync(0xffffffffu, due);
-      for (int served = 0; b && done < 4u; served++) {
-        unsigned int backlog = lane == 0 ? *reinterpret_cast<volatile unsigned int*>(&rq->ring_tail) - head : 0u;
-        backlog = __shfl_sync(0xffffffffu, backlog, 0);
-        if (served > 0 && backlog >= 32u) break;   // one refresh per round always (large k lives on them), more when idle
-        const int src = __ffs(b) - 1;
-        b &= b - 1;
-        refresh_threshold(ev, __shfl_sync(0xffffffffu, q, src), lane, rq->buf);
-      }
-      continue;
-    }
-    if (done >= 4u) break;   // ring empty (tail was read after done) and nobody left to benefit from a refresh
-    const unsigned int v0 = atomicExch(&rq->slot[lane], 0u);
-    const unsigned int v1 = atomicExch(&rq->slot[lane + 32], 0u);
-    unsigned int b0 = __ballot_sync(0xffffffffu, v0 != 0u), b1 = __ballot_sync(0xffffffffu, v1 != 0u);
-    if (!(b0 | b1)) {
-      if (done >= 4u) {
-        // the epilogue warps counted themselves done after their last emission: one more look at the ring
-        unsigned int t2 = lane == 0 ? *reinterpret_cast<volatile unsigned int*>(&rq->ring_tail) : 0u;
-        t2 = __shfl_sync(0xffffffffu, t2, 0);
-        if (t2 == head) break;
-        continue;
-      }
-      __nanosleep(200);
-      continue;
-    }
-    while (b0) {
-      const int src = __ffs(b0) - 1;
-      b0 &= b0 - 1;
-      refresh_threshold(ev, (int)__shfl_sync(0xffffffffu, v0, src) - 1, lane, rq->buf);
-    }
-    while (b1) {
-      const int src = __ffs(b1) - 1;
-      b1 &= b1 - 1;
-      refresh_threshold(ev, (int)__shfl_sync(0xffffffffu, v1, src) - 1, lane, rq->buf);
-    }
-  }
-}
-
 // Body of warp 3 in an emission launch: drain the ring into the per-query lists (up to four entries per lane per
 // round, their atomicAdds in flight together) until the four epilogue warps are done and the ring is empty.  An
 // entry that takes its query's count across a multiple of `trigger` (or to k) files a refresh request for warp 2.
 // Draining and refreshing are two warps' work because at k = 100 a refresh costs as much as draining 500 entries:
 // with both on one warp (ncu, 1.25M x 768, top-100) the ring stood full, two thirds of the emissions took the direct
-// append with their whole epilogue warp waiting on L2, and the tensor pipe idled 43 % of the kernel.
+// append with their whole epilogue warp waiting on L2, and the tensor pipe idled 43 % of the kernel.  Measured on
+// one box, one warp vs two: 540 k -> 591 k queries/s there, 453 k -> 462 k at 1M x 1536 top-10, scorer 0.292 ->
+// 0.281 ms on a 125k-row shard.
 __device__ void drain_loop(const EmitView& ev, RefreshQueue* rq, int lane) {
   unsigned int head = 0;
   while (true) {
@@ -426,15 +328,23 @@ __device__ void refresh_loop(const EmitView& ev, RefreshQueue* rq, int lane) {
       __nanosleep(200);
       continue;
     }
-    while (b0) {
-      const int src = __ffs(b0) - 1;
-      b0 &= b0 - 1;
-      refresh_threshold(ev, (int)__shfl_sync(0xffffffffu, v0, src) - 1, lane, rq->buf);
-    }
-    while (b1) {
-      const int src = __ffs(b1) - 1;
-      b1 &= b1 - 1;
-      refresh_threshold(ev, (int)__shfl_sync(0xffffffffu, v1, src) - 1, lane, rq->buf);
+    // `done` is looked at before every refresh: a sweep can hold 64 requests, and the CTA must not outlive its
+    // epilogue by their service time
+    while (b0 | b1) {
+      done = lane == 0 ? *reinterpret_cast<volatile unsigned int*>(&rq->epi_done) : 0u;
+      done = __shfl_sync(0xffffffffu, done, 0);
+      if (done >= 4u) return;
+      unsigned int v;
+      if (b0) {
+        const int src = __ffs(b0) - 1;
+        b0 &= b0 - 1;
+        v = __shfl_sync(0xffffffffu, v0, src);
+      } else {
+        const int src = __ffs(b1) - 1;
+        b1 &= b1 - 1;
+        v = __shfl_sync(0xffffffffu, v1, src);
+      }
+      refresh_threshold(ev, (int)v - 1, lane, rq->buf);
     }
   }
 }
@@ -784,14 +694,11 @@ __global__ void __launch_bounds__(kNumThreads, 1)
   } else if (kEpi == kEpiEmit && warp == 3) {
     // ---------------- ring drain ----------------
     ptx::grid_dep_wait();   // thresholds and counts come from the seed kernel
-    if (args.ev.split) drain_loop(args.ev, rq, lane);
-    else drain_refresh_loop(args.ev, rq, lane);
+    drain_loop(args.ev, rq, lane);
   } else if (kEpi == kEpiEmit && warp == 2) {
     // ---------------- threshold refresh (the allocator warp has nothing else to do until the end) ----------------
-    if (args.ev.split) {
-      ptx::grid_dep_wait();
-      refresh_loop(args.ev, rq, lane);
-    }
+    ptx::grid_dep_wait();
+    refresh_loop(args.ev, rq, lane);
   } else if (kSelfJoin && warp == 3) {
     if (args.pe.run_cut) join_cut_loop(args.pe, jh, lane);
   } else if (warp >= kEpilogueWarp0) {
@@ -1062,14 +969,11 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kNumThreads, 1)
   } else if (kEpi == kEpiEmit && warp == 3) {
     // ---------------- ring drain (one warp per CTA) ----------------
     ptx::grid_dep_wait();   // thresholds and counts come from the seed kernel
-    if (args.ev.split) drain_loop(args.ev, rq, lane);
-    else drain_refresh_loop(args.ev, rq, lane);
+    drain_loop(args.ev, rq, lane);
   } else if (kEpi == kEpiEmit && warp == 2) {
     // ---------------- threshold refresh (the allocator warp has nothing else to do until the end) ----------------
-    if (args.ev.split) {
-      ptx::grid_dep_wait();
-      refresh_loop(args.ev, rq, lane);
-    }
+    ptx::grid_dep_wait();
+    refresh_loop(args.ev, rq, lane);
   } else if (kSelfJoin && warp == 3) {
     if (args.pe.run_cut) join_cut_loop(args.pe, jh, lane);
   } else if (warp >= kEpilogueWarp0) {

@@ -48,7 +48,6 @@ struct EmitView {
   int k = 0;
   int trigger = 32; // power of two: a threshold refresh is requested every `trigger` appended entries
   float band = 0.0f;
-  int split = 0;   // 1: warp 3 only drains the ring and warp 2 serves the refreshes (k_score_umma.cu)
 };
 // Seeds thr[] from the top-2-per-32-row keys of the first `seed_tiles` row tiles and zeroes count[].
 // Queries q >= nq (tile padding) and zero-norm queries get a threshold nothing clears.

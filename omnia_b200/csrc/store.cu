@@ -715,13 +715,11 @@ int omr_store::prepare_emit(Lane& L, int qpad, int k, int n_tiles, cudaStream_t 
   // entries per query: a 10M-row scan at k = 100 ends with ~4200 on average, and a query that overflows costs an
   // exact scan of the whole shard
   ev.cap = std::min(16384, std::max(2048, pow2ceil_i(96 * k)));
-  // measured (profiles/r02_trigger_sweep.txt): a refresh costs warp 3 a few microseconds, so too small a trigger
-  // starves the appends on short shards (125k rows, k = 10: scorer 0.39 ms at 32, 0.28 ms at 128) and too large a
-  // one lets the lists of a large k overflow (k = 100: 256 and 512 are equal, 1024 sends queries to the exact scan)
-  ev.trigger = std::max(128, pow2ceil_i(2 * k));
+  // measured (profiles/r02_trigger_sweep.txt, r02_refresh_warp_ab.txt): too small a trigger floods the refresh warp
+  // on short shards (125k rows, k = 10: scorer 0.39 ms at 32, 0.28 ms at 128), too large a one lets the lists of a
+  // large k grow (1.25M x 768, top-100: 570 k queries/s at 256, 590 k at 512, 574 k at 1024)
+  ev.trigger = std::max(128, pow2ceil_i(4 * k));
   if (const char* e = getenv("OMR_EMIT_TRIGGER")) ev.trigger = std::max(32, pow2ceil_i(atoi(e)));   // tuning knob
-  ev.split = k > 32 ? 1 : 0;
-  if (const char* e = getenv("OMR_EMIT_SPLIT")) ev.split = e[0] != '0';   // tuning knob
   const int wave = std::max(1, num_sms / std::max(1, qpad / kQueryTile));
   *seed_n = std::min(n_tiles, std::max((k + 7) / 8 + 1, std::min(std::min(20, wave), std::max(1, n_tiles / 16))));
   if (const char* e = getenv("OMR_SEED_TILES"))   // tuning knob; never fewer tiles than hold k keys
