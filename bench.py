@@ -345,7 +345,8 @@ def main():
     torch.cuda.synchronize()
     latency_ms = lat0.elapsed_time(lat1) / n_lat
     stp = sr.store.stats()
-    scorer_ms = stp.scorer_ms_sum / max(1, stp.scorer_timed)
+    scorer_ms = (stp.scorer_kernel_ms_sum / stp.scorer_kernel_timed if stp.scorer_kernel_timed
+                 else stp.scorer_ms_sum / max(1, stp.scorer_timed))
     sr.store.set_profiling(False)
     barrier()
 
@@ -354,28 +355,49 @@ def main():
     # hundred milliseconds of back-to-back tensor work.  Every timed arm therefore starts the same way --
     # ARM_IDLE_S of idle, W warm-up steps, K timed steps -- so `value` and `e2e` are measured in the same
     # power state instead of e2e inheriting the heat of the arms before it.
-    time.sleep(ARM_IDLE_S)
-    run_steps(0, args.warmup)
-    torch.cuda.synchronize()
-    barrier()
-    sampler = ClockSampler(local_rank, float(os.environ.get("OMNIA_BENCH_SAMPLER_S", 0.004)))
-    # the scorer kernel is timed INSIDE this region (CUDA events on the stream it is launched on, recorded by
-    # the library around that one kernel of every step), so roofline.achieved and `value` share one power state
-    sr.store.set_profiling(True)
-    st0 = sr.store.stats()
-    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    if rank == 0:
-        sampler.start()
-    torch.cuda.synchronize()
-    barrier()
-    ev0.record(stream)
-    run_steps(args.warmup, args.steps)
-    ev1.record(stream)
-    torch.cuda.synchronize()
-    barrier()
-    ms_total = ev0.elapsed_time(ev1)
-    clocks = sampler.stop() if rank == 0 else None
-    st1 = sr.store.stats()
+    def value_window():
+        """One timed window of the `value` arm: idle, W warm-up steps, K timed steps; returns the window's duration
+        (max over ranks), the clocks sampled during it and the library's counters before / after."""
+        time.sleep(ARM_IDLE_S)
+        run_steps(0, args.warmup)
+        torch.cuda.synchronize()
+        barrier()
+        sampler = ClockSampler(local_rank, float(os.environ.get("OMNIA_BENCH_SAMPLER_S", 0.004)))
+        # the scorer kernel is timed INSIDE this region (its own %globaltimer span, written by the kernel of every
+        # step), so roofline.achieved and `value` share one power state
+        sr.store.set_profiling(True)
+        s0 = sr.store.stats()
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        if rank == 0:
+            sampler.start()
+        torch.cuda.synchronize()
+        barrier()
+        ev0.record(stream)
+        run_steps(args.warmup, args.steps)
+        ev1.record(stream)
+        torch.cuda.synchronize()
+        barrier()
+        ms = ev0.elapsed_time(ev1)
+        ck = sampler.stop() if rank == 0 else None
+        s1 = sr.store.stats()
+        sr.store.set_profiling(False)
+        t = torch.tensor([ms], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item()), ck, s0, s1
+
+    ms_total, clocks, st0, st1 = value_window()
+    # A pipelined step cannot legitimately take longer than the same step run alone (latency_ms, measured above on
+    # this box).  A window that does was disturbed from outside the GPU (seen once: a 65 ms stall of the whole
+    # process, NVML samples included): it is measured again, once, and the discarded figure is reported.
+    remeasured = None
+    again = torch.tensor([1.0 if pipelined and ms_total / args.steps > 1.5 * latency_ms else 0.0], dtype=torch.float64, device=dev)
+    if world > 1:   # one decision for all ranks (rank 0's)
+        dist.broadcast(again, 0)
+    if again.item() > 0:
+        remeasured = {"discarded_ms_per_step": ms_total / args.steps, "single_step_latency_ms": latency_ms,
+                      "reason": "pipelined window slower than 1.5x the unpipelined step: disturbed, measured again once"}
+        ms_total, clocks, st0, st1 = value_window()
     # the kernel's own span (first CTA start to last CTA end, %globaltimer): with several batches in flight the
     # stream events around the kernel also count the time it queued behind the previous batch
     # With batches in flight the CTAs of one launch do not start together (an SM takes its CTA when the previous
@@ -391,12 +413,7 @@ def main():
                                "post_kernel_span_ms": st.post_span_ms_sum / n_t,
                                "post_end_after_scorer_end_ms": st.post_end_after_scorer_ms_sum / n_t}
     scorer_ms_timed, scorer_span_timed = kernel_ms_of(st1)
-    phases_ms = [float(x) / max(1, st1.scorer_timed) for x in st1.phase_ms_sum]
-    sr.store.set_profiling(False)
-    t = torch.tensor([ms_total], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms_step = float(t.item()) / args.steps
+    ms_step = ms_total / args.steps
     value = NQ / (ms_step / 1e3)
     launches = int(st1.kernel_launches - st0.kernel_launches)   # every kernel the library enqueued, merge included
 
@@ -606,10 +623,10 @@ def main():
                                    "not a bench line") % (N_ROWS / world * DIM * 2 / 1e9),
                        "rescued_rows": int(st1.rescued_rows - st0.rescued_rows),
                        "listed_entries": int(st1.listed_entries - st0.listed_entries),
-                       "phases_ms": {"seed_pass": phases_ms[0], "seed_thresholds": phases_ms[1], "scorer": scorer_ms_timed,
-                                     "post": phases_ms[2]},
+                       "scorer_kernel_ms": scorer_ms_timed,
                        "answer_check": check,
-                       "fallback_queries": int(st1.fallback_queries - st0.fallback_queries), "setup_s": round(setup_s, 1)},
+                       "fallback_queries": int(st1.fallback_queries - st0.fallback_queries), "setup_s": round(setup_s, 1),
+                       **({"remeasured": remeasured} if remeasured else {})},
             "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "roofline": roofline}
         if world == 1 and not args.no_cpu_baseline:
             qps, n, dt, threads = cpu_scan_rate(shard, hq_np[0], 12.0)

@@ -375,16 +375,18 @@ typedef struct omr_stats {
   int32_t last_sub_bucket;
   int32_t last_rescore_width;
   int32_t num_sms;
-  double scorer_ms_sum;      /* device time of the approximate scorer, summed (profiling on) */
+  double scorer_ms_sum;      /* device time of the approximate scorer, summed (profiling on, key-table paths: stream
+                                events around the kernel; emission mode reports scorer_kernel_ms_sum instead) */
   int64_t scorer_timed;      /* batches that sum covers */
   int64_t host_calls;        /* omr_search / omr_search_rows calls */
   int64_t host_batches;      /* searches they were coalesced into (concurrent calls share one pass) */
   int64_t listed_entries;    /* candidate-list entries the tensor-core scorers emitted (emission mode) */
-  double phase_ms_sum[3];    /* profiling on, emission mode: seed pass | seed thresholds | post kernel, summed over
-                                the batches scorer_timed counts (stream time between the events around each) */
+  double phase_ms_sum[3];    /* unused since the seed pass, the seed thresholds and the scorer are chained by
+                                programmatic dependent launch (no stream event fits between them); always 0 */
   double scorer_kernel_ms_sum; /* profiling on, emission mode: the scorer kernel's own span (first CTA start to last
-                                  CTA end, %globaltimer), summed; unlike scorer_ms_sum it excludes the time the
-                                  kernel queued behind another batch in flight */
+                                  CTA end, %globaltimer), summed; it excludes the time the kernel queued behind
+                                  another batch in flight.  The stamps travel with the batch's counters, so
+                                  profiling adds no stream operation to a batch */
   int64_t scorer_kernel_timed;
   int64_t join_candidates;   /* candidate pairs the self-join's tensor-core pass emitted (before the exact rescore) */
   double scorer_start_skew_ms_sum; /* latest minus earliest CTA start of those launches, summed */

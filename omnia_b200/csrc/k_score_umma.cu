@@ -658,7 +658,13 @@ __global__ void __launch_bounds__(kNumThreads, 1)
     }
   } else if (warp == 1) {
     // ---------------- MMA issuer ----------------
+    // Everything the MMAs take -- descriptors, accumulator address, barrier addresses -- is computed by the whole
+    // warp from warp-uniform values and only the instructions themselves sit under elect.sync: computed under
+    // `lane == 0`, ptxas could not prove them uniform and wrapped every tcgen05.mma in an ELECT / 5 x R2UR loop
+    // (~110 instructions per K block, more cycles than the four MMAs they issue).
     constexpr uint32_t idesc = ptx::make_idesc_bf16(kQueryTile, kTileRows);
+    const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem_base, 0);
+    const uint32_t a_base = ptx::smem_u32(smem_a), b_base = ptx::smem_u32(smem_b);
     int stage = 0;
     uint32_t phase = 0;
     uint32_t it = 0;
@@ -675,12 +681,12 @@ __global__ void __launch_bounds__(kNumThreads, 1)
       for (int kb = 0; kb < args.k_blocks; kb++) {
         if (!OMR_EXP(args, 2)) ptx::mbar_wait(&bars->full[stage], phase);
         ptx::tc_fence_after_sync();
-        if (lane == 0) {
-          const uint64_t da = ptx::make_smem_desc_sw128(ptx::smem_u32(smem_a + stage * kABytes));
-          const uint64_t db = ptx::make_smem_desc_sw128(ptx::smem_u32(smem_b + stage * kBBytes));
+        const uint64_t da = ptx::make_smem_desc_sw128(a_base + stage * kABytes);
+        const uint64_t db = ptx::make_smem_desc_sw128(b_base + stage * kBBytes);
+        const uint32_t d_tmem = tmem_u + as * kTileRows;
+        if (ptx::elect_one()) {
 #pragma unroll
-          for (int k = 0; k < kBlockK / 16; k++)
-            ptx::umma_bf16(tmem_base + as * kTileRows, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
+          for (int k = 0; k < kBlockK / 16; k++) ptx::umma_bf16(d_tmem, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
           if (!OMR_EXP(args, 2)) ptx::umma_commit(&bars->empty[stage]);  // frees the smem stage when these MMAs retire
           if (kb == args.k_blocks - 1) ptx::umma_commit(&bars->tmem_full[as]);
         }
@@ -934,7 +940,10 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kNumThreads, 1)
     }
   } else if (warp == 1 && leader) {
     // ---------------- MMA issuer (leader CTA only) ----------------
+    // operands from warp-uniform values, only the instructions under elect.sync (see the 1-CTA kernel)
     constexpr uint32_t idesc = ptx::make_idesc_bf16(2 * kQueryTile, kTileRows);
+    const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem_base, 0);
+    const uint32_t a_base = ptx::smem_u32(smem_a), b_base = ptx::smem_u32(smem_b);
     int stage = 0;
     uint32_t phase = 0, it = 0;
     for (int64_t w = cluster; w < args.n_work; w += n_clusters) {
@@ -950,12 +959,12 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kNumThreads, 1)
       for (int kb = 0; kb < args.k_blocks; kb++) {
         ptx::mbar_wait(&bars->full[stage], phase);
         ptx::tc_fence_after_sync();
-        if (lane == 0) {
-          const uint64_t da = ptx::make_smem_desc_sw128(ptx::smem_u32(smem_a + stage * kABytes));
-          const uint64_t db = ptx::make_smem_desc_sw128(ptx::smem_u32(smem_b + stage * kHalfBBytes));
+        const uint64_t da = ptx::make_smem_desc_sw128(a_base + stage * kABytes);
+        const uint64_t db = ptx::make_smem_desc_sw128(b_base + stage * kHalfBBytes);
+        const uint32_t d_tmem = tmem_u + as * kTileRows;
+        if (ptx::elect_one()) {
 #pragma unroll
-          for (int k = 0; k < kBlockK / 16; k++)
-            ptx::umma_bf16_2sm(tmem_base + as * kTileRows, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
+          for (int k = 0; k < kBlockK / 16; k++) ptx::umma_bf16_2sm(d_tmem, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
           ptx::umma_commit_2sm(&bars->empty[stage]);
           if (kb == args.k_blocks - 1) ptx::umma_commit_2sm(&bars->tmem_full[as]);
         }

@@ -211,20 +211,18 @@ struct omr_store {
     DevBuf<unsigned long long> elist;
     bool elist_dirty = true;   // a batch was enqueued past the scorer without its post kernel: lists may hold entries
     DevBuf<long long> timing;
-    DevBuf<unsigned long long> ktimer;
     PinBuf<int32_t> pin;
     CUtensorMap tmap_q{};
     size_t tmap_q_rows = 0;
     const void* tmap_q_ptr = nullptr;
     cudaStream_t stream = nullptr;
     cudaEvent_t ev_in = nullptr, ev_done = nullptr, ev0 = nullptr, ev1 = nullptr;
-    cudaEvent_t ph[3] = {nullptr, nullptr, nullptr};   // profiling: before the seed pass, after it, after the post kernel
     // The finishing kernel of a batch runs on a LOW-priority stream of its own (ordered by events): its thousand
     // small blocks must not take the SMs ahead of the next batch's scorer CTAs, which need a whole SM's shared
     // memory each and fit beside at most one of them.
     cudaStream_t pstream = nullptr;
     cudaEvent_t ev_scored = nullptr, ev_post = nullptr;
-    bool busy = false, immediate = false, timed = false, phased = false, want_post_timer = false;
+    bool busy = false, immediate = false, timed = false, phased = false;
     // the batch in flight
     const float* d_q = nullptr;
     const uint32_t* d_bitmaps = nullptr;
@@ -301,6 +299,7 @@ struct omr_store {
   std::vector<unsigned long long> xslot_epoch;
   int xnq_max = 0, xk_max = 0;
   DevBuf<unsigned int> xwords;        // [0] error word, then 16 scatter block counters per lane
+  DevBuf<int32_t> counters_init;      // what a lane's counters start a batch with: zeros, and ~0 where a time stamp takes a minimum
   PinBuf<unsigned int> xerr_pin;
   int submit(HostReq& r);
   void run_batch(std::vector<HostReq*>& batch);
@@ -396,6 +395,13 @@ int omr_store::open() {
   if (rc) return rc;
   rc = make_tmap(&tmap_rows_a, d_bf16, (uint64_t)cap, kQueryTile);
   if (rc) return rc;
+  {
+    // [0..3] counters = 0; then six 64-bit stamps: scorer earliest start (min), latest end, latest start, earliest end
+    // (min), post earliest start (min), post latest end
+    if ((rc = counters_init.reserve(16))) return rc;
+    unsigned long long t[8] = {0ull, 0ull, ~0ull, 0ull, 0ull, ~0ull, ~0ull, 0ull};
+    OMR_CUDA_OK(cudaMemcpy(counters_init.p, t, sizeof(t), cudaMemcpyHostToDevice));
+  }
   for (Lane& L : lanes) {
     int prio_lo = 0, prio_hi = 0;
     OMR_CUDA_OK(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));   // numerically lower = higher priority
@@ -407,9 +413,8 @@ int omr_store::open() {
     OMR_CUDA_OK(cudaEventCreateWithFlags(&L.ev_done, cudaEventDisableTiming));
     OMR_CUDA_OK(cudaEventCreate(&L.ev0));
     OMR_CUDA_OK(cudaEventCreate(&L.ev1));
-    for (cudaEvent_t& e : L.ph) OMR_CUDA_OK(cudaEventCreate(&e));
     if ((rc = L.pin.reserve(16))) return rc;
-    if ((rc = L.counters.reserve(8))) return rc;
+    if ((rc = L.counters.reserve(16))) return rc;   // 4 counters, then (profiling) 6 x 64-bit kernel time stamps
   }
   return 0;
 }
@@ -426,10 +431,10 @@ void omr_store::destroy() {
     L.xlocal.release(); L.xcount.release();
     L.hq.release(); L.hgroup.release(); L.hcount.release(); L.hmaxd.release(); L.hdist.release(); L.hrows.release();
     L.hbitmaps.release(); L.hfilters.release(); L.hin.release(); L.hout.release();
-    L.ethr.release(); L.seed_keys.release(); L.ecount.release(); L.elist.release(); L.ktimer.release();
+    L.ethr.release(); L.seed_keys.release(); L.ecount.release(); L.elist.release();
     L.qn.release(); L.qnorm2.release(); L.cand.release(); L.fail_list.release(); L.counters.release();
     L.extra_cnt.release(); L.timing.release(); L.pin.release();
-    for (cudaEvent_t e : {L.ev_in, L.ev_done, L.ev0, L.ev1, L.ph[0], L.ph[1], L.ph[2], L.ev_scored, L.ev_post})
+    for (cudaEvent_t e : {L.ev_in, L.ev_done, L.ev0, L.ev1, L.ev_scored, L.ev_post})
       if (e) cudaEventDestroy(e);
     if (L.pstream) {
       cudaStreamSynchronize(L.pstream);
@@ -813,7 +818,7 @@ int omr_store::enqueue(Lane& L, const float* d_q, int nq, const uint32_t* d_bitm
   }
   if (path != 3 && !emit && (rc = L.cand.reserve((size_t)qpad * kpq))) return rc;
 
-  OMR_CUDA_OK(cudaMemsetAsync(L.counters.p, 0, 4 * sizeof(int32_t), st));
+  OMR_CUDA_OK(cudaMemcpyAsync(L.counters.p, counters_init.p, 16 * sizeof(int32_t), cudaMemcpyDeviceToDevice, st));
   OMR_CUDA_OK(cudaMemsetAsync(L.extra_cnt.p, 0, (size_t)qpad * sizeof(int32_t), st));
   int32_t* extra_total = L.counters.p;
   int32_t* fail_count = L.counters.p + 1;
@@ -845,7 +850,7 @@ int omr_store::enqueue(Lane& L, const float* d_q, int nq, const uint32_t* d_bitm
   }
   L.nfail_known = -1;
   {
-    if (profiling) OMR_CUDA_OK(cudaEventRecord(L.ev0, st));
+    if (profiling && !emit) OMR_CUDA_OK(cudaEventRecord(L.ev0, st));
     if (path == 1) {
       // the streaming scorer takes 8 queries per pass over the matrix
       for (int q0 = 0; q0 < nq; q0 += 8) {
@@ -865,39 +870,22 @@ int omr_store::enqueue(Lane& L, const float* d_q, int nq, const uint32_t* d_bitm
       if (emit) {
         // The three kernels are chained by programmatic dependent launch: the full-store scorer is scheduled onto
         // SMs as they come free and runs its loads and MMAs while the seed finishes; only its threshold reads wait.
-        // Nothing may be enqueued between them, so with the chain on, the stream events of the two seed phases
-        // collapse onto its start and the scorer is timed by its own %globaltimer span alone.
+        // Nothing may be enqueued between them, so the scorer is timed by its own %globaltimer stamps (the six words
+        // behind the lane's counters, initialised and read back with them): profiling adds no stream operation.
         const bool pdl = use_pdl;
-        unsigned long long* timer = nullptr;
-        if (profiling) {
-          if ((rc = L.ktimer.reserve(6))) return rc;
-          OMR_CUDA_OK(cudaMemsetAsync(L.ktimer.p, 0, 48, st));
-          OMR_CUDA_OK(cudaMemsetAsync(L.ktimer.p, 0xFF, 8, st));
-          OMR_CUDA_OK(cudaMemsetAsync(L.ktimer.p + 3, 0xFF, 16, st));
-          timer = L.ktimer.p;
-          OMR_CUDA_OK(cudaEventRecord(L.ph[0], st));
-          if (pdl) {
-            OMR_CUDA_OK(cudaEventRecord(L.ph[1], st));
-            OMR_CUDA_OK(cudaEventRecord(L.ev0, st));
-          }
-        }
+        unsigned long long* timer = profiling ? reinterpret_cast<unsigned long long*>(L.counters.p + 4) : nullptr;
         rc = launch_score_umma(L.tmap_q, tmap_rows_b, nq, qpad / kQueryTile, seed_n, pitch / kBlockK, 32, d_bitmaps, wpg,
                                d_qgroup, L.seed_keys.p, num_sms, st);
         if (rc) return rc;
-        if (profiling && !pdl) OMR_CUDA_OK(cudaEventRecord(L.ph[1], st));
         if ((rc = launch_emit_seed(L.seed_keys.p, seed_kpq, L.qnorm2.p, nq, qpad, ev, pdl, st))) return rc;
         st_launches += 2;
-        // without the chain: time the full-store scorer, not its seed, by events on the stream as well
-        if (profiling && !pdl) OMR_CUDA_OK(cudaEventRecord(L.ev0, st));
         if (path == 4)
           rc = launch_score_umma2_emit(L.tmap_q, tmap_rows_a, nq, qpad / (2 * kQueryTile), n_tiles, pitch / kBlockK,
                                        d_bitmaps, wpg, d_qgroup, ev, timer, num_sms, pdl, st);
         else
           rc = launch_score_umma_emit(L.tmap_q, tmap_rows_b, nq, qpad / kQueryTile, n_tiles, pitch / kBlockK, d_bitmaps,
                                       wpg, d_qgroup, ev, timer, num_sms, pdl, st);
-        if (!rc && timer)
-          OMR_CUDA_OK(cudaMemcpyAsync(L.pin.p + 4, L.ktimer.p, 32, cudaMemcpyDeviceToHost, st));
-        if (!rc && timer) L.want_post_timer = true;
+        L.phased = timer != nullptr;
       } else if (path == 4)
         rc = launch_score_umma2(L.tmap_q, tmap_rows_a, nq, qpad / (2 * kQueryTile), n_tiles, pitch / kBlockK, S, d_bitmaps, wpg,
                                 d_qgroup, L.cand.p, num_sms, st);
@@ -907,7 +895,7 @@ int omr_store::enqueue(Lane& L, const float* d_q, int nq, const uint32_t* d_bitm
       if (rc) return rc;
       st_launches++;
     }
-    if (profiling) OMR_CUDA_OK(cudaEventRecord(L.ev1, st));
+    if (profiling && !emit) OMR_CUDA_OK(cudaEventRecord(L.ev1, st));
     if (emit) {
       EmitPostArgs pa;
       pa.sh = sh; pa.q = d_q; pa.qnorm2 = L.qnorm2.p; pa.ev = ev;
@@ -918,16 +906,12 @@ int omr_store::enqueue(Lane& L, const float* d_q, int nq, const uint32_t* d_bitm
       pa.out_rows = d_rows; pa.out_dist = d_dist; pa.out_count = d_count;
       pa.fail_list = L.fail_list.p; pa.fail_count = fail_count; pa.rescued_total = extra_total;
       pa.listed_total = L.counters.p + 3;
-      if (L.want_post_timer) pa.timer = L.ktimer.p + 4;
+      if (L.phased) pa.timer = reinterpret_cast<unsigned long long*>(L.counters.p + 4) + 4;
       OMR_CUDA_OK(cudaEventRecord(L.ev_scored, st));
       OMR_CUDA_OK(cudaStreamWaitEvent(L.pstream, L.ev_scored, 0));
       if ((rc = launch_emit_post(pa, L.pstream))) return rc;
       OMR_CUDA_OK(cudaEventRecord(L.ev_post, L.pstream));
       OMR_CUDA_OK(cudaStreamWaitEvent(st, L.ev_post, 0));
-      if (L.want_post_timer) OMR_CUDA_OK(cudaMemcpyAsync(L.pin.p + 12, L.ktimer.p + 4, 16, cudaMemcpyDeviceToHost, st));
-      L.want_post_timer = false;
-      if (profiling) OMR_CUDA_OK(cudaEventRecord(L.ph[2], st));
-      L.phased = profiling;
       st_launches += 1;
       L.elist_dirty = false;
     } else if (fused) {
@@ -958,8 +942,8 @@ int omr_store::enqueue(Lane& L, const float* d_q, int nq, const uint32_t* d_bitm
       if ((rc = launch_finalize_extra(fa, st))) return rc;
       st_launches += 5;
     }
-    OMR_CUDA_OK(cudaMemcpyAsync(L.pin.p, L.counters.p, 4 * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
-    L.timed = profiling;
+    OMR_CUDA_OK(cudaMemcpyAsync(L.pin.p, L.counters.p, (L.phased ? 16 : 4) * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+    L.timed = profiling && !emit;
   }
   return 0;
 }
@@ -981,35 +965,30 @@ int omr_store::complete(Lane& L, cudaStream_t st) {
     st_rescued += L.pin.p[0];
     st_listed += L.pin.p[3];
     nfail = L.pin.p[1];
-    if (L.timed) {
+    if (L.timed) {   // key-table paths: stream events around the scorer
       float ms = 0.0f;
       OMR_CUDA_OK(cudaEventElapsedTime(&ms, L.ev0, L.ev1));
       scorer_ms_sum += ms;
       scorer_timed++;
-      if (L.phased) {   // seed pass | seed thresholds | (scorer, above) | post kernel
-        unsigned long long t01[4];
-        memcpy(t01, L.pin.p + 4, 32);
-        if (t01[1] > t01[0]) {
-          kernel_ns_sum += (double)(t01[1] - t01[0]);
-          kernel_start_skew_ns += (double)(t01[2] - t01[0]);
-          kernel_end_skew_ns += (double)(t01[1] - t01[3]);
-          kernel_ns_n++;
-          // idle between consecutive scorers on this GPU (batches are finished in the order they began)
-          if (last_main_end_ns && t01[0] > last_main_end_ns && t01[0] - last_main_end_ns < 50000000ull)
-            gap_ns_sum += (double)(t01[0] - last_main_end_ns);
-          last_main_end_ns = t01[1];
-          unsigned long long tp[2];
-          memcpy(tp, L.pin.p + 12, 16);
-          if (tp[1] > tp[0]) {
-            post_ns_sum += (double)(tp[1] - tp[0]);
-            post_lag_ns_sum += (double)(tp[1] > t01[1] ? tp[1] - t01[1] : 0);
-          }
+    }
+    if (L.phased) {   // emission mode: the kernels' own %globaltimer stamps, read back with the counters
+      unsigned long long t01[4];
+      memcpy(t01, L.pin.p + 4, 32);
+      if (t01[1] > t01[0]) {
+        kernel_ns_sum += (double)(t01[1] - t01[0]);
+        kernel_start_skew_ns += (double)(t01[2] - t01[0]);
+        kernel_end_skew_ns += (double)(t01[1] - t01[3]);
+        kernel_ns_n++;
+        // idle between consecutive scorers on this GPU (batches are finished in the order they began)
+        if (last_main_end_ns && t01[0] > last_main_end_ns && t01[0] - last_main_end_ns < 50000000ull)
+          gap_ns_sum += (double)(t01[0] - last_main_end_ns);
+        last_main_end_ns = t01[1];
+        unsigned long long tp[2];
+        memcpy(tp, L.pin.p + 12, 16);
+        if (tp[1] > tp[0]) {
+          post_ns_sum += (double)(tp[1] - tp[0]);
+          post_lag_ns_sum += (double)(tp[1] > t01[1] ? tp[1] - t01[1] : 0);
         }
-        float a = 0, b = 0, c = 0;
-        OMR_CUDA_OK(cudaEventElapsedTime(&a, L.ph[0], L.ph[1]));
-        OMR_CUDA_OK(cudaEventElapsedTime(&b, L.ph[1], L.ev0));
-        OMR_CUDA_OK(cudaEventElapsedTime(&c, L.ev1, L.ph[2]));
-        phase_ms_sum[0] += a; phase_ms_sum[1] += b; phase_ms_sum[2] += c;
       }
     }
   }

@@ -49,12 +49,21 @@ def _cpu_signature() -> str:
 
 
 def build(force: bool = False) -> Path:
+    """Builds liboracle.so (once per CPU model).  Several test processes may get here together (the multi-process
+    tests on a box that has not built it yet), so the whole step holds a file lock."""
+    import fcntl
     stamp = _BUILD / "cpu.sig"
     sig = _cpu_signature()
-    if force or not _LIB.exists() or not stamp.exists() or stamp.read_text() != sig:
-        subprocess.run(["make", "-C", str(_HERE), "clean"], check=True, capture_output=True)
-    subprocess.run(["make", "-C", str(_HERE)], check=True, capture_output=True)
-    stamp.write_text(sig)
+    with open(_HERE / ".build.lock", "w") as lock:
+        fcntl.flock(lock, fcntl.LOCK_EX)
+        try:
+            if force or not _LIB.exists() or not stamp.exists() or stamp.read_text() != sig:
+                subprocess.run(["make", "-C", str(_HERE), "clean"], check=True, capture_output=True)
+            subprocess.run(["make", "-C", str(_HERE)], check=True, capture_output=True)
+            _BUILD.mkdir(exist_ok=True)
+            stamp.write_text(sig)
+        finally:
+            fcntl.flock(lock, fcntl.LOCK_UN)
     return _LIB
 
 
