@@ -614,7 +614,8 @@ def main():
                        "sharding": f"rows round-robin over {world} GPU(s)" + (", shard-local corpus generation" if local_gen else ""),
                        "pipeline": "%s batches in flight (omr_device_search_begin/_finish)" % os.environ.get("OMNIA_BENCH_DEPTH", 3) if pipelined else "none",
                        "single_step_latency_ms": latency_ms,
-                       "timing": "each timed arm: %.1f s idle, W warm-up steps, K timed steps" % ARM_IDLE_S,
+                       "timing": "each timed arm: %.1f s idle, W warm-up steps, K timed steps: `value` and `e2e` are BURST-clock "
+                                 "figures (the scorer is power-bound); the steady state under the power cap is `sustained`" % ARM_IDLE_S,
                        "sustained": sustained,
                        "exchange": ("fused peer-memory scatter + on-device flags" if exchange == "p2p" else "NCCL allgather + merge kernel") if world > 1 else "none", "scorer_path": int(st1.last_path),
                        "sub_bucket": int(st1.last_sub_bucket), "rescore_width": int(st1.last_rescore_width),
